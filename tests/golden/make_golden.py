@@ -172,6 +172,19 @@ def main():
         at[f"v_{tag}"] = vs.numpy()
         at[f"q_{tag}"] = qs.numpy()
         at[f"out_{tag}"] = torch.stack(outs).numpy()
+    # head_dim 128 (the only head size of the BASELINE shapes; what the CUDA kernel implements), bf16 cache
+    L, H, D, S = 2, 4, 128, 40
+    cfg = kvmod.KVCacheConfig(max_seq_len=S, num_layers=L, num_heads=H, head_dim=D, dtype=kvmod.KVCacheDtype.BF16)
+    cache = kvmod.KVCache(cfg)
+    gg = torch.Generator().manual_seed(11)
+    ks = torch.randn(S, 1, 1, H, D, generator=gg).to(torch.bfloat16)
+    vs = torch.randn(S, 1, 1, H, D, generator=gg).to(torch.bfloat16)
+    qs = torch.randn(S, 1, H, 1, D, generator=gg).to(torch.bfloat16)
+    outs = [kvmod.attention_with_kv_cache(qs[pos], cache, 0, ks[pos], vs[pos], pos).float() for pos in range(S)]
+    at["k_d128"] = ks.float().numpy()
+    at["v_d128"] = vs.float().numpy()
+    at["q_d128"] = qs.float().numpy()
+    at["out_d128"] = torch.stack(outs).numpy()
     mem = kvmod.compute_kv_cache_memory({"num_layers": 30, "num_heads": 5, "head_dim": 128}, 4096, kvmod.KVCacheDtype.BF16)
     at["mem_total_mb"] = np.array(mem["total_mb"])
     at["mem_per_token_kb"] = np.array(mem["per_token_kb"])

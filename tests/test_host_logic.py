@@ -1,0 +1,104 @@
+"""Host-side logic (no GPU): synthetic-weight packer, LSB<->I2_S re-blocking, page allocator,
+KV config arithmetic, sgl_kernel argument errors."""
+import numpy as np
+import pytest
+import torch
+
+import oracle as O
+from oracle import model as OM
+
+
+def test_synth_packer_equals_oracle_pack():
+    from wf_bitnet.synth import pack_i2s_numpy
+    rng = np.random.default_rng(0)
+    for n, k in [(16, 128), (40, 640), (64, 2560)]:
+        w = rng.integers(-1, 2, size=(n, k)).astype(np.float32)
+        assert np.array_equal(pack_i2s_numpy(w), O.pack_ternary(w)[0])
+
+
+def test_native_numpy_helpers_match_reference_golden(golden):
+    from wrinklefree_inference.kernels import native
+    g = golden["native"]
+    w = g["w"].astype(np.float32)
+    assert np.array_equal(native.pack_weights(w), g["packed"])
+    assert np.array_equal(native.unpack_weights(g["packed"]).astype(np.int8), g["unpacked"])
+    h = golden["hf"]
+    assert np.array_equal(native.repack_hf_weights(h["hf_packed"]), h["native_repack"])
+    a = golden["actquant"]
+    q, s = native.quantize_activations(a["x_vec"])
+    assert np.array_equal(q, a["native_q_vec"]) and s == float(a["native_s_vec"])
+
+
+def test_lsb_to_i2s_is_the_same_ternary_matrix():
+    from wrinklefree_inference.kernels import native
+    rng = np.random.default_rng(1)
+    w = rng.integers(-1, 2, size=(8, 256)).astype(np.float32)
+    assert np.array_equal(native._lsb_to_i2s(native.pack_weights(w)), O.pack_ternary(w)[0])
+    with pytest.raises(ValueError):
+        native._lsb_to_i2s(np.zeros((2, 16), np.uint8))   # K=64
+
+
+def test_page_allocator_matches_reference_semantics():
+    from sgl_kernel.kvcache import PageAllocator
+    ref = OM.PagedKVReference(num_layers=1, num_heads=1, head_dim=8, page_size=16, max_pages=100)
+    mine = PageAllocator(100)
+    assert mine.num_free_pages() == ref.num_free_pages() == 100
+    p1, p2 = mine.allocate_pages(10), ref.allocate_pages(10)
+    assert p1.dtype == torch.int32 and torch.equal(p1, p2)
+    assert len(set(p1.tolist())) == 10
+    assert mine.allocate_pages(91).shape == (0,) and mine.num_free_pages() == 90    # exhaustion: empty tensor, nothing taken
+    allp = mine.allocate_pages(90)
+    assert allp.shape == (90,) and mine.allocate_page() == -1
+    mine.free_pages(p1)
+    ref.free_pages(p2)
+    assert mine.num_free_pages() == 10
+    mine.free_page(1000)     # out of range ids are ignored
+    assert mine.num_free_pages() == 10
+    assert torch.equal(mine.allocate_pages(3), torch.tensor(p1.tolist()[::-1][:3], dtype=torch.int32))   # LIFO like the list
+
+
+def test_kv_config_arithmetic(golden):
+    from wrinklefree_inference.kv_cache import KVCacheConfig, KVCacheDtype, compute_kv_cache_memory
+    g = golden["attention"]
+    m = compute_kv_cache_memory({"num_layers": 30, "num_heads": 5, "head_dim": 128}, 4096, KVCacheDtype.BF16)
+    assert m["total_mb"] == float(g["mem_total_mb"]) and m["per_token_kb"] == float(g["mem_per_token_kb"])
+    assert KVCacheConfig(dtype=KVCacheDtype.INT8).bytes_per_token_per_layer == 2 * 32 * 128
+    assert KVCacheConfig(dtype=KVCacheDtype.FP32).bytes_per_token_per_layer == 2 * 32 * 128 * 4
+
+
+def test_sgl_kernel_argument_errors_are_value_errors():
+    from sgl_kernel.quantization import bitnet_gemm, bitnet_gemv, BITNET_BLOCK_SIZE, QK_I2_S
+    assert BITNET_BLOCK_SIZE == QK_I2_S == 128
+    with pytest.raises(ValueError, match="multiple of 128"):
+        bitnet_gemv(torch.zeros(4, 16, dtype=torch.uint8), torch.zeros(64, dtype=torch.int8), 1.0)
+    with pytest.raises(ValueError, match="in_features"):
+        bitnet_gemv(torch.zeros(4, 32, dtype=torch.uint8), torch.zeros(64, dtype=torch.int8), 1.0)
+    with pytest.raises(ValueError):
+        bitnet_gemm(torch.zeros(4, 32, dtype=torch.uint8), torch.zeros(128, dtype=torch.int8), 1.0)   # 1-D to gemm
+    with pytest.raises(ValueError):
+        bitnet_gemv(torch.zeros(4, 32, dtype=torch.uint8), torch.zeros(128, dtype=torch.float32), 1.0)
+
+
+def test_torch_ops_are_registered_under_reference_names():
+    import sgl_kernel  # noqa: F401
+    for name in ("bitnet_gemv_cpu", "bitnet_gemm_cpu", "bitnet_quantize_activations_cpu"):
+        assert hasattr(torch.ops.sgl_kernel, name)
+    # fake (meta) kernels give the reference's shapes (docs/research/sglang_optimization_plan.md:59-75)
+    pw = torch.empty(24, 32, dtype=torch.uint8, device="meta")
+    x = torch.empty(5, 128, dtype=torch.int8, device="meta")
+    assert torch.ops.sgl_kernel.bitnet_gemm_cpu(pw, x, 1.0).shape == (5, 24)
+    assert torch.ops.sgl_kernel.bitnet_gemv_cpu(pw, x[0], 1.0).shape == (24,)
+    q, s = torch.ops.sgl_kernel.bitnet_quantize_activations_cpu(torch.empty(3, 128, device="meta"))
+    assert q.dtype == torch.int8 and q.shape == (3, 128) and s.shape == (1,)
+
+
+def test_oracle_model_runs_tiny_config():
+    from wf_bitnet.synth import make_weights
+    cfg = OM.ModelConfig(hidden=256, layers=2, heads=2, kv_heads=1, head_dim=128, ffn=384, vocab=512, max_seq=64)
+    w = make_weights(cfg, seed=3)
+    m = OM.OracleModel(cfg, w, use_ref=False)
+    toks, gaps = m.generate_greedy([1, 2, 3], 4)
+    assert len(toks) == 4 and all(0 <= t < 512 for t in toks) and all(g >= 0 for g in gaps)
+    m2 = OM.OracleModel(cfg, w, use_ref=True)          # reference SIMD kernel inside the same forward
+    toks2, _ = m2.generate_greedy([1, 2, 3], 4)
+    assert toks2 == toks

@@ -1,0 +1,499 @@
+// Paged KV cache + split-KV flash-decode attention (north-star item 5).
+//
+// Replaces the reference's KV utilities:
+//   * KVCache.update / .get + attention_with_kv_cache  (src/wrinklefree_inference/kv_cache/kv_cache.py:230-369)
+//   * the GQA decode attention of scripts/direct_inference_full.py:210-244 (RoPE, cache write, SDPA)
+//   * sgl_kernel.kvcache.KVCacheManager scatter/gather  (tests/test_kv_cache_cpp.py:75-127)
+//
+// Pool layout: [page][layer][K|V][kv_head][slot][D] bf16 — the (page, layer, K|V, head) block is a
+// contiguous page_size*D*2-byte run, so a 16-token block of one head is exactly 4 KB of K and 4 KB of V.
+//
+// Decode attention is HBM-bound (2*Hkv*D*2 bytes per token per layer, every step).  Design:
+//   grid = (kv chunks, kv heads, batch); 4 warps per CTA, 2 CTAs per SM; every WARP is an independent
+//   flash-decode worker over a strided set of 16-token blocks with its own 3-stage cp.async ring
+//   (8 KB per stage, XOR-swizzled rows => conflict-free ldmatrix), so there is no block-level barrier in
+//   the streaming loop and ~100 KB of loads stay in flight per SM.  The G = H/Hkv query heads of a KV
+//   head form the (padded) M=16 rows of mma.m16n8k16 bf16: S = Q K^T (fp32), online softmax in fp32 with
+//   exp2, O += P V.  Warps are merged through shared memory; chunks are merged by a second tiny kernel.
+#include "common.cuh"
+#include "wf_bitnet.h"
+
+namespace wf {
+
+constexpr int AT_WARPS = 4;
+constexpr int AT_STAGES = 3;
+constexpr int AT_BLK = 16;                              // tokens per stage
+constexpr int AT_D = 128;                               // head_dim (all BASELINE shapes)
+constexpr int AT_ROW = AT_D * 2;                        // bytes per token row
+constexpr int AT_STAGE_BYTES = 2 * AT_BLK * AT_ROW;     // K + V
+constexpr int AT_SMEM = AT_WARPS * AT_STAGES * AT_STAGE_BYTES;   // 96 KB
+
+struct AttnParams {
+    const __nv_bfloat16* q;      // [B][H][D]
+    const __nv_bfloat16* pool;
+    const int32_t* block_table;  // [B][max_blocks]
+    const int32_t* seq_lens;     // [B]
+    int B, H, Hkv, G;
+    int layers, layer, page_size, max_blocks;
+    int chunk_blocks;            // 16-token blocks per CTA
+    int max_chunks;              // partial slots per (b, h)
+    float scale_log2e;           // softmax scale * log2(e)
+    void* out;                   // [B][H][D] bf16 or f32
+    int out_dtype;
+    float* part_o;               // [B][H][max_chunks][D]
+    float* part_ml;              // [B][H][max_chunks][2]
+    int direct;                  // 1: single chunk per sequence everywhere -> write final output
+};
+
+__device__ __forceinline__ size_t kv_block_offset(int page, int layers, int layer, int kv, int Hkv, int head, int page_size) {
+    return ((((size_t)page * layers + layer) * 2 + kv) * Hkv + head) * (size_t)page_size * AT_D;
+}
+
+__global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(const AttnParams p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int chunk = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
+    const int g = lane >> 2, t = lane & 3;
+
+    pdl_wait_prior();
+    const int seq_len = p.seq_lens[b];
+    const int nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
+    const int blk0 = chunk * p.chunk_blocks;
+    if (blk0 >= nblocks && !(chunk == 0)) return;
+    const int blk1 = min(nblocks, blk0 + p.chunk_blocks);
+    const int my_n = (blk1 - blk0 - warp + AT_WARPS - 1) / AT_WARPS;   // blocks blk0 + warp + 4*i
+    unsigned char* wsm = smem + warp * (AT_STAGES * AT_STAGE_BYTES);
+    const int32_t* bt = p.block_table + (size_t)b * p.max_blocks;
+
+    // ---- Q fragments (rows g < G valid; rows 8..15 are zero padding)
+    uint32_t qa[8][2];
+    {
+        const __nv_bfloat16* qrow = p.q + ((size_t)b * p.H + (size_t)kvh * p.G + g) * AT_D;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+            qa[ks][0] = (g < p.G) ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 2 * t) : 0u;
+            qa[ks][1] = (g < p.G) ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8 + 2 * t) : 0u;
+        }
+    }
+
+    auto issue = [&](int i) {   // i-th block of this warp -> stage i % AT_STAGES
+        if (i < my_n) {
+            const int blk = blk0 + warp + AT_WARPS * i;
+            const int tok0 = blk * AT_BLK;
+            const int page = bt[tok0 / p.page_size];
+            const int slot0 = tok0 % p.page_size;
+            const __nv_bfloat16* kb = p.pool + kv_block_offset(page, p.layers, p.layer, 0, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
+            const __nv_bfloat16* vb = p.pool + kv_block_offset(page, p.layers, p.layer, 1, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
+            unsigned char* ks = wsm + (i % AT_STAGES) * AT_STAGE_BYTES;
+            unsigned char* vs = ks + AT_BLK * AT_ROW;
+            const int valid = seq_len - tok0;   // tokens >= valid are zero-filled (pool slots may be uninitialised)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int gi = lane + 32 * j;
+                const int r = gi >> 4, c = gi & 15;
+                const int dst = r * AT_ROW + ((c ^ (r & 7)) << 4);
+                const int nb = (r < valid) ? 16 : 0;
+                cp_async16_zfill(ks + dst, reinterpret_cast<const unsigned char*>(kb) + gi * 16, nb);
+                cp_async16_zfill(vs + dst, reinterpret_cast<const unsigned char*>(vb) + gi * 16, nb);
+            }
+        }
+        cp_async_commit();
+    };
+
+    float o[16][4];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { o[j][0] = 0.f; o[j][1] = 0.f; o[j][2] = 0.f; o[j][3] = 0.f; }
+    float m_run = -INFINITY, l_run = 0.f;   // row g (replicated over the 4 lanes of a group)
+
+#pragma unroll
+    for (int s = 0; s < AT_STAGES - 1; ++s) issue(s);
+
+    for (int i = 0; i < my_n; ++i) {
+        issue(i + AT_STAGES - 1);
+        cp_async_wait<AT_STAGES - 1>();
+        __syncwarp();
+        const unsigned char* ks = wsm + (i % AT_STAGES) * AT_STAGE_BYTES;
+        const unsigned char* vs = ks + AT_BLK * AT_ROW;
+        const int tok0 = (blk0 + warp + AT_WARPS * i) * AT_BLK;
+
+        // ---- S = Q K^T : 16 (heads) x 16 (tokens)
+        float s[2][4];
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) { s[nt][0] = 0.f; s[nt][1] = 0.f; s[nt][2] = 0.f; s[nt][3] = 0.f; }
+        {
+            const int r = (lane & 7) + ((lane >> 4) << 3);   // token row supplied by this lane
+            const int gsel = (lane >> 3) & 1;                // granule parity supplied by this lane
+#pragma unroll
+            for (int ks_i = 0; ks_i < 8; ++ks_i) {
+                const int c = 2 * ks_i + gsel;
+                uint32_t b0, b1, b2, b3;
+                ldmatrix_x4(b0, b1, b2, b3, ks + r * AT_ROW + ((c ^ (r & 7)) << 4));
+                mma_bf16_16816(s[0], qa[ks_i][0], 0u, qa[ks_i][1], 0u, b0, b1);
+                mma_bf16_16816(s[1], qa[ks_i][0], 0u, qa[ks_i][1], 0u, b2, b3);
+            }
+        }
+        // ---- online softmax for row g over this block's 16 tokens (columns 8nt+2t, 8nt+2t+1)
+        float mx = -INFINITY;
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int tok = tok0 + nt * 8 + 2 * t + e;
+                const float v = (tok < seq_len) ? s[nt][e] * p.scale_log2e : -INFINITY;
+                s[nt][e] = v;
+                mx = fmaxf(mx, v);
+            }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        const float m_new = fmaxf(m_run, mx);
+        const float corr = exp2f(m_run - m_new);   // 0 on the first block (m_run = -inf)
+        float psum = 0.f;
+        uint32_t pa[4];
+        {
+            const float p00 = exp2f(s[0][0] - m_new), p01 = exp2f(s[0][1] - m_new);
+            const float p10 = exp2f(s[1][0] - m_new), p11 = exp2f(s[1][1] - m_new);
+            psum = (p00 + p01) + (p10 + p11);
+            pa[0] = pack_bf16x2(p00, p01);   // A frag: row g, k = 2t,2t+1
+            pa[1] = 0u;                      // rows 8..15 unused
+            pa[2] = pack_bf16x2(p10, p11);   // row g, k = 8+2t,..
+            pa[3] = 0u;
+        }
+        psum += __shfl_xor_sync(0xffffffffu, psum, 1);
+        psum += __shfl_xor_sync(0xffffffffu, psum, 2);
+        l_run = l_run * corr + psum;
+        m_run = m_new;
+        if (__any_sync(0xffffffffu, corr != 1.0f)) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { o[j][0] *= corr; o[j][1] *= corr; }
+        }
+        // ---- O += P V : V^T fragments via ldmatrix.trans
+        {
+            const int r = (lane & 7) + (((lane >> 3) & 1) << 3);   // token row
+            const int gsel = lane >> 4;                            // d-granule parity
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj) {
+                const int c = 2 * jj + gsel;
+                uint32_t b0, b1, b2, b3;
+                ldmatrix_x4_trans(b0, b1, b2, b3, vs + r * AT_ROW + ((c ^ (r & 7)) << 4));
+                mma_bf16_16816(o[2 * jj], pa[0], pa[1], pa[2], pa[3], b0, b1);
+                mma_bf16_16816(o[2 * jj + 1], pa[0], pa[1], pa[2], pa[3], b2, b3);
+            }
+        }
+        __syncwarp();
+    }
+    cp_async_wait<0>();
+    __syncthreads();
+
+    // ---- merge the 4 warps through shared memory: [warp][G][D] fp32 + [warp][G][2]
+    float* mo = reinterpret_cast<float*>(smem);                       // AT_WARPS * 8 * 128 floats = 16 KB
+    float* mml = mo + AT_WARPS * 8 * AT_D;                            // AT_WARPS * 8 * 2
+    if (g < p.G) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            *reinterpret_cast<float2*>(mo + ((warp * 8 + g) * AT_D) + j * 8 + 2 * t) = make_float2(o[j][0], o[j][1]);
+        }
+        if (t == 0) {
+            mml[(warp * 8 + g) * 2 + 0] = m_run;
+            mml[(warp * 8 + g) * 2 + 1] = l_run;
+        }
+    }
+    __syncthreads();
+    {
+        const int d = tid;   // 128 threads == AT_D
+        for (int hh = 0; hh < p.G; ++hh) {
+            float M = -INFINITY;
+#pragma unroll
+            for (int w = 0; w < AT_WARPS; ++w) M = fmaxf(M, mml[(w * 8 + hh) * 2]);
+            float L = 0.f, O = 0.f;
+#pragma unroll
+            for (int w = 0; w < AT_WARPS; ++w) {
+                const float mw = mml[(w * 8 + hh) * 2];
+                const float f = (mw == -INFINITY) ? 0.f : exp2f(mw - M);
+                L += mml[(w * 8 + hh) * 2 + 1] * f;
+                O += mo[(w * 8 + hh) * AT_D + d] * f;
+            }
+            const int h = kvh * p.G + hh;
+            if (p.direct) {
+                const float v = (L > 0.f) ? O / L : 0.f;
+                if (p.out_dtype == WF_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[((size_t)b * p.H + h) * AT_D + d] = __float2bfloat16_rn(v);
+                else reinterpret_cast<float*>(p.out)[((size_t)b * p.H + h) * AT_D + d] = v;
+            } else {
+                const size_t slot = ((size_t)b * p.H + h) * p.max_chunks + chunk;
+                p.part_o[slot * AT_D + d] = O;
+                if (d == 0) { p.part_ml[slot * 2] = M; p.part_ml[slot * 2 + 1] = L; }
+            }
+        }
+    }
+    pdl_launch_dependents();
+}
+
+struct MergeParams {
+    const float* part_o;
+    const float* part_ml;
+    const int32_t* seq_lens;
+    int H, max_chunks, chunk_tokens;
+    void* out;
+    int out_dtype;
+};
+
+// grid = (H, B), block = 128 (one thread per d)
+__global__ void __launch_bounds__(AT_D) attn_merge_kernel(const MergeParams p) {
+    const int h = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
+    pdl_wait_prior();
+    const int seq_len = p.seq_lens[b];
+    const int nch = (seq_len + p.chunk_tokens - 1) / p.chunk_tokens;
+    const size_t base = ((size_t)b * p.H + h) * p.max_chunks;
+    float M = -INFINITY;
+    for (int c = 0; c < nch; ++c) M = fmaxf(M, p.part_ml[(base + c) * 2]);
+    float L = 0.f, O = 0.f;
+    for (int c = 0; c < nch; ++c) {
+        const float mc = p.part_ml[(base + c) * 2];
+        const float f = (mc == -INFINITY) ? 0.f : exp2f(mc - M);
+        L += p.part_ml[(base + c) * 2 + 1] * f;
+        O += p.part_o[(base + c) * AT_D + d] * f;
+    }
+    const float v = (L > 0.f) ? O / L : 0.f;
+    if (p.out_dtype == WF_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[((size_t)b * p.H + h) * AT_D + d] = __float2bfloat16_rn(v);
+    else reinterpret_cast<float*>(p.out)[((size_t)b * p.H + h) * AT_D + d] = v;
+    pdl_launch_dependents();
+}
+
+// ---------------------------------------------------------------------------------------------
+// RoPE + KV append.  grid = (H + 2*Hkv, B), block = D/2 threads.
+// Rounding follows the reference's bf16 tensor ops (direct_inference_full.py:58-70):
+//   out1 = bf16( bf16(x1*cos) - bf16(x2*sin) ),  out2 = bf16( bf16(x1*sin) + bf16(x2*cos) )
+struct RopeParams {
+    const __nv_bfloat16* qkv;   // [B][(H+2Hkv)*D]
+    int B, H, Hkv, D;
+    __nv_bfloat16* pool;
+    int layers, layer, page_size, max_blocks;
+    const int32_t* positions;
+    const int32_t* block_table;
+    const __nv_bfloat16* cos_tab;   // [max_pos][D/2]
+    const __nv_bfloat16* sin_tab;
+    int max_pos;
+    __nv_bfloat16* q_out;       // [B][H][D]
+};
+
+__global__ void rope_kv_append_kernel(const RopeParams p) {
+    const int head = blockIdx.x, b = blockIdx.y, i = threadIdx.x;
+    const int half = p.D / 2;
+    pdl_wait_prior();
+    const int pos = p.positions[b];
+    const __nv_bfloat16* src = p.qkv + (size_t)b * (p.H + 2 * p.Hkv) * p.D + (size_t)head * p.D;
+    const float x1 = __bfloat162float(src[i]), x2 = __bfloat162float(src[i + half]);
+    __nv_bfloat16* dst;
+    if (head < p.H) {
+        dst = p.q_out + ((size_t)b * p.H + head) * p.D;
+    } else {
+        const int kv = (head < p.H + p.Hkv) ? 0 : 1;
+        const int kh = head - p.H - kv * p.Hkv;
+        const int page = p.block_table[(size_t)b * p.max_blocks + pos / p.page_size];
+        const int slot = pos % p.page_size;
+        dst = p.pool + ((((size_t)page * p.layers + p.layer) * 2 + kv) * p.Hkv + kh) * (size_t)p.page_size * p.D + (size_t)slot * p.D;
+        if (kv == 1) {   // V: plain copy
+            dst[i] = src[i];
+            dst[i + half] = src[i + half];
+            pdl_launch_dependents();
+            return;
+        }
+    }
+    const int pc = min(pos, p.max_pos - 1);
+    const float c = __bfloat162float(p.cos_tab[(size_t)pc * half + i]);
+    const float s = __bfloat162float(p.sin_tab[(size_t)pc * half + i]);
+    const float o1 = bf16_round(x1 * c) - bf16_round(x2 * s);
+    const float o2 = bf16_round(x1 * s) + bf16_round(x2 * c);
+    dst[i] = __float2bfloat16_rn(o1);
+    dst[i + half] = __float2bfloat16_rn(o2);
+    pdl_launch_dependents();
+}
+
+// ---------------------------------------------------------------------------------------------
+// KVCacheManager scatter / gather: one CTA per token, rows [Hkv*D] <-> (page, slot, layer)
+template <typename T, bool SCATTER>
+__global__ void kv_scatter_gather_kernel(T* pool, T* k, T* v, const int32_t* pages, const int32_t* slots, int layers, int layer,
+                                         int Hkv, int page_size, int D, int max_pages) {
+    const int tkn = blockIdx.x;
+    const int page = pages[tkn], slot = slots[tkn];
+    if (page < 0 || page >= max_pages || slot < 0 || slot >= page_size) return;
+    const int HD = Hkv * D;
+    for (int e = threadIdx.x; e < HD; e += blockDim.x) {
+        const int hh = e / D, d = e % D;
+        const size_t ok = ((((size_t)page * layers + layer) * 2 + 0) * Hkv + hh) * (size_t)page_size * D + (size_t)slot * D + d;
+        const size_t ov = ok + (size_t)Hkv * page_size * D;
+        if (SCATTER) { pool[ok] = k[(size_t)tkn * HD + e]; pool[ov] = v[(size_t)tkn * HD + e]; }
+        else { k[(size_t)tkn * HD + e] = pool[ok]; v[(size_t)tkn * HD + e] = pool[ov]; }
+    }
+}
+
+static int elt_size(int dtype) { return dtype == WF_F32 ? 4 : 2; }
+
+int launch_rope_kv_append(const RopeParams& p, cudaStream_t s, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(p.H + 2 * p.Hkv, p.B);
+    cfg.blockDim = dim3(p.D / 2);
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return launch_check(cudaLaunchKernelEx(&cfg, rope_kv_append_kernel, p), "rope_kv_append");
+}
+
+// picks the chunking, launches attention (+ merge when sequences span several chunks)
+int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, size_t workspace_bytes, cudaStream_t s, bool pdl) {
+    static bool attr = false;
+    if (!attr) {
+        if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM), "attn smem")) return WF_ERR_CUDA;
+        attr = true;
+    }
+    const int max_blocks16 = (max_seq_hint + AT_BLK - 1) / AT_BLK;
+    // chunk size: aim for >= 4 CTAs per SM-slot (2 per SM) over the whole grid, but never below 4 blocks (64 tokens)
+    const long long pairs = (long long)p.B * p.Hkv;
+    const long long want = 8LL * 2 * sm_count();
+    int chunks = (int)((want + pairs - 1) / pairs);
+    if (chunks < 1) chunks = 1;
+    int chunk_blocks = (max_blocks16 + chunks - 1) / chunks;
+    if (chunk_blocks < 4) chunk_blocks = 4;
+    chunk_blocks = (chunk_blocks + 3) & ~3;
+    const int nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+    p.chunk_blocks = chunk_blocks;
+    p.max_chunks = nchunks;
+    p.direct = (nchunks <= 1);
+    if (!p.direct) {
+        const size_t need = (size_t)p.B * p.H * nchunks * (AT_D + 2) * sizeof(float);
+        if (!workspace || workspace_bytes < need) { set_error("paged_decode_attn: workspace too small (%zu < %zu)", workspace_bytes, need); return WF_ERR_INVALID; }
+        p.part_o = (float*)workspace;
+        p.part_ml = p.part_o + (size_t)p.B * p.H * nchunks * AT_D;
+    }
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(nchunks < 1 ? 1 : nchunks, p.Hkv, p.B);
+        cfg.blockDim = dim3(AT_WARPS * 32);
+        cfg.dynamicSmemBytes = AT_SMEM;
+        cfg.stream = s;
+        cfg.attrs = at;
+        cfg.numAttrs = pdl ? 1 : 0;
+        if (launch_check(cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel, p), "paged_decode_attn")) return WF_ERR_CUDA;
+    }
+    if (!p.direct) {
+        MergeParams mp;
+        mp.part_o = p.part_o; mp.part_ml = p.part_ml; mp.seq_lens = p.seq_lens;
+        mp.H = p.H; mp.max_chunks = nchunks; mp.chunk_tokens = chunk_blocks * AT_BLK;
+        mp.out = p.out; mp.out_dtype = p.out_dtype;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(p.H, p.B);
+        cfg.blockDim = dim3(AT_D);
+        cfg.stream = s;
+        cfg.attrs = at;
+        cfg.numAttrs = pdl ? 1 : 0;
+        if (launch_check(cudaLaunchKernelEx(&cfg, attn_merge_kernel, mp), "attn_merge")) return WF_ERR_CUDA;
+    }
+    return WF_OK;
+}
+
+
+int rope_append(const void* qkv, int B, int H, int Hkv, int D, void* pool, int layers, int layer, int page_size,
+                const int32_t* positions, const int32_t* block_table, int max_blocks, const void* cos_tab, const void* sin_tab,
+                int max_pos, void* q_out, cudaStream_t s, bool pdl) {
+    RopeParams p;
+    p.qkv = (const __nv_bfloat16*)qkv; p.B = B; p.H = H; p.Hkv = Hkv; p.D = D;
+    p.pool = (__nv_bfloat16*)pool; p.layers = layers; p.layer = layer; p.page_size = page_size; p.max_blocks = max_blocks;
+    p.positions = positions; p.block_table = block_table;
+    p.cos_tab = (const __nv_bfloat16*)cos_tab; p.sin_tab = (const __nv_bfloat16*)sin_tab; p.max_pos = max_pos;
+    p.q_out = (__nv_bfloat16*)q_out;
+    return launch_rope_kv_append(p, s, pdl);
+}
+
+int attn_decode(const void* q, const void* pool, int layers, int layer, int Hkv, int page_size, const int32_t* block_table,
+                int max_blocks, const int32_t* seq_lens, int B, int H, float scale, void* out, int out_dtype, int max_seq_hint,
+                void* ws, size_t ws_bytes, cudaStream_t s, bool pdl) {
+    AttnParams p = {};
+    p.q = (const __nv_bfloat16*)q; p.pool = (const __nv_bfloat16*)pool;
+    p.block_table = block_table; p.seq_lens = seq_lens;
+    p.B = B; p.H = H; p.Hkv = Hkv; p.G = H / Hkv;
+    p.layers = layers; p.layer = layer; p.page_size = page_size; p.max_blocks = max_blocks;
+    p.scale_log2e = scale * 1.4426950408889634f;
+    p.out = out; p.out_dtype = out_dtype;
+    return launch_paged_decode_attn(p, max_seq_hint, ws, ws_bytes, s, pdl);
+}
+
+}  // namespace wf
+
+using namespace wf;
+
+extern "C" size_t wf_kv_pool_bytes(int max_pages, int layers, int kv_heads, int page_size, int head_dim, int dtype) {
+    return (size_t)max_pages * layers * 2 * kv_heads * page_size * head_dim * elt_size(dtype);
+}
+
+static int check_kv(const wf_kv_layout* kv, const char* who) {
+    if (!kv || !kv->pool) { set_error("%s: null kv layout/pool", who); return WF_ERR_INVALID; }
+    if (kv->max_pages <= 0 || kv->layers <= 0 || kv->kv_heads <= 0 || kv->page_size <= 0 || kv->head_dim <= 0) { set_error("%s: bad kv layout", who); return WF_ERR_INVALID; }
+    return WF_OK;
+}
+
+template <bool SC>
+static int scatter_gather(const wf_kv_layout* kv, void* k, void* v, const int32_t* pages, const int32_t* slots, int T, int layer, void* stream) {
+    int rc = check_kv(kv, SC ? "wf_kv_scatter" : "wf_kv_gather");
+    if (rc) return rc;
+    if (!k || !v || !pages || !slots) { set_error("kv scatter/gather: null pointer"); return WF_ERR_INVALID; }
+    if (layer < 0 || layer >= kv->layers) { set_error("kv scatter/gather: layer %d out of range", layer); return WF_ERR_INVALID; }
+    if (T <= 0) return WF_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (kv->dtype == WF_F32)
+        kv_scatter_gather_kernel<float, SC><<<T, 256, 0, s>>>((float*)kv->pool, (float*)k, (float*)v, pages, slots, kv->layers, layer, kv->kv_heads, kv->page_size, kv->head_dim, kv->max_pages);
+    else if (kv->dtype == WF_BF16)
+        kv_scatter_gather_kernel<__nv_bfloat16, SC><<<T, 256, 0, s>>>((__nv_bfloat16*)kv->pool, (__nv_bfloat16*)k, (__nv_bfloat16*)v, pages, slots, kv->layers, layer, kv->kv_heads, kv->page_size, kv->head_dim, kv->max_pages);
+    else { set_error("kv scatter/gather: dtype must be f32 or bf16"); return WF_ERR_INVALID; }
+    return launch_check(cudaGetLastError(), "kv scatter/gather");
+}
+
+extern "C" int wf_kv_scatter(const wf_kv_layout* kv, const void* k, const void* v, const int32_t* pages, const int32_t* slots, int T, int layer, void* stream) {
+    return scatter_gather<true>(kv, (void*)k, (void*)v, pages, slots, T, layer, stream);
+}
+extern "C" int wf_kv_gather(const wf_kv_layout* kv, void* k_out, void* v_out, const int32_t* pages, const int32_t* slots, int T, int layer, void* stream) {
+    return scatter_gather<false>(kv, k_out, v_out, pages, slots, T, layer, stream);
+}
+
+extern "C" int wf_rope_kv_append(const void* qkv, int B, int H, const wf_kv_layout* kv, int layer, const int32_t* positions,
+                                 const int32_t* block_table, int max_blocks, const void* cos_tab, const void* sin_tab, int max_pos,
+                                 void* q_out, void* stream) {
+    int rc = check_kv(kv, "wf_rope_kv_append");
+    if (rc) return rc;
+    if (!qkv || !positions || !block_table || !cos_tab || !sin_tab || !q_out) { set_error("wf_rope_kv_append: null pointer"); return WF_ERR_INVALID; }
+    if (kv->dtype != WF_BF16) { set_error("wf_rope_kv_append: pool must be bf16"); return WF_ERR_UNSUPPORTED; }
+    if (kv->head_dim % 2 || kv->head_dim > 2048) { set_error("wf_rope_kv_append: bad head_dim"); return WF_ERR_UNSUPPORTED; }
+    if (B <= 0) return WF_OK;
+    return rope_append(qkv, B, H, kv->kv_heads, kv->head_dim, kv->pool, kv->layers, layer, kv->page_size, positions, block_table,
+                       max_blocks, cos_tab, sin_tab, max_pos, q_out, (cudaStream_t)stream, false);
+}
+
+extern "C" size_t wf_attn_workspace_bytes(int B, int H, int head_dim, int max_seq) {
+    const size_t chunks = (size_t)(max_seq + 63) / 64 + 1;
+    return (size_t)B * H * chunks * (head_dim + 2) * sizeof(float);
+}
+
+extern "C" int wf_paged_decode_attn(const void* q, const wf_kv_layout* kv, int layer, const int32_t* block_table, int max_blocks,
+                                    const int32_t* seq_lens, int B, int H, float scale, void* out, int out_dtype, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+    int rc = check_kv(kv, "wf_paged_decode_attn");
+    if (rc) return rc;
+    if (!q || !block_table || !seq_lens || !out) { set_error("wf_paged_decode_attn: null pointer"); return WF_ERR_INVALID; }
+    if (kv->dtype != WF_BF16) { set_error("wf_paged_decode_attn: pool must be bf16"); return WF_ERR_UNSUPPORTED; }
+    if (kv->head_dim != AT_D) { set_error("wf_paged_decode_attn: head_dim must be 128 (got %d)", kv->head_dim); return WF_ERR_UNSUPPORTED; }
+    if (kv->page_size % AT_BLK) { set_error("wf_paged_decode_attn: page_size must be a multiple of 16 (got %d)", kv->page_size); return WF_ERR_UNSUPPORTED; }
+    if (H % kv->kv_heads || H / kv->kv_heads > 8) { set_error("wf_paged_decode_attn: H/Hkv must be an integer <= 8"); return WF_ERR_UNSUPPORTED; }
+    if (layer < 0 || layer >= kv->layers) { set_error("wf_paged_decode_attn: layer out of range"); return WF_ERR_INVALID; }
+    if (out_dtype != WF_BF16 && out_dtype != WF_F32) { set_error("wf_paged_decode_attn: out dtype"); return WF_ERR_INVALID; }
+    if (B <= 0) return WF_OK;
+    return attn_decode(q, kv->pool, kv->layers, layer, kv->kv_heads, kv->page_size, block_table, max_blocks, seq_lens, B, H, scale, out,
+                       out_dtype, max_blocks * kv->page_size, workspace, workspace_bytes, (cudaStream_t)stream, false);
+}
+
+namespace wf {
+void attn_init_attrs() { cudaFuncSetAttribute(paged_decode_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM); }
+}

@@ -1,0 +1,604 @@
+// Decode engine: the whole per-token step of the reference's DirectBitNetInference.forward
+// (scripts/direct_inference_full.py:267-302) as one CUDA-graph-captured sequence of our kernels, with
+// resident tile-layout weights, a paged KV pool and a free-list page allocator
+// (KVCacheManager semantics, tests/test_kv_cache_cpp.py:44-70).  Batched: every sequence is an
+// independent copy of the reference's bs=1 loop (per-token activation scales).
+//
+// Per layer (11 launches):  rmsnorm+quant -> qkv linear -> rope+kv append -> paged attention (+merge)
+//   -> sub-norm+quant -> o linear (+residual) -> rmsnorm+quant -> gate|up linear (relu^2*up)
+//   -> sub-norm+quant -> down linear (+residual).
+#include "kernels.cuh"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+using namespace wf;
+
+namespace {
+
+struct LayerW {
+    uint8_t *qkv = nullptr, *o = nullptr, *gu = nullptr, *down = nullptr;   // b200_tile_v1
+    float* scales = nullptr;      // device [7]: q,k,v,o,gate,up,down
+    float h_scales[7] = {1, 1, 1, 1, 1, 1, 1};
+    __nv_bfloat16 *g_in = nullptr, *g_post = nullptr, *g_attn = nullptr, *g_ffn = nullptr;
+    uint8_t* stage[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // I2_S staging until finalize
+};
+
+const char* kLinNames[7] = {"q", "k", "v", "o", "gate", "up", "down"};
+
+}  // namespace
+
+struct wf_engine {
+    wf_model_config cfg;
+    cudaStream_t stream = nullptr;
+    std::vector<LayerW> layers;
+    __nv_bfloat16 *embed = nullptr, *final_norm = nullptr, *cos_tab = nullptr, *sin_tab = nullptr;
+    // local (per TP rank) dims
+    int H, Hkv, D, hidden, ffn, qkv_rows, attn_dim;
+    // kv
+    __nv_bfloat16* pool = nullptr;
+    int max_blocks = 0;
+    int32_t* d_block_table = nullptr;
+    std::vector<int32_t> h_block_table;
+    std::vector<int32_t> free_pages;
+    std::vector<int32_t> h_pos;
+    bool table_dirty = true;
+    int32_t *d_pos = nullptr, *d_len = nullptr, *d_tok = nullptr, *d_next = nullptr;
+    int32_t *h_tok_pinned = nullptr, *h_next_pinned = nullptr, *h_pos_pinned = nullptr;
+    // activations
+    __nv_bfloat16 *hid = nullptr, *qkv = nullptr, *qrot = nullptr, *attn = nullptr, *gu = nullptr, *normed = nullptr;
+    int8_t* q8 = nullptr;
+    float* a_scale = nullptr;
+    int32_t* rowsum = nullptr;
+    float* logits = nullptr;
+    void *ws_lin = nullptr, *ws_attn = nullptr, *ws_lm = nullptr;
+    size_t ws_lin_bytes = 0, ws_attn_bytes = 0, ws_lm_bytes = 0;
+    size_t dev_bytes = 0;
+    bool finalized = false;
+    bool pdl = false;
+    int linear_algo = 0;
+    int launches = 0;
+    int attn_seq_hint = 0;   // max sequence length the chunking is sized for (fixed per captured graph)
+    cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};   // [feed_back]
+    int graph_B[2] = {0, 0};
+    int graph_hint[2] = {0, 0};
+    std::vector<void*> allocs;
+};
+
+namespace {
+
+template <typename T>
+int dalloc(wf_engine* e, T** p, size_t count) {
+    void* q = nullptr;
+    size_t bytes = count * sizeof(T);
+    if (bytes == 0) bytes = 16;
+    if (cuda_check(cudaMalloc(&q, bytes), "cudaMalloc")) return WF_ERR_CUDA;
+    e->allocs.push_back(q);
+    e->dev_bytes += bytes;
+    *p = (T*)q;
+    return WF_OK;
+}
+
+int lin_index(const char* name) {
+    for (int i = 0; i < 7; ++i)
+        if (!strcmp(name, kLinNames[i])) return i;
+    return -1;
+}
+
+void lin_shape(const wf_engine* e, int idx, int* N, int* K) {
+    switch (idx) {
+        case 0: *N = e->H * e->D; *K = e->hidden; break;
+        case 1: case 2: *N = e->Hkv * e->D; *K = e->hidden; break;
+        case 3: *N = e->hidden; *K = e->attn_dim; break;
+        case 4: case 5: *N = e->ffn; *K = e->hidden; break;
+        default: *N = e->hidden; *K = e->ffn; break;
+    }
+}
+
+void invalidate_graphs(wf_engine* e) {
+    for (int i = 0; i < 2; ++i)
+        if (e->graph_exec[i]) { cudaGraphExecDestroy(e->graph_exec[i]); e->graph_exec[i] = nullptr; }
+}
+
+int linear(wf_engine* e, const uint8_t* w, int N, int K, int B, const float* w_scale, int nseg, const int* seg_end, int flags,
+           void* out, int ldo, const void* residual) {
+    wf_linear_args a;
+    memset(&a, 0, sizeof a);
+    a.w = w; a.w_layout = WF_W_TILE; a.N = N; a.K = K;
+    a.q = e->q8; a.M = B; a.ldq = K;
+    a.rowsum = e->rowsum; a.act_scale = e->a_scale; a.act_scale_per_token = 1;
+    a.w_scale = w_scale; a.nseg = nseg;
+    for (int i = 0; i < nseg && i < 4; ++i) a.seg_end[i] = seg_end[i];
+    a.out_mode = WF_OUT_LINEAR; a.epi_flags = flags; a.out_dtype = WF_BF16;
+    a.out = out; a.ldo = ldo; a.residual = residual;
+    a.workspace = e->ws_lin; a.workspace_bytes = e->ws_lin_bytes;
+    EpiParams ep;
+    int rc = fill_epi(&a, &ep);
+    if (rc) return rc;
+    int algo = e->linear_algo;
+    if (algo == 0) algo = (B <= 8) ? 1 : 2;
+    if (algo == 1 && B <= 8) return launch_gemv_stream(&a, ep, e->stream, e->pdl);
+    if (algo == 3) return launch_gemm_tc(&a, ep, e->stream);
+    return launch_gemm_mma(&a, ep, e->stream);
+}
+
+// the kernel sequence of one decode step (captured into a graph by the callers)
+int run_step(wf_engine* e, int B, int feed_back) {
+    const wf_model_config& c = e->cfg;
+    cudaStream_t s = e->stream;
+    const long long launches0 = launch_count();
+    int rc;
+    if ((rc = launch_embed(e->embed, e->d_tok, B, e->hidden, e->hid, s))) return rc;
+    const float attn_scale = 1.0f / sqrtf((float)e->D);
+    for (int l = 0; l < c.layers; ++l) {
+        LayerW& L = e->layers[l];
+        if ((rc = launch_rmsnorm_quant(e->hid, L.g_in, c.eps, B, e->hidden, nullptr, e->q8, e->a_scale, e->rowsum, s, e->pdl))) return rc;
+            {
+            const int seg[3] = {e->H * e->D, (e->H + e->Hkv) * e->D, e->qkv_rows};
+            if ((rc = linear(e, L.qkv, e->qkv_rows, e->hidden, B, L.scales + 0, 3, seg, 0, e->qkv, e->qkv_rows, nullptr))) return rc;
+        }
+        if ((rc = rope_append(e->qkv, B, e->H, e->Hkv, e->D, e->pool, c.layers, l, c.page_size, e->d_pos, e->d_block_table, e->max_blocks,
+                              e->cos_tab, e->sin_tab, c.max_seq, e->qrot, s, e->pdl))) return rc;
+            if ((rc = attn_decode(e->qrot, e->pool, c.layers, l, e->Hkv, c.page_size, e->d_block_table, e->max_blocks, e->d_len, B, e->H,
+                              attn_scale, e->attn, WF_BF16, e->attn_seq_hint, e->ws_attn, e->ws_attn_bytes, s, e->pdl))) return rc;
+            if ((rc = launch_rmsnorm_quant(e->attn, L.g_attn, c.eps, B, e->attn_dim, nullptr, e->q8, e->a_scale, e->rowsum, s, e->pdl))) return rc;
+            {
+            const int seg[1] = {e->hidden};
+            if ((rc = linear(e, L.o, e->hidden, e->attn_dim, B, L.scales + 3, 1, seg, WF_EPI_RESIDUAL, e->hid, e->hidden, e->hid))) return rc;
+        }
+        if ((rc = launch_rmsnorm_quant(e->hid, L.g_post, c.eps, B, e->hidden, nullptr, e->q8, e->a_scale, e->rowsum, s, e->pdl))) return rc;
+            {
+            const int seg[2] = {e->ffn, 2 * e->ffn};   // unused by RELU2_MUL (scales picked per 16-row block)
+            if ((rc = linear(e, L.gu, 2 * e->ffn, e->hidden, B, L.scales + 4, 2, seg, WF_EPI_RELU2_MUL, e->gu, e->ffn, nullptr))) return rc;
+        }
+        if ((rc = launch_rmsnorm_quant(e->gu, L.g_ffn, c.eps, B, e->ffn, nullptr, e->q8, e->a_scale, e->rowsum, s, e->pdl))) return rc;
+            {
+            const int seg[1] = {e->hidden};
+            if ((rc = linear(e, L.down, e->hidden, e->ffn, B, L.scales + 6, 1, seg, WF_EPI_RESIDUAL, e->hid, e->hidden, e->hid))) return rc;
+        }
+    }
+    // final norm (quant outputs unused) + tied LM head + greedy argmax
+    if ((rc = launch_rmsnorm_quant(e->hid, e->final_norm, c.eps, B, e->hidden, e->normed, e->q8, e->a_scale, e->rowsum, s, false))) return rc;
+    if ((rc = launch_lm_head_argmax(e->normed, e->embed, B, c.vocab, e->hidden, e->logits, e->d_next, e->ws_lm, s))) return rc;
+    if ((rc = launch_advance(e->d_pos, e->d_len, e->d_tok, e->d_next, B, feed_back, s))) return rc;
+    e->launches = (int)(launch_count() - launches0);
+    return WF_OK;
+}
+
+// host-side bookkeeping before a step: make sure every active sequence has a page for its next token
+int prepare_pages(wf_engine* e, int B) {
+    const int ps = e->cfg.page_size;
+    for (int b = 0; b < B; ++b) {
+        const int pos = e->h_pos[b];
+        if (pos >= e->cfg.max_seq) { set_error("sequence %d reached max_seq %d", b, e->cfg.max_seq); return WF_ERR_INVALID; }
+        const int blk = pos / ps;
+        if (e->h_block_table[(size_t)b * e->max_blocks + blk] < 0) {
+            if (e->free_pages.empty()) { set_error("KV pool exhausted (%d pages)", e->cfg.max_pages); return WF_ERR_INVALID; }
+            e->h_block_table[(size_t)b * e->max_blocks + blk] = e->free_pages.back();
+            e->free_pages.pop_back();
+            e->table_dirty = true;
+        }
+    }
+    if (e->table_dirty) {
+        // unused entries point at page 0 so that a stale lookup can never leave the pool
+        std::vector<int32_t> tmp(e->h_block_table);
+        for (auto& v : tmp) if (v < 0) v = 0;
+        if (cuda_check(cudaMemcpyAsync(e->d_block_table, tmp.data(), tmp.size() * 4, cudaMemcpyHostToDevice, e->stream), "block table H2D")) return WF_ERR_CUDA;
+        if (cuda_check(cudaStreamSynchronize(e->stream), "sync")) return WF_ERR_CUDA;   // tmp is pageable
+        e->table_dirty = false;
+    }
+    return WF_OK;
+}
+
+int seq_hint_for(const wf_engine* e, int B) {
+    int mx = 0;
+    for (int b = 0; b < B; ++b) mx = e->h_pos[b] + 1 > mx ? e->h_pos[b] + 1 : mx;
+    // round up to a power of two >= 256 so that captured graphs survive many steps
+    int h = 256;
+    while (h < mx) h <<= 1;
+    if (h > e->cfg.max_seq) h = e->cfg.max_seq;
+    return h;
+}
+
+int step_graph(wf_engine* e, int B, int feed_back, int use_graph) {
+    const int hint = seq_hint_for(e, B);
+    if (!use_graph) {
+        e->attn_seq_hint = hint;
+        return run_step(e, B, feed_back);
+    }
+    const int gi = feed_back ? 1 : 0;
+    if (!e->graph_exec[gi] || e->graph_B[gi] != B || e->graph_hint[gi] != hint) {
+        if (e->graph_exec[gi]) { cudaGraphExecDestroy(e->graph_exec[gi]); e->graph_exec[gi] = nullptr; }
+        e->attn_seq_hint = hint;
+        // one eager run first: sets function attributes (not allowed during capture) — on scratch state
+        // this would advance positions, so capture directly but pre-set attributes through a dry launch
+        // with B rows on the real buffers is unsafe; instead we rely on launchers being attribute-idempotent
+        // and run them once outside capture in wf_engine_finalize_weights (warm-up step on slot state 0).
+        cudaGraph_t graph = nullptr;
+        if (cuda_check(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal), "begin capture")) return WF_ERR_CUDA;
+        int rc = run_step(e, B, feed_back);
+        cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
+        if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+        if (cuda_check(ce, "end capture")) return WF_ERR_CUDA;
+        ce = cudaGraphInstantiate(&e->graph_exec[gi], graph, 0);
+        cudaGraphDestroy(graph);
+        if (cuda_check(ce, "graph instantiate")) return WF_ERR_CUDA;
+        e->graph_B[gi] = B;
+        e->graph_hint[gi] = hint;
+    }
+    return cuda_check(cudaGraphLaunch(e->graph_exec[gi], e->stream), "graph launch");
+}
+
+}  // namespace
+
+extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
+    if (!cfg || !out) { set_error("wf_engine_create: null argument"); return WF_ERR_INVALID; }
+    const wf_model_config& c = *cfg;
+    if (c.head_dim != 128) { set_error("engine: head_dim must be 128"); return WF_ERR_UNSUPPORTED; }
+    if (c.tp_size != 1 && c.tp_size != 0) { set_error("engine: tensor parallel engine is driven from the host layer (tp.py); tp_size must be 1 here"); return WF_ERR_UNSUPPORTED; }
+    if (c.heads % c.kv_heads || c.heads / c.kv_heads > 8) { set_error("engine: heads/kv_heads must be an integer <= 8"); return WF_ERR_UNSUPPORTED; }
+    if (c.hidden % 128 || c.ffn % 128 || (c.heads * c.head_dim) % 128) { set_error("engine: hidden, ffn, heads*head_dim must be multiples of 128"); return WF_ERR_UNSUPPORTED; }
+    if (c.ffn % 16 || c.page_size % 16 || c.page_size <= 0) { set_error("engine: page_size must be a positive multiple of 16"); return WF_ERR_UNSUPPORTED; }
+    if (c.max_batch < 1 || c.max_batch > 64) { set_error("engine: max_batch must be 1..64"); return WF_ERR_UNSUPPORTED; }
+    if (c.max_seq % c.page_size) { set_error("engine: max_seq must be a multiple of page_size"); return WF_ERR_INVALID; }
+    wf_engine* e = new wf_engine();
+    e->cfg = c;
+    e->cfg.tp_size = 1; e->cfg.tp_rank = 0;
+    e->H = c.heads; e->Hkv = c.kv_heads; e->D = c.head_dim; e->hidden = c.hidden; e->ffn = c.ffn;
+    e->qkv_rows = (e->H + 2 * e->Hkv) * e->D;
+    e->attn_dim = e->H * e->D;
+    const char* env_pdl = getenv("WF_PDL");
+    e->pdl = env_pdl && atoi(env_pdl) != 0;
+    const char* env_algo = getenv("WF_LINEAR_ALGO");
+    e->linear_algo = env_algo ? atoi(env_algo) : 0;
+    int rc = WF_OK;
+    auto fail = [&](int r) { wf_engine_destroy(e); return r; };
+    if (cuda_check(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking), "stream create")) return fail(WF_ERR_CUDA);
+    init_all_kernel_attrs();
+    cudaGetLastError();
+    const int B = c.max_batch;
+    e->layers.resize(c.layers);
+    for (int l = 0; l < c.layers; ++l) {
+        LayerW& L = e->layers[l];
+        if ((rc = dalloc(e, &L.qkv, wf_tile_bytes(e->qkv_rows, e->hidden)))) return fail(rc);
+        if ((rc = dalloc(e, &L.o, wf_tile_bytes(e->hidden, e->attn_dim)))) return fail(rc);
+        if ((rc = dalloc(e, &L.gu, wf_tile_bytes(2 * e->ffn, e->hidden)))) return fail(rc);
+        if ((rc = dalloc(e, &L.down, wf_tile_bytes(e->hidden, e->ffn)))) return fail(rc);
+        if ((rc = dalloc(e, &L.scales, 8))) return fail(rc);
+        if ((rc = dalloc(e, &L.g_in, e->hidden))) return fail(rc);
+        if ((rc = dalloc(e, &L.g_post, e->hidden))) return fail(rc);
+        if ((rc = dalloc(e, &L.g_attn, e->attn_dim))) return fail(rc);
+        if ((rc = dalloc(e, &L.g_ffn, e->ffn))) return fail(rc);
+    }
+    if ((rc = dalloc(e, &e->embed, (size_t)c.vocab * c.hidden))) return fail(rc);
+    if ((rc = dalloc(e, &e->final_norm, c.hidden))) return fail(rc);
+    if ((rc = dalloc(e, &e->cos_tab, (size_t)c.max_seq * (c.head_dim / 2)))) return fail(rc);
+    if ((rc = dalloc(e, &e->sin_tab, (size_t)c.max_seq * (c.head_dim / 2)))) return fail(rc);
+    // rope tables, same construction as RotaryEmbedding.__init__ (direct_inference_full.py:31-45):
+    // fp32 inv_freq, fp32 outer product, cos/sin, round to bf16.  (The host layer may overwrite them with
+    // torch-computed tables through wf_engine_set_tensor("rope_cos"/"rope_sin") for bit-level parity.)
+    {
+        const int half = c.head_dim / 2;
+        std::vector<__nv_bfloat16> hc((size_t)c.max_seq * half), hs((size_t)c.max_seq * half);
+        for (int i = 0; i < half; ++i) {
+            const float inv = 1.0f / powf(c.rope_theta, (float)(2 * i) / (float)c.head_dim);
+            for (int p = 0; p < c.max_seq; ++p) {
+                const float f = (float)p * inv;
+                hc[(size_t)p * half + i] = __float2bfloat16_rn(cosf(f));
+                hs[(size_t)p * half + i] = __float2bfloat16_rn(sinf(f));
+            }
+        }
+        if (cuda_check(cudaMemcpy(e->cos_tab, hc.data(), hc.size() * 2, cudaMemcpyHostToDevice), "rope cos")) return fail(WF_ERR_CUDA);
+        if (cuda_check(cudaMemcpy(e->sin_tab, hs.data(), hs.size() * 2, cudaMemcpyHostToDevice), "rope sin")) return fail(WF_ERR_CUDA);
+    }
+    // KV pool
+    const size_t pool_elems = (size_t)c.max_pages * c.layers * 2 * e->Hkv * c.page_size * c.head_dim;
+    if ((rc = dalloc(e, &e->pool, pool_elems))) return fail(rc);
+    if (cuda_check(cudaMemset(e->pool, 0, pool_elems * 2), "pool memset")) return fail(WF_ERR_CUDA);
+    e->max_blocks = c.max_seq / c.page_size;
+    if ((rc = dalloc(e, &e->d_block_table, (size_t)B * e->max_blocks))) return fail(rc);
+    if ((rc = dalloc(e, &e->d_pos, B)) || (rc = dalloc(e, &e->d_len, B)) || (rc = dalloc(e, &e->d_tok, B)) || (rc = dalloc(e, &e->d_next, B))) return fail(rc);
+    if (cuda_check(cudaMallocHost(&e->h_tok_pinned, B * 4), "pinned") || cuda_check(cudaMallocHost(&e->h_next_pinned, B * 4), "pinned") ||
+        cuda_check(cudaMallocHost(&e->h_pos_pinned, 2 * B * 4), "pinned")) return fail(WF_ERR_CUDA);
+    // activations
+    const int maxK = e->ffn > e->hidden ? (e->ffn > e->attn_dim ? e->ffn : e->attn_dim) : (e->hidden > e->attn_dim ? e->hidden : e->attn_dim);
+    if ((rc = dalloc(e, &e->hid, (size_t)B * e->hidden)) || (rc = dalloc(e, &e->normed, (size_t)B * e->hidden)) ||
+        (rc = dalloc(e, &e->qkv, (size_t)B * e->qkv_rows)) || (rc = dalloc(e, &e->qrot, (size_t)B * e->attn_dim)) ||
+        (rc = dalloc(e, &e->attn, (size_t)B * e->attn_dim)) || (rc = dalloc(e, &e->gu, (size_t)B * e->ffn)) ||
+        (rc = dalloc(e, &e->q8, (size_t)B * maxK)) || (rc = dalloc(e, &e->a_scale, B)) || (rc = dalloc(e, &e->rowsum, B)) ||
+        (rc = dalloc(e, &e->logits, (size_t)B * c.vocab))) return fail(rc);
+    const int maxN = 2 * e->ffn > e->qkv_rows ? 2 * e->ffn : e->qkv_rows;
+    e->ws_lin_bytes = wf_linear_workspace_bytes(B, maxN, maxK) + (size_t)maxN * 4;
+    e->ws_attn_bytes = wf_attn_workspace_bytes(B, e->H, e->D, c.max_seq);
+    e->ws_lm_bytes = wf_lm_head_workspace_bytes(B, c.vocab);
+    {
+        char *a = nullptr, *b2 = nullptr, *c2 = nullptr;
+        if ((rc = dalloc(e, &a, e->ws_lin_bytes)) || (rc = dalloc(e, &b2, e->ws_attn_bytes)) || (rc = dalloc(e, &c2, e->ws_lm_bytes))) return fail(rc);
+        e->ws_lin = a; e->ws_attn = b2; e->ws_lm = c2;
+        if (cuda_check(cudaMemset(e->ws_lin, 0, e->ws_lin_bytes), "ws memset")) return fail(WF_ERR_CUDA);
+    }
+    e->h_block_table.assign((size_t)B * e->max_blocks, -1);
+    e->h_pos.assign(B, 0);
+    wf_engine_reset(e);
+    *out = e;
+    return WF_OK;
+}
+
+extern "C" void wf_engine_destroy(wf_engine* e) {
+    if (!e) return;
+    cudaDeviceSynchronize();
+    invalidate_graphs(e);
+    for (void* p : e->allocs) cudaFree(p);
+    for (auto& L : e->layers)
+        for (int i = 0; i < 7; ++i)
+            if (L.stage[i]) cudaFree(L.stage[i]);
+    if (e->h_tok_pinned) cudaFreeHost(e->h_tok_pinned);
+    if (e->h_next_pinned) cudaFreeHost(e->h_next_pinned);
+    if (e->h_pos_pinned) cudaFreeHost(e->h_pos_pinned);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+extern "C" size_t wf_engine_device_bytes(const wf_engine* e) { return e ? e->dev_bytes : 0; }
+extern "C" void* wf_engine_stream(wf_engine* e) { return e ? (void*)e->stream : nullptr; }
+extern "C" int wf_engine_launches_per_step(const wf_engine* e) { return e ? e->launches : 0; }
+extern "C" int wf_engine_sync(wf_engine* e) { return e ? cuda_check(cudaStreamSynchronize(e->stream), "engine sync") : WF_ERR_INVALID; }
+
+extern "C" int wf_engine_set_linear(wf_engine* e, int layer, const char* name, const uint8_t* i2s, float weight_scale, int is_host) {
+    if (!e || !name || !i2s) { set_error("wf_engine_set_linear: null argument"); return WF_ERR_INVALID; }
+    if (layer < 0 || layer >= e->cfg.layers) { set_error("wf_engine_set_linear: layer %d out of range", layer); return WF_ERR_INVALID; }
+    const int idx = lin_index(name);
+    if (idx < 0) { set_error("wf_engine_set_linear: unknown projection '%s'", name); return WF_ERR_INVALID; }
+    int N, K;
+    lin_shape(e, idx, &N, &K);
+    LayerW& L = e->layers[layer];
+    const size_t bytes = (size_t)N * K / 4;
+    if (!L.stage[idx] && cuda_check(cudaMalloc((void**)&L.stage[idx], bytes), "stage alloc")) return WF_ERR_CUDA;
+    if (cuda_check(cudaMemcpy(L.stage[idx], i2s, bytes, is_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice), "stage copy")) return WF_ERR_CUDA;
+    L.h_scales[idx] = weight_scale;
+    e->finalized = false;
+    return WF_OK;
+}
+
+extern "C" int wf_engine_set_tensor(wf_engine* e, int layer, const char* name, const void* data, size_t count, int is_host) {
+    if (!e || !name || !data) { set_error("wf_engine_set_tensor: null argument"); return WF_ERR_INVALID; }
+    __nv_bfloat16* dst = nullptr;
+    size_t expect = 0;
+    const std::string n(name);
+    if (layer < 0) {
+        if (n == "embed") { dst = e->embed; expect = (size_t)e->cfg.vocab * e->hidden; }
+        else if (n == "final_norm") { dst = e->final_norm; expect = e->hidden; }
+        else if (n == "rope_cos") { dst = e->cos_tab; expect = (size_t)e->cfg.max_seq * (e->D / 2); }
+        else if (n == "rope_sin") { dst = e->sin_tab; expect = (size_t)e->cfg.max_seq * (e->D / 2); }
+    } else if (layer < e->cfg.layers) {
+        LayerW& L = e->layers[layer];
+        if (n == "input_layernorm") { dst = L.g_in; expect = e->hidden; }
+        else if (n == "post_attention_layernorm") { dst = L.g_post; expect = e->hidden; }
+        else if (n == "attn_sub_norm") { dst = L.g_attn; expect = e->attn_dim; }
+        else if (n == "ffn_sub_norm") { dst = L.g_ffn; expect = e->ffn; }
+    }
+    if (!dst) { set_error("wf_engine_set_tensor: unknown tensor '%s' (layer %d)", name, layer); return WF_ERR_INVALID; }
+    if (count != expect) { set_error("wf_engine_set_tensor: '%s' expects %zu elements, got %zu", name, expect, count); return WF_ERR_INVALID; }
+    return cuda_check(cudaMemcpy(dst, data, count * 2, is_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice), "set_tensor copy");
+}
+
+extern "C" int wf_engine_finalize_weights(wf_engine* e) {
+    if (!e) return WF_ERR_INVALID;
+    cudaStream_t s = e->stream;
+    for (int l = 0; l < e->cfg.layers; ++l) {
+        LayerW& L = e->layers[l];
+        bool any = false, all = true;
+        for (int i = 0; i < 7; ++i) { any |= L.stage[i] != nullptr; all &= L.stage[i] != nullptr; }
+        if (!any) continue;   // synthetic or already finalized
+        if (!all) { set_error("layer %d: all seven projections must be set before finalize", l); return WF_ERR_INVALID; }
+        int rc;
+        const int K4 = e->hidden / 4;
+        // q|k|v: rows concatenated -> one I2_S matrix -> tiles
+        {
+            uint8_t* cat = nullptr;
+            const size_t bq = (size_t)e->H * e->D * K4, bk = (size_t)e->Hkv * e->D * K4;
+            if (cuda_check(cudaMalloc((void**)&cat, bq + 2 * bk), "cat alloc")) return WF_ERR_CUDA;
+            cudaMemcpyAsync(cat, L.stage[0], bq, cudaMemcpyDeviceToDevice, s);
+            cudaMemcpyAsync(cat + bq, L.stage[1], bk, cudaMemcpyDeviceToDevice, s);
+            cudaMemcpyAsync(cat + bq + bk, L.stage[2], bk, cudaMemcpyDeviceToDevice, s);
+            rc = wf_repack_i2s_to_tile(cat, e->qkv_rows, e->hidden, L.qkv, s);
+            cudaStreamSynchronize(s);
+            cudaFree(cat);
+            if (rc) return rc;
+        }
+        if ((rc = wf_repack_i2s_to_tile(L.stage[3], e->hidden, e->attn_dim, L.o, s))) return rc;
+        {
+            uint8_t* il = nullptr;
+            if (cuda_check(cudaMalloc((void**)&il, (size_t)2 * e->ffn * K4), "interleave alloc")) return WF_ERR_CUDA;
+            rc = wf_interleave_rows16(L.stage[4], L.stage[5], e->ffn, K4, il, s);
+            if (!rc) rc = wf_repack_i2s_to_tile(il, 2 * e->ffn, e->hidden, L.gu, s);
+            cudaStreamSynchronize(s);
+            cudaFree(il);
+            if (rc) return rc;
+        }
+        if ((rc = wf_repack_i2s_to_tile(L.stage[6], e->hidden, e->ffn, L.down, s))) return rc;
+        if (cuda_check(cudaMemcpyAsync(L.scales, L.h_scales, 7 * 4, cudaMemcpyHostToDevice, s), "scales")) return WF_ERR_CUDA;
+        cudaStreamSynchronize(s);
+        for (int i = 0; i < 7; ++i) { cudaFree(L.stage[i]); L.stage[i] = nullptr; }
+    }
+    e->finalized = true;
+    invalidate_graphs(e);
+    return cuda_check(cudaStreamSynchronize(s), "finalize");
+}
+
+extern "C" int wf_engine_init_synthetic(wf_engine* e, uint64_t seed) {
+    if (!e) return WF_ERR_INVALID;
+    cudaStream_t s = e->stream;
+    int rc;
+    for (int l = 0; l < e->cfg.layers; ++l) {
+        LayerW& L = e->layers[l];
+        const uint64_t sd = seed * 1000003ull + (uint64_t)l * 7919ull;
+        if ((rc = launch_fill_ternary(L.qkv, wf_tile_bytes(e->qkv_rows, e->hidden), sd + 1, s))) return rc;
+        if ((rc = launch_fill_ternary(L.o, wf_tile_bytes(e->hidden, e->attn_dim), sd + 2, s))) return rc;
+        if ((rc = launch_fill_ternary(L.gu, wf_tile_bytes(2 * e->ffn, e->hidden), sd + 3, s))) return rc;
+        if ((rc = launch_fill_ternary(L.down, wf_tile_bytes(e->hidden, e->ffn), sd + 4, s))) return rc;
+        // weight_scale ~ U(0.5, 2.5); deterministic LCG on the host
+        uint64_t st = sd ^ 0xD1B54A32D192ED03ull;
+        for (int i = 0; i < 7; ++i) {
+            st = st * 6364136223846793005ull + 1442695040888963407ull;
+            L.h_scales[i] = 0.5f + 2.0f * (float)((st >> 40) & 0xffff) / 65536.0f;
+        }
+        if (cuda_check(cudaMemcpyAsync(L.scales, L.h_scales, 7 * 4, cudaMemcpyHostToDevice, s), "scales")) return WF_ERR_CUDA;
+        cudaStreamSynchronize(s);
+        if ((rc = launch_fill_bf16(L.g_in, e->hidden, sd + 5, 1.0f, 0.1f, s))) return rc;
+        if ((rc = launch_fill_bf16(L.g_post, e->hidden, sd + 6, 1.0f, 0.1f, s))) return rc;
+        if ((rc = launch_fill_bf16(L.g_attn, e->attn_dim, sd + 7, 1.0f, 0.1f, s))) return rc;
+        if ((rc = launch_fill_bf16(L.g_ffn, e->ffn, sd + 8, 1.0f, 0.1f, s))) return rc;
+    }
+    if ((rc = launch_fill_bf16(e->embed, (size_t)e->cfg.vocab * e->hidden, seed + 11, 0.0f, 0.02f, s))) return rc;
+    if ((rc = launch_fill_bf16(e->final_norm, e->hidden, seed + 12, 1.0f, 0.1f, s))) return rc;
+    e->finalized = true;
+    invalidate_graphs(e);
+    return cuda_check(cudaStreamSynchronize(s), "init_synthetic");
+}
+
+extern "C" int wf_engine_reset(wf_engine* e) {
+    if (!e) return WF_ERR_INVALID;
+    const int B = e->cfg.max_batch;
+    e->free_pages.clear();
+    for (int p = e->cfg.max_pages - 1; p >= 0; --p) e->free_pages.push_back(p);   // pop_back hands out 0,1,2,... like the reference free list
+    std::fill(e->h_block_table.begin(), e->h_block_table.end(), -1);
+    std::fill(e->h_pos.begin(), e->h_pos.end(), 0);
+    e->table_dirty = true;
+    if (cuda_check(cudaMemsetAsync(e->d_pos, 0, B * 4, e->stream), "reset")) return WF_ERR_CUDA;
+    std::vector<int32_t> ones(B, 1);
+    if (cuda_check(cudaMemcpyAsync(e->d_len, ones.data(), B * 4, cudaMemcpyHostToDevice, e->stream), "reset")) return WF_ERR_CUDA;
+    return cuda_check(cudaStreamSynchronize(e->stream), "reset");
+}
+
+extern "C" int wf_engine_set_context(wf_engine* e, int slot, int len, int fill_random) {
+    if (!e || slot < 0 || slot >= e->cfg.max_batch || len < 0 || len >= e->cfg.max_seq) { set_error("wf_engine_set_context: bad slot/len"); return WF_ERR_INVALID; }
+    const int ps = e->cfg.page_size;
+    // release pages beyond the new length, allocate up to it
+    for (int blk = 0; blk < e->max_blocks; ++blk) {
+        int32_t& ent = e->h_block_table[(size_t)slot * e->max_blocks + blk];
+        const bool need = blk * ps < len;
+        if (need && ent < 0) {
+            if (e->free_pages.empty()) { set_error("KV pool exhausted"); return WF_ERR_INVALID; }
+            ent = e->free_pages.back();
+            e->free_pages.pop_back();
+        } else if (!need && ent >= 0) {
+            e->free_pages.push_back(ent);
+            ent = -1;
+        }
+    }
+    e->table_dirty = true;
+    e->h_pos[slot] = len;
+    const int32_t pl[2] = {len, len + 1};
+    if (cuda_check(cudaMemcpy(e->d_pos + slot, &pl[0], 4, cudaMemcpyHostToDevice), "ctx pos")) return WF_ERR_CUDA;
+    if (cuda_check(cudaMemcpy(e->d_len + slot, &pl[1], 4, cudaMemcpyHostToDevice), "ctx len")) return WF_ERR_CUDA;
+    if (fill_random) {
+        // a page is one contiguous run of layers*2*Hkv*page_size*D elements
+        const size_t page_elems = (size_t)e->cfg.layers * 2 * e->Hkv * ps * e->D;
+        for (int blk = 0; blk * ps < len; ++blk) {
+            const int32_t page = e->h_block_table[(size_t)slot * e->max_blocks + blk];
+            int rc = launch_fill_bf16(e->pool + (size_t)page * page_elems, page_elems, 0xC0FFEEull + (uint64_t)page, 0.0f, 1.0f, e->stream);
+            if (rc) return rc;
+        }
+        return cuda_check(cudaStreamSynchronize(e->stream), "fill pool");
+    }
+    return WF_OK;
+}
+
+extern "C" int wf_engine_decode_device(wf_engine* e, int B, int use_graph) {
+    if (!e || B < 1 || B > e->cfg.max_batch) { set_error("wf_engine_decode_device: bad batch %d", B); return WF_ERR_INVALID; }
+    if (!e->finalized) { set_error("engine weights not finalized"); return WF_ERR_INVALID; }
+    int rc = prepare_pages(e, B);
+    if (rc) return rc;
+    rc = step_graph(e, B, /*feed_back=*/1, use_graph);
+    if (rc) return rc;
+    for (int b = 0; b < B; ++b) e->h_pos[b] += 1;
+    return WF_OK;
+}
+
+extern "C" int wf_engine_decode(wf_engine* e, const int32_t* host_tokens, int B, int32_t* host_next_tokens) {
+    if (!e || !host_tokens || !host_next_tokens || B < 1 || B > e->cfg.max_batch) { set_error("wf_engine_decode: bad arguments"); return WF_ERR_INVALID; }
+    if (!e->finalized) { set_error("engine weights not finalized"); return WF_ERR_INVALID; }
+    int rc = prepare_pages(e, B);
+    if (rc) return rc;
+    memcpy(e->h_tok_pinned, host_tokens, (size_t)B * 4);
+    if (cuda_check(cudaMemcpyAsync(e->d_tok, e->h_tok_pinned, (size_t)B * 4, cudaMemcpyHostToDevice, e->stream), "tokens H2D")) return WF_ERR_CUDA;
+    rc = step_graph(e, B, /*feed_back=*/0, 1);
+    if (rc) return rc;
+    if (cuda_check(cudaMemcpyAsync(e->h_next_pinned, e->d_next, (size_t)B * 4, cudaMemcpyDeviceToHost, e->stream), "next D2H")) return WF_ERR_CUDA;
+    if (cuda_check(cudaStreamSynchronize(e->stream), "decode sync")) return WF_ERR_CUDA;
+    memcpy(host_next_tokens, e->h_next_pinned, (size_t)B * 4);
+    for (int b = 0; b < B; ++b) e->h_pos[b] += 1;
+    return WF_OK;
+}
+
+extern "C" void* wf_engine_buffer(wf_engine* e, const char* name) {
+    if (!e || !name) return nullptr;
+    const std::string n(name);
+    if (n == "hidden") return e->hid;
+    if (n == "normed") return e->normed;
+    if (n == "logits") return e->logits;
+    if (n == "qkv") return e->qkv;
+    if (n == "attn") return e->attn;
+    if (n == "tokens") return e->d_tok;
+    if (n == "next") return e->d_next;
+    if (n == "positions") return e->d_pos;
+    if (n == "seq_lens") return e->d_len;
+    if (n == "pool") return e->pool;
+    if (n == "block_table") return e->d_block_table;
+    if (n == "q8") return e->q8;
+    return nullptr;
+}
+
+// Times one component of the step in isolation on the engine's resident state (CUDA events on the
+// engine stream; `iters` launches cycling over the layers so the working set exceeds L2).
+extern "C" int wf_engine_time_kernel(wf_engine* e, const char* which, int B, int iters, float* ms_out) {
+    if (!e || !which || !ms_out || B < 1 || B > e->cfg.max_batch || iters < 1) { set_error("wf_engine_time_kernel: bad arguments"); return WF_ERR_INVALID; }
+    int rc = prepare_pages(e, B);
+    if (rc) return rc;
+    e->attn_seq_hint = seq_hint_for(e, B);
+    const std::string w(which);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const wf_model_config& c = e->cfg;
+    auto body = [&](int it) -> int {
+        const int l = it % c.layers;
+        LayerW& L = e->layers[l];
+        if (w == "attn")
+            return attn_decode(e->qrot, e->pool, c.layers, l, e->Hkv, c.page_size, e->d_block_table, e->max_blocks, e->d_len, B, e->H,
+                               1.0f / sqrtf((float)e->D), e->attn, WF_BF16, e->attn_seq_hint, e->ws_attn, e->ws_attn_bytes, e->stream, false);
+        if (w == "qkv") { const int seg[3] = {e->H * e->D, (e->H + e->Hkv) * e->D, e->qkv_rows}; return linear(e, L.qkv, e->qkv_rows, e->hidden, B, L.scales, 3, seg, 0, e->qkv, e->qkv_rows, nullptr); }
+        if (w == "o") { const int seg[1] = {e->hidden}; return linear(e, L.o, e->hidden, e->attn_dim, B, L.scales + 3, 1, seg, 0, e->normed, e->hidden, nullptr); }
+        if (w == "gateup") { const int seg[2] = {e->ffn, 2 * e->ffn}; return linear(e, L.gu, 2 * e->ffn, e->hidden, B, L.scales + 4, 2, seg, WF_EPI_RELU2_MUL, e->gu, e->ffn, nullptr); }
+        if (w == "down") { const int seg[1] = {e->hidden}; return linear(e, L.down, e->hidden, e->ffn, B, L.scales + 6, 1, seg, 0, e->normed, e->hidden, nullptr); }
+        if (w == "linears") {
+            int r;
+            const int s3[3] = {e->H * e->D, (e->H + e->Hkv) * e->D, e->qkv_rows};
+            const int s1[1] = {e->hidden};
+            const int s2[2] = {e->ffn, 2 * e->ffn};
+            if ((r = linear(e, L.qkv, e->qkv_rows, e->hidden, B, L.scales, 3, s3, 0, e->qkv, e->qkv_rows, nullptr))) return r;
+            if ((r = linear(e, L.o, e->hidden, e->attn_dim, B, L.scales + 3, 1, s1, 0, e->normed, e->hidden, nullptr))) return r;
+            if ((r = linear(e, L.gu, 2 * e->ffn, e->hidden, B, L.scales + 4, 2, s2, WF_EPI_RELU2_MUL, e->gu, e->ffn, nullptr))) return r;
+            return linear(e, L.down, e->hidden, e->ffn, B, L.scales + 6, 1, s1, 0, e->normed, e->hidden, nullptr);
+        }
+        if (w == "lm_head") return launch_lm_head_argmax(e->normed, e->embed, B, c.vocab, e->hidden, nullptr, e->d_next, e->ws_lm, e->stream);
+        if (w == "norm") return launch_rmsnorm_quant(e->hid, L.g_in, c.eps, B, e->hidden, nullptr, e->q8, e->a_scale, e->rowsum, e->stream, false);
+        set_error("wf_engine_time_kernel: unknown component '%s'", which);
+        return WF_ERR_INVALID;
+    };
+    for (int it = 0; it < 3; ++it) if ((rc = body(it))) return rc;
+    cudaStreamSynchronize(e->stream);
+    cudaEventRecord(e0, e->stream);
+    for (int it = 0; it < iters; ++it) if ((rc = body(it))) return rc;
+    cudaEventRecord(e1, e->stream);
+    if (cuda_check(cudaEventSynchronize(e1), "time_kernel sync")) return WF_ERR_CUDA;
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *ms_out = ms / iters;
+    return WF_OK;
+}

@@ -1,0 +1,313 @@
+// Glue kernels around the ternary linears: embedding gather, tied bf16 LM head with
+// greedy argmax, step bookkeeping, and on-device synthetic data generators for bench / smoke.
+//
+// Reference: scripts/direct_inference_full.py:290 (embedding row), :297-300 (F.linear(hidden, embed) in
+// bf16), :305-306 (argmax sampling at temperature 0).
+#include "common.cuh"
+#include "wf_bitnet.h"
+
+namespace wf {
+
+// ---------------------------------------------------------------------------------------------
+__global__ void embed_kernel(const uint4* __restrict__ table, const int32_t* __restrict__ tokens, int Hv, uint4* __restrict__ out) {
+    const int b = blockIdx.x;
+    pdl_wait_prior();
+    const int tok = tokens[b];
+    for (int i = threadIdx.x; i < Hv; i += blockDim.x) out[(size_t)b * Hv + i] = table[(size_t)tok * Hv + i];
+    pdl_launch_dependents();
+}
+
+// ---------------------------------------------------------------------------------------------
+// LM head: logits[b, v] = sum_k h[b,k] * E[v,k]; E bf16 [V,K] streamed once from HBM (657 MB for the 2B
+// model — more bytes than all ternary layers together).  CTA = 8 warps x 16 vocab rows,
+// 64-wide k stages through a 4-stage cp.async ring, XOR-swizzled smem, ldmatrix + mma.m16n8k16 bf16.
+constexpr int LM_ROWS = 128;
+constexpr int LM_KC = 64;                       // k per stage (128 B per row)
+constexpr int LM_STAGES = 4;
+
+template <int NT>
+__global__ void __launch_bounds__(256) lm_head_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* __restrict__ E,
+                                                      int B, int V, int K, float* __restrict__ logits_out,
+                                                      float* __restrict__ part_val, int* __restrict__ part_idx) {
+    constexpr int MT = NT * 8;
+    constexpr int E_STAGE = LM_ROWS * 128;
+    constexpr int H_STAGE = MT * 128;
+    constexpr int STAGE = E_STAGE + H_STAGE;
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int v0 = blockIdx.x * LM_ROWS;
+    const int m0 = blockIdx.y * MT;
+    const int nchunks = K / LM_KC;
+
+    auto load_stage = [&](int chunk, int stage) {
+        unsigned char* es = smem + stage * STAGE;
+        unsigned char* hs = es + E_STAGE;
+        for (int g = tid; g < LM_ROWS * 8; g += 256) {
+            const int r = g >> 3, c = g & 7;
+            const int v = v0 + r;
+            const int ok = v < V;
+            cp_async16_zfill(es + r * 128 + ((c ^ (r & 7)) << 4),
+                             ok ? (const void*)(E + (size_t)v * K + chunk * LM_KC + c * 8) : (const void*)E, ok ? 16 : 0);
+        }
+        for (int g = tid; g < MT * 8; g += 256) {
+            const int r = g >> 3, c = g & 7;
+            const int m = m0 + r;
+            const int ok = m < B;
+            cp_async16_zfill(hs + r * 128 + ((c ^ (r & 7)) << 4),
+                             ok ? (const void*)(h + (size_t)m * K + chunk * LM_KC + c * 8) : (const void*)h, ok ? 16 : 0);
+        }
+    };
+
+    float acc[NT][4];
+#pragma unroll
+    for (int i = 0; i < NT; ++i) { acc[i][0] = 0.f; acc[i][1] = 0.f; acc[i][2] = 0.f; acc[i][3] = 0.f; }
+
+    pdl_wait_prior();
+#pragma unroll
+    for (int s = 0; s < LM_STAGES - 1; ++s) {
+        if (s < nchunks) load_stage(s, s);
+        cp_async_commit();
+    }
+    for (int c = 0; c < nchunks; ++c) {
+        cp_async_wait<LM_STAGES - 2>();
+        __syncthreads();
+        {
+            const int nc = c + LM_STAGES - 1;
+            if (nc < nchunks) load_stage(nc, nc % LM_STAGES);
+            cp_async_commit();
+        }
+        const unsigned char* es = smem + (c % LM_STAGES) * STAGE;
+        const unsigned char* hs = es + E_STAGE;
+        // A fragments for the 4 k-steps of this stage: rows warp*16 + (lane&15), granule 2*ks + (lane>>4)
+        uint32_t a[4][4];
+        {
+            const int r = warp * 16 + (lane & 15);
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                const int cg = 2 * ks + (lane >> 4);
+                ldmatrix_x4(a[ks][0], a[ks][1], a[ks][2], a[ks][3], es + r * 128 + ((cg ^ (r & 7)) << 4));
+            }
+        }
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            const int r = nt * 8 + (lane & 7);
+#pragma unroll
+            for (int kp = 0; kp < 2; ++kp) {   // pairs of k-steps
+                const int cg = 4 * kp + (lane >> 3);
+                uint32_t b0, b1, b2, b3;
+                ldmatrix_x4(b0, b1, b2, b3, hs + r * 128 + ((cg ^ (r & 7)) << 4));
+                mma_bf16_16816(acc[nt], a[2 * kp][0], a[2 * kp][1], a[2 * kp][2], a[2 * kp][3], b0, b1);
+                mma_bf16_16816(acc[nt], a[2 * kp + 1][0], a[2 * kp + 1][1], a[2 * kp + 1][2], a[2 * kp + 1][3], b2, b3);
+            }
+        }
+    }
+    cp_async_wait<0>();
+    __syncthreads();
+
+    // logits tile -> smem [MT][LM_ROWS+1], rounded to bf16 like F.linear on bf16 tensors
+    float* St = reinterpret_cast<float*>(smem);
+    constexpr int SS = LM_ROWS + 1;
+    {
+        const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            const int ml = nt * 8 + 2 * t, nl = warp * 16 + g;
+            St[ml * SS + nl] = bf16_round(acc[nt][0]);
+            St[(ml + 1) * SS + nl] = bf16_round(acc[nt][1]);
+            St[ml * SS + nl + 8] = bf16_round(acc[nt][2]);
+            St[(ml + 1) * SS + nl + 8] = bf16_round(acc[nt][3]);
+        }
+    }
+    __syncthreads();
+    const int mcount = min(MT, B - m0);
+    if (logits_out) {
+        for (int i = tid; i < mcount * LM_ROWS; i += 256) {
+            const int ml = i / LM_ROWS, nl = i % LM_ROWS;
+            if (v0 + nl < V) logits_out[(size_t)(m0 + ml) * V + v0 + nl] = St[ml * SS + nl];
+        }
+    }
+    // per batch row: max / lowest index over this CTA's 128 vocab rows (warp w handles rows w, w+8, ...)
+    for (int ml = warp; ml < mcount; ml += 8) {
+        float best = -INFINITY;
+        int bi = 0x7fffffff;
+        for (int nl = lane; nl < LM_ROWS; nl += 32) {
+            const int v = v0 + nl;
+            if (v < V) {
+                const float x = St[ml * SS + nl];
+                if (x > best || (x == best && v < bi)) { best = x; bi = v; }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+        }
+        if (lane == 0) {
+            part_val[(size_t)(m0 + ml) * gridDim.x + blockIdx.x] = best;
+            part_idx[(size_t)(m0 + ml) * gridDim.x + blockIdx.x] = bi;
+        }
+    }
+    pdl_launch_dependents();
+}
+
+__global__ void __launch_bounds__(256) argmax_reduce_kernel(const float* __restrict__ part_val, const int* __restrict__ part_idx,
+                                                            int nparts, int32_t* __restrict__ next) {
+    __shared__ float sv[8];
+    __shared__ int si[8];
+    const int b = blockIdx.x;
+    pdl_wait_prior();
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int i = threadIdx.x; i < nparts; i += 256) {
+        const float x = part_val[(size_t)b * nparts + i];
+        const int v = part_idx[(size_t)b * nparts + i];
+        if (x > best || (x == best && v < bi)) { best = x; bi = v; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w)
+            if (sv[w] > best || (sv[w] == best && si[w] < bi)) { best = sv[w]; bi = si[w]; }
+        next[b] = bi;
+    }
+    pdl_launch_dependents();
+}
+
+// positions / seq_lens advance + feed the sampled token back (device-resident decode loop)
+__global__ void advance_kernel(int32_t* positions, int32_t* seq_lens, int32_t* tokens, const int32_t* next, int B, int feed_back) {
+    pdl_wait_prior();
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < B) {
+        positions[b] += 1;
+        seq_lens[b] += 1;
+        if (feed_back) tokens[b] = next[b];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// synthetic data (bench / smoke only): splitmix64 counter hash
+__device__ __forceinline__ uint64_t mix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+// uniformly random ternary codes {0,1,2}, 16 per u32
+__global__ void fill_ternary_kernel(uint32_t* out, size_t nwords, uint64_t seed) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nwords; i += (size_t)gridDim.x * blockDim.x) {
+        uint64_t r = mix64(seed ^ (i * 0x2545F4914F6CDD1Dull));
+        uint64_t r2 = mix64(r);
+        uint32_t w = 0;
+#pragma unroll
+        for (int f = 0; f < 16; ++f) {
+            const uint32_t bits = (uint32_t)((f < 8 ? r : r2) >> (8 * (f & 7))) & 0xff;
+            w |= ((bits * 3u) >> 8) << (2 * f);
+        }
+        out[i] = w;
+    }
+}
+// bf16 values mean + std * approx-normal (sum of 4 uniforms)
+__global__ void fill_bf16_kernel(__nv_bfloat16* out, size_t n, uint64_t seed, float mean, float std) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const uint64_t r = mix64(seed ^ (i * 0x9E3779B97F4A7C15ull));
+        float u = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) u += (float)((r >> (16 * j)) & 0xffff) * (1.0f / 65536.0f);
+        out[i] = __float2bfloat16_rn(mean + std * (u - 2.0f) * 1.7320508f);
+    }
+}
+
+int launch_embed(const void* table, const int32_t* tokens, int B, int H, void* out, cudaStream_t s) {
+    embed_kernel<<<B, 128, 0, s>>>((const uint4*)table, tokens, H / 8, (uint4*)out);
+    return launch_check(cudaGetLastError(), "embed");
+}
+
+int launch_advance(int32_t* positions, int32_t* seq_lens, int32_t* tokens, const int32_t* next, int B, int feed_back, cudaStream_t s) {
+    advance_kernel<<<(B + 127) / 128, 128, 0, s>>>(positions, seq_lens, tokens, next, B, feed_back);
+    return launch_check(cudaGetLastError(), "advance");
+}
+
+int launch_fill_ternary(void* out, size_t bytes, uint64_t seed, cudaStream_t s) {
+    fill_ternary_kernel<<<sm_count() * 8, 256, 0, s>>>((uint32_t*)out, bytes / 4, seed);
+    return launch_check(cudaGetLastError(), "fill_ternary");
+}
+int launch_fill_bf16(void* out, size_t n, uint64_t seed, float mean, float std, cudaStream_t s) {
+    fill_bf16_kernel<<<sm_count() * 8, 256, 0, s>>>((__nv_bfloat16*)out, n, seed, mean, std);
+    return launch_check(cudaGetLastError(), "fill_bf16");
+}
+
+template <int NT>
+static int launch_lm(const void* h, const void* E, int B, int V, int K, float* logits_out, float* pv, int* pi, int nparts, cudaStream_t s) {
+    constexpr int MT = NT * 8;
+    constexpr int STAGE = LM_ROWS * 128 + MT * 128;
+    constexpr int SM_PIPE = STAGE * LM_STAGES;
+    constexpr int SM_EPI = MT * (LM_ROWS + 1) * 4;
+    constexpr int SMEM = SM_PIPE > SM_EPI ? SM_PIPE : SM_EPI;
+    auto kern = lm_head_kernel<NT>;
+    static bool attr = false;
+    if (!attr) {
+        if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM), "lm smem")) return WF_ERR_CUDA;
+        attr = true;
+    }
+    dim3 grid(nparts, (B + MT - 1) / MT);
+    kern<<<grid, 256, SMEM, s>>>((const __nv_bfloat16*)h, (const __nv_bfloat16*)E, B, V, K, logits_out, pv, pi);
+    return launch_check(cudaGetLastError(), "lm_head");
+}
+
+int launch_lm_head_argmax(const void* h, const void* E, int B, int V, int K, float* logits_out, int32_t* next_out, void* workspace,
+                          cudaStream_t s) {
+    const int nparts = (V + LM_ROWS - 1) / LM_ROWS;
+    float* pv = (float*)workspace;
+    int* pi = (int*)(pv + (size_t)B * nparts);
+    int rc;
+    if (B <= 8) rc = launch_lm<1>(h, E, B, V, K, logits_out, pv, pi, nparts, s);
+    else if (B <= 16) rc = launch_lm<2>(h, E, B, V, K, logits_out, pv, pi, nparts, s);
+    else if (B <= 32) rc = launch_lm<4>(h, E, B, V, K, logits_out, pv, pi, nparts, s);
+    else rc = launch_lm<8>(h, E, B, V, K, logits_out, pv, pi, nparts, s);
+    if (rc) return rc;
+    if (next_out) {
+        argmax_reduce_kernel<<<B, 256, 0, s>>>(pv, pi, nparts, next_out);
+        return launch_check(cudaGetLastError(), "argmax_reduce");
+    }
+    return WF_OK;
+}
+
+}  // namespace wf
+
+using namespace wf;
+
+extern "C" int wf_embed(const void* table, const int32_t* tokens, int B, int H, void* out, void* stream) {
+    if (!table || !tokens || !out || B <= 0 || H <= 0 || H % 8) { set_error("wf_embed: bad arguments (H %% 8 == 0)"); return WF_ERR_INVALID; }
+    return launch_embed(table, tokens, B, H, out, (cudaStream_t)stream);
+}
+
+extern "C" size_t wf_lm_head_workspace_bytes(int B, int V) {
+    const size_t nparts = (size_t)(V + LM_ROWS - 1) / LM_ROWS;
+    return (size_t)(B > 0 ? B : 1) * nparts * 8 + 256;
+}
+
+extern "C" int wf_lm_head_argmax(const void* h, const void* E, int B, int V, int K, float* logits_out, int32_t* next_out,
+                                 void* workspace, size_t workspace_bytes, void* stream) {
+    if (!h || !E || !workspace) { set_error("wf_lm_head_argmax: null pointer"); return WF_ERR_INVALID; }
+    if (B <= 0 || V <= 0 || K <= 0 || K % LM_KC) { set_error("wf_lm_head_argmax: bad shape (K %% 64 == 0)"); return WF_ERR_INVALID; }
+    if (B > 64) { set_error("wf_lm_head_argmax: B > 64 not supported"); return WF_ERR_UNSUPPORTED; }
+    if (workspace_bytes < wf_lm_head_workspace_bytes(B, V)) { set_error("wf_lm_head_argmax: workspace too small"); return WF_ERR_INVALID; }
+    return launch_lm_head_argmax(h, E, B, V, K, logits_out, next_out, workspace, (cudaStream_t)stream);
+}
+
+namespace wf {
+template <int NT> static void lm_set_attr() {
+    constexpr int MT = NT * 8;
+    constexpr int SM_PIPE = (LM_ROWS * 128 + MT * 128) * LM_STAGES;
+    constexpr int SM_EPI = MT * (LM_ROWS + 1) * 4;
+    cudaFuncSetAttribute(lm_head_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_PIPE > SM_EPI ? SM_PIPE : SM_EPI);
+}
+void lm_init_attrs() { lm_set_attr<1>(); lm_set_attr<2>(); lm_set_attr<4>(); lm_set_attr<8>(); }
+}
