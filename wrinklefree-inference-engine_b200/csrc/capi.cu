@@ -57,7 +57,8 @@ int fill_epi(const wf_linear_args* a, EpiParams* p) {
     p->ldo = a->ldo;
     p->residual = (const __nv_bfloat16*)a->residual;
 
-    if (!a->w || !a->q || !a->out) { set_error("wf_ternary_linear: null w/q/out"); return WF_ERR_INVALID; }
+    // an empty batch (M == 0) is a no-op: torch hands out null data pointers for zero-size tensors
+    if (!a->w || (a->M > 0 && (!a->q || !a->out))) { set_error("wf_ternary_linear: null w/q/out"); return WF_ERR_INVALID; }
     if (a->N <= 0 || a->M < 0 || a->K <= 0) { set_error("wf_ternary_linear: bad shape M=%d N=%d K=%d", a->M, a->N, a->K); return WF_ERR_INVALID; }
     if (a->K % WF_QK != 0) { set_error("in_features (%d) must be multiple of %d", a->K, WF_QK); return WF_ERR_INVALID; }
     if (a->ldq < a->K || a->ldq % 16 != 0) { set_error("wf_ternary_linear: ldq (%d) must be >= K and a multiple of 16", a->ldq); return WF_ERR_INVALID; }
