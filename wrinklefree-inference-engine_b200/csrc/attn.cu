@@ -15,8 +15,7 @@
 //   the streaming loop and ~100 KB of loads stay in flight per SM.  The G = H/Hkv query heads of a KV
 //   head form the (padded) M=16 rows of mma.m16n8k16 bf16: S = Q K^T (fp32), online softmax in fp32 with
 //   exp2, O += P V.  Warps are merged through shared memory; chunks are merged by a second tiny kernel.
-#include "common.cuh"
-#include "wf_bitnet.h"
+#include "fused_common.cuh"
 
 namespace wf {
 
@@ -43,19 +42,40 @@ struct AttnParams {
     float* part_o;               // [B][H][max_chunks][D]
     float* part_ml;              // [B][H][max_chunks][2]
     int direct;                  // 1: single chunk per sequence everywhere -> write final output
+    // ---- fused prologue / epilogue (decode engine): q, k, v come straight from the qkv linear's raw accumulator
+    const float* qkv_acc;        // [B][qkv_ld] fp32 exact integers: sum (w+1)*a, rows q | k | v
+    int qkv_ld;
+    const int32_t* qkv_rowsum;   // [B]
+    const float* qkv_ascale;     // [B]
+    const float* qkv_wscale;     // device [3]: q, k, v weight scales
+    const int32_t* positions;    // [B] position of the new token (== seq_len - 1)
+    const __nv_bfloat16* cos_tab;
+    const __nv_bfloat16* sin_tab;
+    int max_pos;
+    __nv_bfloat16* pool_w;       // pool, writable (append)
+    int* merge_cnt;              // [B][Hkv] arrival counters (zero; self-cleaning)
+    float* zero0; int zero0_n;   // accumulator range this phase clears
 };
 
 __device__ __forceinline__ size_t kv_block_offset(int page, int layers, int layer, int kv, int Hkv, int head, int page_size) {
     return ((((size_t)page * layers + layer) * 2 + kv) * Hkv + head) * (size_t)page_size * AT_D;
 }
 
+template <bool FUSED>
 __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(const AttnParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int chunk = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
     const int g = lane >> 2, t = lane & 3;
 
+    if (FUSED) pdl_launch_dependents();
     pdl_wait_prior();
+    if (FUSED && p.zero0) {
+        const int nb = gridDim.x * gridDim.y * gridDim.z;
+        const int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        for (int i = (bid * AT_WARPS * 32 + tid) * 4; i < p.zero0_n; i += nb * AT_WARPS * 32 * 4)
+            *reinterpret_cast<float4*>(p.zero0 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     const int seq_len = p.seq_lens[b];
     const int nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
     const int blk0 = chunk * p.chunk_blocks;
@@ -67,12 +87,72 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
 
     // ---- Q fragments (rows g < G valid; rows 8..15 are zero padding)
     uint32_t qa[8][2];
-    {
+    if (!FUSED) {
         const __nv_bfloat16* qrow = p.q + ((size_t)b * p.H + (size_t)kvh * p.G + g) * AT_D;
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
             qa[ks][0] = (g < p.G) ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 2 * t) : 0u;
             qa[ks][1] = (g < p.G) ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8 + 2 * t) : 0u;
+        }
+    } else {
+        // dequantise the qkv accumulator (direct_inference_full.py:204-206), round to bf16 as the linear's output
+        // tensor, half-split RoPE with the reference's bf16 rounding points (:58-70), append k/v (:226-227).
+        const int pos = p.positions[b];
+        const int pc = min(pos, p.max_pos - 1);
+        const float* arow = p.qkv_acc + (size_t)b * p.qkv_ld;
+        const int rs = p.qkv_rowsum[b];
+        const float sa = p.qkv_ascale[b];
+        const __nv_bfloat16* ct = p.cos_tab + (size_t)pc * (AT_D / 2);
+        const __nv_bfloat16* st = p.sin_tab + (size_t)pc * (AT_D / 2);
+        {
+            const float wq = p.qkv_wscale[0];
+            const float* hq = arow + ((size_t)kvh * p.G + g) * AT_D;
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    const int d = ks * 16 + half * 8 + 2 * t;   // < 64; partner at d + 64
+                    float o1[2], o2[2];
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        float x1 = 0.f, x2 = 0.f;
+                        if (g < p.G) {
+                            x1 = bf16_round(lin_value(ldcg_f(hq + d + e), rs, wq, sa));
+                            x2 = bf16_round(lin_value(ldcg_f(hq + d + e + 64), rs, wq, sa));
+                        }
+                        const float c = __bfloat162float(ct[d + e]), s = __bfloat162float(st[d + e]);
+                        o1[e] = bf16_round(x1 * c) - bf16_round(x2 * s);
+                        o2[e] = bf16_round(x1 * s) + bf16_round(x2 * c);
+                    }
+                    qa[ks][half] = pack_bf16x2(o1[0], o1[1]);
+                    qa[ks + 4][half] = pack_bf16x2(o2[0], o2[1]);
+                }
+            }
+        }
+        // the CTA whose chunk holds the new token appends k (RoPE'd) and v before it streams that block
+        const int blk_pos = pos / AT_BLK;
+        if (blk_pos >= blk0 && blk_pos < blk1) {
+            const int page = bt[pos / p.page_size];
+            const int slot = pos % p.page_size;
+            const int d = tid & 63;
+            if (tid < 64) {
+                const float wk = p.qkv_wscale[1];
+                const float* hk = arow + ((size_t)p.H + kvh) * AT_D;
+                const float x1 = bf16_round(lin_value(ldcg_f(hk + d), rs, wk, sa));
+                const float x2 = bf16_round(lin_value(ldcg_f(hk + d + 64), rs, wk, sa));
+                const float c = __bfloat162float(ct[d]), s = __bfloat162float(st[d]);
+                __nv_bfloat16* dst = p.pool_w + kv_block_offset(page, p.layers, p.layer, 0, p.Hkv, kvh, p.page_size) + (size_t)slot * AT_D;
+                dst[d] = __float2bfloat16_rn(bf16_round(x1 * c) - bf16_round(x2 * s));
+                dst[d + 64] = __float2bfloat16_rn(bf16_round(x1 * s) + bf16_round(x2 * c));
+            } else {
+                const float wv = p.qkv_wscale[2];
+                const float* hv = arow + ((size_t)p.H + p.Hkv + kvh) * AT_D;
+                __nv_bfloat16* dst = p.pool_w + kv_block_offset(page, p.layers, p.layer, 1, p.Hkv, kvh, p.page_size) + (size_t)slot * AT_D;
+                dst[d] = __float2bfloat16_rn(lin_value(ldcg_f(hv + d), rs, wv, sa));
+                dst[d + 64] = __float2bfloat16_rn(lin_value(ldcg_f(hv + d + 64), rs, wv, sa));
+            }
+            __threadfence();
+            __syncthreads();
         }
     }
 
@@ -224,7 +304,41 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
             }
         }
     }
-    pdl_launch_dependents();
+    if (FUSED && !p.direct) {
+        // the last chunk to arrive for this (sequence, kv head) merges all of them — no separate merge launch
+        __shared__ int s_last;
+        const int nch = (nblocks + p.chunk_blocks - 1) / p.chunk_blocks;
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            int* c = p.merge_cnt + (size_t)b * p.Hkv + kvh;
+            const int prev = atomicAdd(c, 1);
+            s_last = (prev == nch - 1);
+            if (s_last) *c = 0;
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            const int d = tid;
+            for (int hh = 0; hh < p.G; ++hh) {
+                const int h = kvh * p.G + hh;
+                const size_t base = ((size_t)b * p.H + h) * p.max_chunks;
+                float M = -INFINITY;
+                for (int c = 0; c < nch; ++c) M = fmaxf(M, ldcg_f(p.part_ml + (base + c) * 2));
+                float L = 0.f, O = 0.f;
+                for (int c = 0; c < nch; ++c) {
+                    const float mc = ldcg_f(p.part_ml + (base + c) * 2);
+                    const float f = (mc == -INFINITY) ? 0.f : exp2f(mc - M);
+                    L += ldcg_f(p.part_ml + (base + c) * 2 + 1) * f;
+                    O += ldcg_f(p.part_o + (base + c) * AT_D + d) * f;
+                }
+                const float v = (L > 0.f) ? O / L : 0.f;
+                if (p.out_dtype == WF_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[((size_t)b * p.H + h) * AT_D + d] = __float2bfloat16_rn(v);
+                else reinterpret_cast<float*>(p.out)[((size_t)b * p.H + h) * AT_D + d] = v;
+            }
+        }
+    }
+    if (!FUSED) pdl_launch_dependents();
 }
 
 struct MergeParams {
@@ -345,7 +459,8 @@ int launch_rope_kv_append(const RopeParams& p, cudaStream_t s, bool pdl) {
 int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, size_t workspace_bytes, cudaStream_t s, bool pdl) {
     static bool attr = false;
     if (!attr) {
-        if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM), "attn smem")) return WF_ERR_CUDA;
+        if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM), "attn smem")) return WF_ERR_CUDA;
+        if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM), "attn smem")) return WF_ERR_CUDA;
         attr = true;
     }
     const int max_blocks16 = (max_seq_hint + AT_BLK - 1) / AT_BLK;
@@ -378,7 +493,9 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
         cfg.stream = s;
         cfg.attrs = at;
         cfg.numAttrs = pdl ? 1 : 0;
-        if (launch_check(cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel, p), "paged_decode_attn")) return WF_ERR_CUDA;
+        const bool fused = p.qkv_acc != nullptr;
+        if (launch_check(fused ? cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel<true>, p) : cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel<false>, p), "paged_decode_attn")) return WF_ERR_CUDA;
+        if (fused) return WF_OK;
     }
     if (!p.direct) {
         MergeParams mp;
@@ -420,6 +537,22 @@ int attn_decode(const void* q, const void* pool, int layers, int layer, int Hkv,
     p.scale_log2e = scale * 1.4426950408889634f;
     p.out = out; p.out_dtype = out_dtype;
     return launch_paged_decode_attn(p, max_seq_hint, ws, ws_bytes, s, pdl);
+}
+
+// decode-engine form: q/k/v are dequantised from the qkv linear's raw accumulator inside the kernel (RoPE, KV append,
+// attention and the chunk merge are one launch)
+int attn_decode_fused(const FusedAttnArgs& a, cudaStream_t s, bool pdl) {
+    AttnParams p = {};
+    p.pool = (const __nv_bfloat16*)a.pool; p.pool_w = (__nv_bfloat16*)a.pool;
+    p.block_table = a.block_table; p.seq_lens = a.seq_lens;
+    p.B = a.B; p.H = a.H; p.Hkv = a.Hkv; p.G = a.H / a.Hkv;
+    p.layers = a.layers; p.layer = a.layer; p.page_size = a.page_size; p.max_blocks = a.max_blocks;
+    p.scale_log2e = a.scale * 1.4426950408889634f;
+    p.out = a.out; p.out_dtype = WF_BF16;
+    p.qkv_acc = a.qkv_acc; p.qkv_ld = a.qkv_ld; p.qkv_rowsum = a.qkv_rowsum; p.qkv_ascale = a.qkv_ascale; p.qkv_wscale = a.qkv_wscale;
+    p.positions = a.positions; p.cos_tab = (const __nv_bfloat16*)a.cos_tab; p.sin_tab = (const __nv_bfloat16*)a.sin_tab; p.max_pos = a.max_pos;
+    p.merge_cnt = a.merge_cnt; p.zero0 = a.zero0; p.zero0_n = a.zero0_n;
+    return launch_paged_decode_attn(p, a.max_seq_hint, a.ws, a.ws_bytes, s, pdl);
 }
 
 }  // namespace wf
@@ -495,5 +628,8 @@ extern "C" int wf_paged_decode_attn(const void* q, const wf_kv_layout* kv, int l
 }
 
 namespace wf {
-void attn_init_attrs() { cudaFuncSetAttribute(paged_decode_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM); }
+void attn_init_attrs() {
+    cudaFuncSetAttribute(paged_decode_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    cudaFuncSetAttribute(paged_decode_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+}
 }

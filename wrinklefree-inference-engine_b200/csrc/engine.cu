@@ -8,6 +8,7 @@
 //   -> sub-norm+quant -> o linear (+residual) -> rmsnorm+quant -> gate|up linear (relu^2*up)
 //   -> sub-norm+quant -> down linear (+residual).
 #include "kernels.cuh"
+#include "fused_common.cuh"
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
@@ -59,6 +60,14 @@ struct wf_engine {
     bool finalized = false;
     bool pdl = false;
     int linear_algo = 0;
+    int fused = 1;           // 1: phase kernels (linear_small / glue_rows + gemm_oneshot / fused attention); 0: one kernel per op
+    // fused path state: raw fp32 accumulators of the four linears, their per-token activation scale / Sigma a,
+    // a second hidden buffer (residual ping-pong) and the attention merge counters
+    float *acc_qkv = nullptr, *acc_o = nullptr, *acc_gu = nullptr, *acc_down = nullptr;
+    float* lin_asc = nullptr;      // [4][max_batch]
+    int32_t* lin_rs = nullptr;     // [4][max_batch]
+    __nv_bfloat16* hid2 = nullptr;
+    int* merge_cnt = nullptr;
     int launches = 0;
     int attn_seq_hint = 0;   // max sequence length the chunking is sized for (fixed per captured graph)
     cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};   // [feed_back]
@@ -167,6 +176,99 @@ int run_step(wf_engine* e, int B, int feed_back) {
     return WF_OK;
 }
 
+// The same step as phase kernels (fused_common.cuh): every linear leaves its raw accumulator in an fp32 buffer and the
+// NEXT phase applies scales / residual / relu^2*up / norm / re-quantisation in its prologue.
+//   B <= 8 : 5 launches per layer (qkv, attention, o, gate|up, down), each linear = glue prologue + TMA-streamed GEMV
+//   B  > 8 : 9 launches per layer (glue_rows + gemm_oneshot per linear, fused attention)
+int run_step_fused(wf_engine* e, int B, int feed_back) {
+    const wf_model_config& c = e->cfg;
+    cudaStream_t s = e->stream;
+    const bool pdl = e->pdl;
+    const long long launches0 = launch_count();
+    const int MB = c.max_batch;
+    float* asc[4] = {e->lin_asc, e->lin_asc + MB, e->lin_asc + 2 * MB, e->lin_asc + 3 * MB};
+    int32_t* rs[4] = {e->lin_rs, e->lin_rs + MB, e->lin_rs + 2 * MB, e->lin_rs + 3 * MB};
+    __nv_bfloat16 *hA = e->hid, *hB = e->hid2;
+    int rc;
+    auto phase = [&](GlueParams g, const uint8_t* w, int N, int K, float* acc_out, int slot, bool first) -> int {
+        g.M = B; g.K = K; g.eps = c.eps;
+        if (B <= 8 && linear_small_fits(B, K)) {
+            SmallLinArgs a;
+            a.g = g; a.w = w; a.N = N; a.K = K; a.acc_out = acc_out; a.acc_ld = N; a.lin_ascale = asc[slot]; a.lin_rowsum = rs[slot];
+            return launch_linear_small(a, s, pdl && !first);
+        }
+        g.q_out = e->q8; g.scale_out = asc[slot]; g.rowsum_out = rs[slot];
+        int r = launch_glue_rows(g, s, pdl && !first);
+        if (r) return r;
+        OneshotArgs o;
+        o.w = w; o.N = N; o.K = K; o.q = e->q8; o.M = B; o.acc_out = acc_out; o.acc_ld = N;
+        return launch_gemm_oneshot(o, s, pdl);
+    };
+    const float attn_scale = 1.0f / sqrtf((float)e->D);
+    for (int l = 0; l < c.layers; ++l) {
+        LayerW& L = e->layers[l];
+        // ---- A: (embed | hidden + down-proj of the previous layer) -> input_layernorm -> qkv
+        {
+            GlueParams g = {};
+            if (l == 0) { g.mode = GL_EMBED; g.embed = e->embed; g.tokens = e->d_tok; }
+            else {
+                g.mode = GL_RESID; g.hid_in = hA; g.acc = e->acc_down; g.acc_ld = e->hidden;
+                g.acc_rowsum = rs[3]; g.acc_ascale = asc[3]; g.acc_wscale = e->layers[l - 1].scales + 6;
+            }
+            g.hid_out = hB; g.gamma = L.g_in;
+            g.zero0 = e->acc_gu; g.zero0_n = B * 2 * e->ffn;
+            if ((rc = phase(g, L.qkv, e->qkv_rows, e->hidden, e->acc_qkv, 0, l == 0))) return rc;
+        }
+        // ---- B: dequant + RoPE + KV append + paged attention + chunk merge
+        {
+            FusedAttnArgs a = {};
+            a.pool = e->pool; a.layers = c.layers; a.layer = l; a.Hkv = e->Hkv; a.page_size = c.page_size;
+            a.block_table = e->d_block_table; a.max_blocks = e->max_blocks; a.seq_lens = e->d_len; a.positions = e->d_pos;
+            a.B = B; a.H = e->H; a.scale = attn_scale; a.out = e->attn;
+            a.qkv_acc = e->acc_qkv; a.qkv_ld = e->qkv_rows; a.qkv_rowsum = rs[0]; a.qkv_ascale = asc[0]; a.qkv_wscale = L.scales;
+            a.cos_tab = e->cos_tab; a.sin_tab = e->sin_tab; a.max_pos = c.max_seq;
+            a.merge_cnt = e->merge_cnt; a.zero0 = e->acc_down; a.zero0_n = B * e->hidden;
+            a.max_seq_hint = e->attn_seq_hint; a.ws = e->ws_attn; a.ws_bytes = e->ws_attn_bytes;
+            if ((rc = attn_decode_fused(a, s, pdl))) return rc;
+        }
+        // ---- C: attn_sub_norm -> o
+        {
+            GlueParams g = {};
+            g.mode = GL_PLAIN; g.src = e->attn; g.gamma = L.g_attn;
+            g.zero0 = e->acc_qkv; g.zero0_n = B * e->qkv_rows;
+            if ((rc = phase(g, L.o, e->hidden, e->attn_dim, e->acc_o, 1, false))) return rc;
+        }
+        // ---- D: hidden + o-proj -> post_attention_layernorm -> gate|up
+        {
+            GlueParams g = {};
+            g.mode = GL_RESID; g.hid_in = hB; g.hid_out = hA; g.acc = e->acc_o; g.acc_ld = e->hidden;
+            g.acc_rowsum = rs[1]; g.acc_ascale = asc[1]; g.acc_wscale = L.scales + 3; g.gamma = L.g_post;
+            if ((rc = phase(g, L.gu, 2 * e->ffn, e->hidden, e->acc_gu, 2, false))) return rc;
+        }
+        // ---- E: relu^2(gate)*up -> ffn_sub_norm -> down
+        {
+            GlueParams g = {};
+            g.mode = GL_RELU2; g.acc = e->acc_gu; g.acc_ld = 2 * e->ffn;
+            g.acc_rowsum = rs[2]; g.acc_ascale = asc[2]; g.acc_wscale = L.scales + 4; g.gamma = L.g_ffn;
+            g.zero0 = e->acc_o; g.zero0_n = B * e->hidden;
+            if ((rc = phase(g, L.down, e->hidden, e->ffn, e->acc_down, 3, false))) return rc;
+        }
+    }
+    // hidden + down-proj -> final norm -> tied LM head + greedy argmax
+    {
+        GlueParams g = {};
+        g.mode = GL_RESID; g.M = B; g.K = e->hidden; g.eps = c.eps;
+        g.hid_in = hA; g.hid_out = hB; g.acc = e->acc_down; g.acc_ld = e->hidden;
+        g.acc_rowsum = rs[3]; g.acc_ascale = asc[3]; g.acc_wscale = e->layers[c.layers - 1].scales + 6;
+        g.gamma = e->final_norm; g.y_out = e->normed; g.q_out = e->q8;
+        if ((rc = launch_glue_rows(g, s, pdl))) return rc;
+    }
+    if ((rc = launch_lm_head_argmax(e->normed, e->embed, B, c.vocab, e->hidden, e->logits, e->d_next, e->ws_lm, s))) return rc;
+    if ((rc = launch_advance(e->d_pos, e->d_len, e->d_tok, e->d_next, B, feed_back, s))) return rc;
+    e->launches = (int)(launch_count() - launches0);
+    return WF_OK;
+}
+
 // host-side bookkeeping before a step: make sure every active sequence has a page for its next token
 int prepare_pages(wf_engine* e, int B) {
     const int ps = e->cfg.page_size;
@@ -206,7 +308,7 @@ int step_graph(wf_engine* e, int B, int feed_back, int use_graph) {
     const int hint = seq_hint_for(e, B);
     if (!use_graph) {
         e->attn_seq_hint = hint;
-        return run_step(e, B, feed_back);
+        return e->fused ? run_step_fused(e, B, feed_back) : run_step(e, B, feed_back);
     }
     const int gi = feed_back ? 1 : 0;
     if (!e->graph_exec[gi] || e->graph_B[gi] != B || e->graph_hint[gi] != hint) {
@@ -218,7 +320,7 @@ int step_graph(wf_engine* e, int B, int feed_back, int use_graph) {
         // and run them once outside capture in wf_engine_finalize_weights (warm-up step on slot state 0).
         cudaGraph_t graph = nullptr;
         if (cuda_check(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal), "begin capture")) return WF_ERR_CUDA;
-        int rc = run_step(e, B, feed_back);
+        int rc = e->fused ? run_step_fused(e, B, feed_back) : run_step(e, B, feed_back);
         cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
         if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
         if (cuda_check(ce, "end capture")) return WF_ERR_CUDA;
@@ -253,10 +355,14 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     e->pdl = env_pdl && atoi(env_pdl) != 0;
     const char* env_algo = getenv("WF_LINEAR_ALGO");
     e->linear_algo = env_algo ? atoi(env_algo) : 0;
+    const char* env_fused = getenv("WF_FUSED");
+    e->fused = env_fused ? atoi(env_fused) != 0 : 1;
+    if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
     int rc = WF_OK;
     auto fail = [&](int r) { wf_engine_destroy(e); return r; };
     if (cuda_check(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking), "stream create")) return fail(WF_ERR_CUDA);
     init_all_kernel_attrs();
+    fused_init_attrs();
     cudaGetLastError();
     const int B = c.max_batch;
     e->layers.resize(c.layers);
@@ -309,6 +415,13 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
         (rc = dalloc(e, &e->attn, (size_t)B * e->attn_dim)) || (rc = dalloc(e, &e->gu, (size_t)B * e->ffn)) ||
         (rc = dalloc(e, &e->q8, (size_t)B * maxK)) || (rc = dalloc(e, &e->a_scale, B)) || (rc = dalloc(e, &e->rowsum, B)) ||
         (rc = dalloc(e, &e->logits, (size_t)B * c.vocab))) return fail(rc);
+    if ((rc = dalloc(e, &e->acc_qkv, (size_t)B * e->qkv_rows)) || (rc = dalloc(e, &e->acc_o, (size_t)B * e->hidden)) ||
+        (rc = dalloc(e, &e->acc_gu, (size_t)B * 2 * e->ffn)) || (rc = dalloc(e, &e->acc_down, (size_t)B * e->hidden)) ||
+        (rc = dalloc(e, &e->lin_asc, (size_t)4 * B)) || (rc = dalloc(e, &e->lin_rs, (size_t)4 * B)) ||
+        (rc = dalloc(e, &e->hid2, (size_t)B * e->hidden)) || (rc = dalloc(e, &e->merge_cnt, (size_t)B * e->Hkv))) return fail(rc);
+    if (cuda_check(cudaMemset(e->acc_qkv, 0, (size_t)B * e->qkv_rows * 4), "acc memset") || cuda_check(cudaMemset(e->acc_o, 0, (size_t)B * e->hidden * 4), "acc memset") ||
+        cuda_check(cudaMemset(e->acc_gu, 0, (size_t)B * 2 * e->ffn * 4), "acc memset") || cuda_check(cudaMemset(e->acc_down, 0, (size_t)B * e->hidden * 4), "acc memset") ||
+        cuda_check(cudaMemset(e->merge_cnt, 0, (size_t)B * e->Hkv * 4), "cnt memset")) return fail(WF_ERR_CUDA);
     const int maxN = 2 * e->ffn > e->qkv_rows ? 2 * e->ffn : e->qkv_rows;
     e->ws_lin_bytes = wf_linear_workspace_bytes(B, maxN, maxK) + (size_t)maxN * 4;
     e->ws_attn_bytes = wf_attn_workspace_bytes(B, e->H, e->D, c.max_seq);

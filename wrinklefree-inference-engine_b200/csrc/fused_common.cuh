@@ -1,0 +1,281 @@
+// Fused decode path: conventions shared by the phase kernels (linear_small.cu, gemm_oneshot.cu,
+// glue_rows.cu, attn.cu).
+//
+// Every ternary linear of the decode step leaves its RAW accumulator S[m][n] = sum_k (w+1)*a in a global
+// fp32 buffer.  All values are integers with |S| <= 2*128*28672 < 2^24, so fp32 holds them exactly and
+// fp32 atomic adds (RED, vectorised .v4 where possible) are exact and order-independent — split-K needs no
+// "last CTA" tail.  The CONSUMER of a linear applies the reference's epilogue
+//   out = (S - s_w-free Sigma a) * s_w * s_a      (scripts/direct_inference_full.py:204-206)
+// together with whatever follows it in the reference step (residual add, relu^2*up, RMSNorm / sub-norm,
+// per-token int8 quantisation: direct_inference_full.py:181-184,247,259,262,276,283) — "glue".  The bf16
+// rounding points are the reference's (every torch op on a bf16 tensor rounds).
+#pragma once
+#include "common.cuh"
+#include "wf_bitnet.h"
+
+namespace wf {
+
+enum GlueMode {
+    GL_EMBED = 0,   // x = embed[token]                                  (direct_inference_full.py:290)
+    GL_RESID = 1,   // x = bf16(hid_in + bf16(lin(acc)))                 (:276, :283)
+    GL_PLAIN = 2,   // x = src (bf16)                                    (attention output, :244)
+    GL_RELU2 = 3,   // x = bf16(bf16(relu(g)^2) * u), g/u = bf16(lin(acc gate/up))   (:259)
+};
+
+struct GlueParams {
+    int mode, M, K;
+    const __nv_bfloat16* embed;     // GL_EMBED: [V][K]
+    const int32_t* tokens;          //           [M]
+    const __nv_bfloat16* hid_in;    // GL_RESID: [M][K]
+    __nv_bfloat16* hid_out;         // GL_EMBED / GL_RESID: [M][K] (may be null)
+    const __nv_bfloat16* src;       // GL_PLAIN: [M][K]
+    const float* acc;               // GL_RESID: [M][acc_ld]; GL_RELU2: gate|up interleaved in 16-row blocks
+    int acc_ld;
+    const int32_t* acc_rowsum;      // [M] Sigma a of the linear that produced acc
+    const float* acc_ascale;        // [M] its per-token activation scale
+    const float* acc_wscale;        // device: [1] (RESID) or [2] gate, up (RELU2)
+    const __nv_bfloat16* gamma;     // [K] norm weight
+    float eps;
+    float* zero0; int zero0_n;      // fp32 ranges this phase must clear (accumulators consumed one phase ago)
+    float* zero1; int zero1_n;
+    // outputs of the standalone glue kernel (large batch); the small-batch linear keeps them in smem
+    int8_t* q_out;                  // [M][K]
+    float* scale_out;               // [M]
+    int32_t* rowsum_out;            // [M]
+    __nv_bfloat16* y_out;           // [M][K] normalised activations (final norm -> LM head), optional
+};
+
+__device__ __forceinline__ float4 ldcg_f4(const float* p) {
+    float4 r;
+    asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ uint4 ldcg_u4(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ float ldcg_f(const float* p) {
+    float r;
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p));
+    return r;
+}
+// exact: |S| < 2^24
+__device__ __forceinline__ float lin_value(float S, int rowsum, float ws, float sa) {
+    return ((float)((int)S - rowsum) * ws) * sa;
+}
+__device__ __forceinline__ void red_add_f32(float* p, float v) {
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_v4_f32(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// named barrier over the first NT threads of the CTA (warps 0..NT/32-1)
+template <int ID, int NT>
+__device__ __forceinline__ void group_bar() {
+    asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(NT) : "memory");
+}
+
+// block reductions over a thread GROUP of NT threads (ids 0..NT-1), synchronised with named barrier ID
+template <int ID, int NT>
+__device__ __forceinline__ float group_sum(float v, float* scratch) {
+    v = warp_sum(v);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    group_bar<ID, NT>();
+    if (l == 0) scratch[w] = v;
+    group_bar<ID, NT>();
+    float t = (l < NT / 32) ? scratch[l] : 0.f;
+    return warp_sum(t);
+}
+template <int ID, int NT>
+__device__ __forceinline__ float group_max(float v, float* scratch) {
+    v = warp_max(v);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    group_bar<ID, NT>();
+    if (l == 0) scratch[w] = v;
+    group_bar<ID, NT>();
+    float t = (l < NT / 32) ? scratch[l] : 0.f;   // non-negative values
+    return warp_max(t);
+}
+template <int ID, int NT>
+__device__ __forceinline__ int group_sum_i(int v, int* scratch) {
+    v = warp_sum_i(v);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    group_bar<ID, NT>();
+    if (l == 0) scratch[w] = v;
+    group_bar<ID, NT>();
+    int t = (l < NT / 32) ? scratch[l] : 0;
+    return warp_sum_i(t);
+}
+
+// One activation row through the glue: source -> (residual / relu^2*up) -> RMSNorm -> per-token int8.
+// Executed by the NT-thread group (thread ids 0..NT-1).  ys: K bf16 of scratch (shared); qdst: K int8
+// (shared or global, 8-byte aligned); fs/is: >= 32 floats / ints of shared scratch.
+// Returns the activation scale and Sigma q through the references (identical in every thread).
+template <int ID, int NT>
+__device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat16* ys, int8_t* qdst, float* fs, int* is,
+                                         bool write_side, float& scale_ret, int& rowsum_ret) {
+    const int K = p.K;
+    const int tid = threadIdx.x;
+    float ss = 0.f;
+    // ---- pass 1: x (bf16) -> ys, sum of squares
+    if (p.mode == GL_EMBED || p.mode == GL_PLAIN) {
+        const __nv_bfloat16* row = (p.mode == GL_EMBED) ? p.embed + (size_t)p.tokens[m] * K : p.src + (size_t)m * K;
+        for (int k = tid * 8; k < K; k += NT * 8) {
+            const uint4 t = ldcg_u4(row + k);
+            *reinterpret_cast<uint4*>(ys + k) = t;
+            if (write_side && p.hid_out && p.mode == GL_EMBED) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = t;
+            const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { const float a = bf16lo(w[i]), b = bf16hi(w[i]); ss += a * a + b * b; }
+        }
+    } else if (p.mode == GL_RESID) {
+        const int rs = p.acc_rowsum[m];
+        const float sa = p.acc_ascale[m], ws = p.acc_wscale[0];
+        const float* arow = p.acc + (size_t)m * p.acc_ld;
+        const __nv_bfloat16* hrow = p.hid_in + (size_t)m * K;
+        for (int k = tid * 8; k < K; k += NT * 8) {
+            const uint4 t = ldcg_u4(hrow + k);
+            const float4 a0 = ldcg_f4(arow + k), a1 = ldcg_f4(arow + k + 4);
+            const float S[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const uint32_t hw[4] = {t.x, t.y, t.z, t.w};
+            uint32_t o[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                // hidden + proj, both bf16 tensors: one rounding of the projection, one of the sum
+                const float x0 = bf16_round(bf16lo(hw[i]) + bf16_round(lin_value(S[2 * i], rs, ws, sa)));
+                const float x1 = bf16_round(bf16hi(hw[i]) + bf16_round(lin_value(S[2 * i + 1], rs, ws, sa)));
+                ss += x0 * x0 + x1 * x1;
+                o[i] = pack_bf16x2(x0, x1);
+            }
+            const uint4 ov = make_uint4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<uint4*>(ys + k) = ov;
+            if (write_side && p.hid_out) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = ov;
+        }
+    } else {  // GL_RELU2
+        const int rs = p.acc_rowsum[m];
+        const float sa = p.acc_ascale[m], wg = p.acc_wscale[0], wu = p.acc_wscale[1];
+        const float* arow = p.acc + (size_t)m * p.acc_ld;
+        for (int k = tid * 8; k < K; k += NT * 8) {
+            const int ng = (k >> 4) * 32 + (k & 15);   // gate rows of this 8-group; up rows at +16
+            const float4 g0 = ldcg_f4(arow + ng), g1 = ldcg_f4(arow + ng + 4);
+            const float4 u0 = ldcg_f4(arow + ng + 16), u1 = ldcg_f4(arow + ng + 20);
+            const float G[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+            const float U[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+            float x[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float g = bf16_round(lin_value(G[i], rs, wg, sa));
+                const float u = bf16_round(lin_value(U[i], rs, wu, sa));
+                const float r = fmaxf(g, 0.f);
+                x[i] = bf16_round(bf16_round(r * r) * u);
+                ss += x[i] * x[i];
+            }
+            *reinterpret_cast<uint4*>(ys + k) =
+                make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
+        }
+    }
+    ss = group_sum<ID, NT>(ss, fs);
+    const float var = ss / (float)K;
+    const float r = bf16_round(1.0f / sqrtf(var + p.eps));
+    // ---- pass 2: y = bf16(bf16(x*r)*gamma) in place, absmax
+    float amax = 0.f;
+    for (int k = tid * 8; k < K; k += NT * 8) {
+        const uint4 t = *reinterpret_cast<const uint4*>(ys + k);
+        const uint4 gq = *reinterpret_cast<const uint4*>(p.gamma + k);
+        const uint32_t xw[4] = {t.x, t.y, t.z, t.w}, gw[4] = {gq.x, gq.y, gq.z, gq.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float y0 = bf16_round(bf16_round(bf16lo(xw[i]) * r) * bf16lo(gw[i]));
+            const float y1 = bf16_round(bf16_round(bf16hi(xw[i]) * r) * bf16hi(gw[i]));
+            amax = fmaxf(amax, fmaxf(fabsf(y0), fabsf(y1)));
+            o[i] = pack_bf16x2(y0, y1);
+        }
+        const uint4 ov = make_uint4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<uint4*>(ys + k) = ov;
+        if (write_side && p.y_out) *reinterpret_cast<uint4*>(p.y_out + (size_t)m * K + k) = ov;
+    }
+    amax = group_max<ID, NT>(amax, fs);
+    const float scale = act_scale_from_absmax(amax);
+    // ---- pass 3: int8 codes (each thread re-reads exactly what it wrote)
+    int psum = 0;
+    for (int k = tid * 8; k < K; k += NT * 8) {
+        const uint4 t = *reinterpret_cast<const uint4*>(ys + k);
+        const uint32_t yw[4] = {t.x, t.y, t.z, t.w};
+        uint32_t w0 = 0, w1 = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int q0 = quant_i8(bf16lo(yw[i]), scale), q1 = quant_i8(bf16hi(yw[i]), scale);
+            psum += q0 + q1;
+            const uint32_t pr = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8);
+            if (i < 2) w0 |= pr << (16 * i); else w1 |= pr << (16 * (i - 2));
+        }
+        *reinterpret_cast<uint2*>(qdst + k) = make_uint2(w0, w1);
+    }
+    const int total = group_sum_i<ID, NT>(psum, is);
+    scale_ret = scale;
+    rowsum_ret = total;
+}
+
+// grid-strided clearing of the accumulators a phase is responsible for (by the NT-thread group of every CTA)
+template <int NT>
+__device__ __forceinline__ void glue_zero_duty(const GlueParams& p) {
+    const int gtid = blockIdx.x * NT + threadIdx.x, gstride = gridDim.x * NT;
+    if (p.zero0)
+        for (int i = gtid * 4; i < p.zero0_n; i += gstride * 4) *reinterpret_cast<float4*>(p.zero0 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.zero1)
+        for (int i = gtid * 4; i < p.zero1_n; i += gstride * 4) *reinterpret_cast<float4*>(p.zero1 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// launchers (host)
+struct SmallLinArgs {
+    GlueParams g;
+    const uint8_t* w;        // b200_tile_v1
+    int N, K;
+    float* acc_out;          // fp32 [M][acc_ld], zero on entry
+    int acc_ld;
+    float* lin_ascale;       // [M] out: activation scale of THIS linear's input
+    int32_t* lin_rowsum;     // [M] out: Sigma a
+};
+int launch_linear_small(const SmallLinArgs& a, cudaStream_t s, bool pdl);
+bool linear_small_fits(int M, int K);
+int launch_glue_rows(const GlueParams& g, cudaStream_t s, bool pdl);
+struct OneshotArgs {
+    const uint8_t* w;
+    int N, K;
+    const int8_t* q;         // [M][K]
+    int M;
+    float* acc_out;
+    int acc_ld;
+};
+int launch_gemm_oneshot(const OneshotArgs& a, cudaStream_t s, bool pdl);
+void fused_init_attrs();
+struct FusedAttnArgs {
+    void* pool;
+    int layers, layer, Hkv, page_size;
+    const int32_t* block_table;
+    int max_blocks;
+    const int32_t* seq_lens;
+    const int32_t* positions;
+    int B, H;
+    float scale;
+    void* out;                 // bf16 [B][H][128]
+    const float* qkv_acc;
+    int qkv_ld;
+    const int32_t* qkv_rowsum;
+    const float* qkv_ascale;
+    const float* qkv_wscale;   // device [3]
+    const void *cos_tab, *sin_tab;
+    int max_pos;
+    int* merge_cnt;            // [B][Hkv], zero
+    float* zero0;
+    int zero0_n;
+    int max_seq_hint;
+    void* ws;
+    size_t ws_bytes;
+};
+int attn_decode_fused(const FusedAttnArgs& a, cudaStream_t s, bool pdl);
+
+}  // namespace wf

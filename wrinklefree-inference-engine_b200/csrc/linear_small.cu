@@ -1,0 +1,246 @@
+// Small-batch (M <= 8) decode linear: ONE launch = glue prologue + bandwidth-bound ternary GEMV.
+//
+//   prologue : x -> (residual | relu^2*up) -> RMSNorm -> per-token int8   (fused_common.cuh, every CTA redundantly:
+//              M*K <= 8*28672 elements, cheaper than a launch + a trip through HBM)
+//   main     : S[m,n] += sum_k code[n,k] * a[m,k] over this CTA's contiguous slab of b200_tile_v1 tiles
+//              (reference row dot: extern/BitNet/src/ggml-bitnet-mad.cpp:94-186)
+//   epilogue : exact fp32 RED of the partial sums into the global accumulator; the NEXT phase dequantises.
+//
+// B200 mapping:
+//   * persistent grid, one CTA per SM, the T tiles of the matrix split evenly (split-K falls out of it);
+//   * a dedicated producer warp streams the slab with the TMA engine (cp.async.bulk 1-D, 8 KB stages,
+//     mbarrier full/empty ring).  The slab does not depend on the previous kernel, so the producer never
+//     executes griddepcontrol.wait, and every CTA signals griddepcontrol.launch_dependents FIRST: under
+//     programmatic dependent launch the NEXT linear's CTAs become co-resident and fill their rings while this
+//     one is still computing — the weight stream runs ahead of the layer's dependency chain;
+//   * 8 consumer warps: 16-byte LDS of a tile = the four A-fragment source words; 2-bit -> u8 is one AND per
+//     fragment (fields stay at their bit position, four int32 accumulator sets are shifted back at flush);
+//     int8 activations via ldmatrix from a skewed smem copy; mma.sync.m16n8k32.u8.s8.
+#include "fused_common.cuh"
+
+namespace wf {
+
+constexpr int LS_STAGE_TILES = 16;                        // 8 KB per stage
+constexpr int LS_STAGE_BYTES = LS_STAGE_TILES * WF_TILE_BYTES;
+constexpr int LS_STAGES = 8;                              // 64 KB ring
+constexpr int LS_CW = 8;                                  // consumer warps
+constexpr int LS_CT = LS_CW * 32;                         // consumer threads
+constexpr int LS_THREADS = LS_CT + 32;
+
+struct SmallLinParams {
+    GlueParams g;
+    const uint8_t* w;
+    int N, K, KB;
+    long long T;
+    int act_stride;       // bytes per activation row in smem (K + 16: 16-B skew => conflict-free ldmatrix)
+    int sacc_rbs;         // row-blocks of smem accumulators
+    float* acc_out;
+    int acc_ld;
+    float* lin_ascale;
+    int32_t* lin_rowsum;
+};
+
+__global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const SmallLinParams p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char* ring = smem;                                         // LS_STAGES * LS_STAGE_BYTES
+    unsigned char* acts = ring + LS_STAGES * LS_STAGE_BYTES;            // M * act_stride
+    __nv_bfloat16* ys = reinterpret_cast<__nv_bfloat16*>(acts + ((p.g.M * p.act_stride + 127) & ~127));   // K bf16
+    int* sacc = reinterpret_cast<int*>(reinterpret_cast<unsigned char*>(ys) + ((p.K * 2 + 127) & ~127));   // [rbl][8][16]
+    __shared__ __align__(8) uint64_t full_bar[LS_STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[LS_STAGES];
+    __shared__ float fs[32];
+    __shared__ int is[32];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int M = p.g.M;
+    const long long t0 = (long long)blockIdx.x * p.T / gridDim.x;
+    const long long t1 = (long long)(blockIdx.x + 1) * p.T / gridDim.x;
+    const int ntiles = (int)(t1 - t0);
+    const int nstages = (ntiles + LS_STAGE_TILES - 1) / LS_STAGE_TILES;
+    const int rb_first = (int)(t0 / p.KB);
+
+    pdl_launch_dependents();   // let the next phase's CTAs in: their weight stream overlaps this phase
+    if (tid == 0) {
+        for (int s = 0; s < LS_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], LS_CW);
+        }
+        fence_mbar_init();
+    }
+    for (int i = tid; i < p.sacc_rbs * 128; i += LS_THREADS) sacc[i] = 0;
+    __syncthreads();
+
+    if (warp == LS_CW) {
+        // ------------------------------------------------ producer warp (one elected lane); never waits on the prior grid
+        if (lane == 0) {
+            for (int it = 0; it < nstages; ++it) {
+                const int s = it % LS_STAGES;
+                mbar_wait(&empty_bar[s], ((it / LS_STAGES) & 1) ^ 1);
+                const int tiles = min(LS_STAGE_TILES, ntiles - it * LS_STAGE_TILES);
+                const uint32_t bytes = (uint32_t)tiles * WF_TILE_BYTES;
+                mbar_expect_tx(&full_bar[s], bytes);
+                bulk_g2s(ring + s * LS_STAGE_BYTES, p.w + (size_t)(t0 + (long long)it * LS_STAGE_TILES) * WF_TILE_BYTES, bytes,
+                         &full_bar[s]);
+            }
+        }
+    } else {
+        // ------------------------------------------------ consumer warps
+        pdl_wait_prior();          // everything below reads what the previous phase wrote
+        glue_zero_duty<LS_CT>(p.g);
+        for (int m = 0; m < M; ++m) {
+            float sc; int rsum;
+            glue_row<1, LS_CT>(p.g, m, ys, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, blockIdx.x == 0, sc, rsum);
+            if (blockIdx.x == 0 && tid == 0) { p.lin_ascale[m] = sc; p.lin_rowsum[m] = rsum; }
+        }
+        group_bar<1, LS_CT>();     // activations complete
+
+        int acc[4][4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[g][j] = 0;
+        int cur_rb = -1;
+        const int arow = min(lane & 7, M - 1);
+        const unsigned char* abase = acts + arow * p.act_stride + (lane >> 3) * 16;
+
+        auto flush = [&](int rb) {
+            if (rb < 0) return;
+            const int g = lane >> 2, t = lane & 3;
+            int v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                v[j] = (acc[0][j] >> 6) + (acc[1][j] >> 4) + (acc[2][j] >> 2) + acc[3][j];
+#pragma unroll
+                for (int gg = 0; gg < 4; ++gg) acc[gg][j] = 0;
+            }
+            int* dst = sacc + (rb - rb_first) * 128;
+            const int m = 2 * t;
+            if (m < M) {
+                if (v[0]) atomicAdd(dst + m * 16 + g, v[0]);
+                if (v[2]) atomicAdd(dst + m * 16 + g + 8, v[2]);
+            }
+            if (m + 1 < M) {
+                if (v[1]) atomicAdd(dst + (m + 1) * 16 + g, v[1]);
+                if (v[3]) atomicAdd(dst + (m + 1) * 16 + g + 8, v[3]);
+            }
+        };
+
+        for (int it = 0; it < nstages; ++it) {
+            const int s = it % LS_STAGES;
+            mbar_wait(&full_bar[s], (it / LS_STAGES) & 1);
+            const int tiles = min(LS_STAGE_TILES, ntiles - it * LS_STAGE_TILES);
+            for (int tl = warp; tl < tiles; tl += LS_CW) {
+                const long long tg = t0 + (long long)it * LS_STAGE_TILES + tl;
+                const int rb = (int)(tg / p.KB), kb = (int)(tg - (long long)rb * p.KB);
+                if (rb != cur_rb) { flush(cur_rb); cur_rb = rb; }
+                const uint4 Wv = *reinterpret_cast<const uint4*>(ring + s * LS_STAGE_BYTES + tl * WF_TILE_BYTES + lane * 16);
+                uint32_t b[8];
+                const unsigned char* ap = abase + kb * 128;
+                ldmatrix_x4(b[0], b[1], b[2], b[3], ap);
+                ldmatrix_x4(b[4], b[5], b[6], b[7], ap + 64);
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const uint32_t mask = 0x03030303u << (6 - 2 * g);   // k-group g sits in bits (7-2g .. 6-2g)
+                    mma_u8s8_16832(acc[g], Wv.x & mask, Wv.y & mask, Wv.z & mask, Wv.w & mask, b[2 * g], b[2 * g + 1]);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[s]);
+        }
+        flush(cur_rb);
+        group_bar<1, LS_CT>();
+        // ------------------------------------------------ exact fp32 RED of this CTA's partial sums
+        if (ntiles > 0) {
+            const int rb_last = (int)((t1 - 1) / p.KB);
+            const int n_rbs = rb_last - rb_first + 1;
+            for (int i = tid; i < n_rbs * 128; i += LS_CT) {
+                const int rbl = i >> 7, m = (i >> 4) & 7, r = i & 15;
+                const int n = (rb_first + rbl) * 16 + r;
+                const int v = sacc[i];
+                if (m < M && n < p.N && v) red_add_f32(p.acc_out + (size_t)m * p.acc_ld + n, (float)v);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Standalone glue for large batch: grid = M rows, 256 threads; int8 codes / scale / rowsum go to global.
+constexpr int GR_T = 256;
+__global__ void __launch_bounds__(GR_T) glue_rows_kernel(const GlueParams p) {
+    extern __shared__ __align__(16) unsigned char gsm[];
+    __nv_bfloat16* ys = reinterpret_cast<__nv_bfloat16*>(gsm);
+    __shared__ float fs[32];
+    __shared__ int is[32];
+    pdl_launch_dependents();
+    pdl_wait_prior();
+    glue_zero_duty<GR_T>(p);
+    const int m = blockIdx.x;
+    float sc; int rsum;
+    glue_row<1, GR_T>(p, m, ys, p.q_out + (size_t)m * p.K, fs, is, true, sc, rsum);
+    if (threadIdx.x == 0) {
+        if (p.scale_out) p.scale_out[m] = sc;
+        if (p.rowsum_out) p.rowsum_out[m] = rsum;
+    }
+}
+
+static void set_pdl(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* at, bool pdl) {
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+}
+
+bool linear_small_fits(int M, int K) {
+    if (M < 1 || M > 8) return false;
+    const size_t smem = (size_t)LS_STAGES * LS_STAGE_BYTES + (((size_t)M * (K + 16) + 127) & ~(size_t)127) + (((size_t)K * 2 + 127) & ~(size_t)127) + 16 * 1024;
+    return smem <= 220 * 1024;
+}
+
+int launch_linear_small(const SmallLinArgs& a, cudaStream_t s, bool pdl) {
+    if (a.g.M < 1 || a.g.M > 8) { set_error("linear_small: M=%d outside 1..8", a.g.M); return WF_ERR_UNSUPPORTED; }
+    if (a.K % WF_QK || a.g.K != a.K) { set_error("linear_small: bad K"); return WF_ERR_INVALID; }
+    SmallLinParams p;
+    p.g = a.g;
+    p.w = a.w; p.N = a.N; p.K = a.K; p.KB = a.K / WF_QK;
+    const int RB = (a.N + 15) / 16;
+    p.T = (long long)p.KB * RB;
+    p.act_stride = a.K + 16;
+    p.acc_out = a.acc_out; p.acc_ld = a.acc_ld;
+    p.lin_ascale = a.lin_ascale; p.lin_rowsum = a.lin_rowsum;
+    int grid = sm_count();
+    const long long min_tiles = 4;
+    if (p.T / min_tiles < grid) grid = (int)((p.T + min_tiles - 1) / min_tiles);
+    if (grid < 1) grid = 1;
+    const long long max_tiles = (p.T + grid - 1) / grid + 1;
+    p.sacc_rbs = (int)(max_tiles / p.KB) + 3;
+    const size_t smem = (size_t)LS_STAGES * LS_STAGE_BYTES + (((size_t)a.g.M * p.act_stride + 127) & ~(size_t)127) +
+                        (((size_t)a.K * 2 + 127) & ~(size_t)127) + (size_t)p.sacc_rbs * 512;
+    if (smem > 220 * 1024) { set_error("linear_small: M*K=%d*%d does not fit in shared memory", a.g.M, a.K); return WF_ERR_UNSUPPORTED; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(LS_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    set_pdl(cfg, at, pdl);
+    return launch_check(cudaLaunchKernelEx(&cfg, linear_small_kernel, p), "linear_small");
+}
+
+int launch_glue_rows(const GlueParams& g, cudaStream_t s, bool pdl) {
+    if (g.M < 1 || g.K % 8) { set_error("glue_rows: bad shape"); return WF_ERR_INVALID; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(g.M);
+    cfg.blockDim = dim3(GR_T);
+    cfg.dynamicSmemBytes = (size_t)g.K * 2;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    set_pdl(cfg, at, pdl);
+    return launch_check(cudaLaunchKernelEx(&cfg, glue_rows_kernel, g), "glue_rows");
+}
+
+void linear_small_init_attrs() {
+    cudaFuncSetAttribute(linear_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(glue_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+}
+
+}  // namespace wf
