@@ -1,0 +1,75 @@
+#!/usr/bin/env python
+"""BASELINE config 3: BitNet-2B-4T-shaped prefill, 8 x 2048 tokens (M = 16384) through the ternary linears of one
+layer on the tcgen05 int8 path.  Prints one JSON line: int8 TOP/s per linear and per layer, next to the int8
+tensor-pipe peak measured on the same box with torch._int_mm (cuBLASLt) at 8192^3."""
+import argparse
+import json
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+for p in (str(ROOT), str(ROOT / "wrinklefree-inference-engine_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch  # noqa: E402
+
+
+def timed(fn, iters, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    e1.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--tokens", type=int, default=16384)
+    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--algo", type=int, default=3)
+    ap.add_argument("--shape", default="2b", choices=["2b", "8b"])
+    args = ap.parse_args()
+    from wf_bitnet import _lib, ops
+    _lib.require_gpu()
+    torch.cuda.set_device(0)
+    M = args.tokens
+    hid, ffn, qkv = (2560, 6912, 3840) if args.shape == "2b" else (4096, 14336, 6144)
+    shapes = {"qkv": (qkv, hid), "o": (hid, hid), "gate_up": (2 * ffn, hid), "down": (hid, ffn)}
+    g = torch.Generator(device="cuda").manual_seed(0)
+    out = {"tokens": M, "shape": args.shape, "algo": args.algo}
+    total_ms, total_ops = 0.0, 0.0
+    for name, (n, k) in shapes.items():
+        tile = torch.randint(0, 256, (ops.tile_bytes(n, k),), generator=g, device="cuda", dtype=torch.uint8)
+        q = torch.randint(-127, 128, (M, k), generator=g, device="cuda", dtype=torch.int8)
+        rs = q.sum(1, dtype=torch.int32)
+        sc = torch.rand(M, generator=g, device="cuda") * 0.05 + 0.01
+        ws = torch.tensor([1.7], device="cuda")
+        fn = lambda: ops.ternary_linear(tile, n, k, q, mode="linear", rowsum=rs, act_scale=sc, w_scale=ws, out_dtype=torch.bfloat16, algo=args.algo)  # noqa: E731
+        ms = timed(fn, args.iters)
+        opsn = 2.0 * M * n * k
+        out[name] = {"N": n, "K": k, "ms": round(ms, 4), "TOPs": round(opsn / ms / 1e9, 1)}
+        total_ms += ms
+        total_ops += opsn
+    out["layer_ms"] = round(total_ms, 4)
+    out["layer_TOPs"] = round(total_ops / total_ms / 1e9, 1)
+    out["prefill_30_layers_ms"] = round(30 * total_ms, 2)
+    out["prefill_tok_s_linears_only"] = round(M / (30 * total_ms * 1e-3), 0)
+    a = torch.randint(-127, 128, (8192, 8192), device="cuda", dtype=torch.int8)
+    b = torch.randint(-127, 128, (8192, 8192), device="cuda", dtype=torch.int8).t()
+    try:
+        ms = timed(lambda: torch._int_mm(a, b), 10)
+        out["int8_peak_TOPs_cublaslt_8192"] = round(2 * 8192.0 ** 3 / ms / 1e9, 1)
+        out["frac_of_int8_peak"] = round(out["layer_TOPs"] / out["int8_peak_TOPs_cublaslt_8192"], 4)
+    except Exception as ex:  # noqa: BLE001
+        out["int8_peak_error"] = str(ex)[:200]
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

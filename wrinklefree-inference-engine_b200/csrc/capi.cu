@@ -118,7 +118,7 @@ extern "C" int wf_ternary_linear(const wf_linear_args* a, void* stream) {
     int algo = a->algo;
     if (algo == 0) {
         if (a->M <= 8 && a->w_layout == WF_W_TILE && a->workspace) algo = 1;
-        else if (a->M >= 128 && a->w_layout == WF_W_TILE) algo = 3;
+        else if (a->M >= 128) algo = 3;   // a real dense contraction: tcgen05 int8
         else algo = 2;
     }
     switch (algo) {

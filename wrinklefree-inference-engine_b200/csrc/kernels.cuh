@@ -24,5 +24,6 @@ void gemv_stream_init_attrs();
 void attn_init_attrs();
 void lm_init_attrs();
 void quant_init_attrs();
-inline void init_all_kernel_attrs() { gemm_mma_init_attrs(); gemv_stream_init_attrs(); attn_init_attrs(); lm_init_attrs(); quant_init_attrs(); }
+void gemm_tc_init_attrs();
+inline void init_all_kernel_attrs() { gemm_mma_init_attrs(); gemv_stream_init_attrs(); attn_init_attrs(); lm_init_attrs(); quant_init_attrs(); gemm_tc_init_attrs(); }
 }
