@@ -34,6 +34,8 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--algo", type=int, default=3)
     ap.add_argument("--shape", default="2b", choices=["2b", "8b"])
+    ap.add_argument("--only", default="", help="time just this linear (qkv|o|gate_up|down)")
+    ap.add_argument("--layout", default="tile", choices=["tile", "i2s"])
     args = ap.parse_args()
     from wf_bitnet import _lib, ops
     _lib.require_gpu()
@@ -45,12 +47,16 @@ def main():
     out = {"tokens": M, "shape": args.shape, "algo": args.algo}
     total_ms, total_ops = 0.0, 0.0
     for name, (n, k) in shapes.items():
+        if args.only and name != args.only:
+            continue
         tile = torch.randint(0, 256, (ops.tile_bytes(n, k),), generator=g, device="cuda", dtype=torch.uint8)
+        if args.layout == "i2s":
+            tile = tile[: n * k // 4].reshape(n, k // 4).contiguous()
         q = torch.randint(-127, 128, (M, k), generator=g, device="cuda", dtype=torch.int8)
         rs = q.sum(1, dtype=torch.int32)
         sc = torch.rand(M, generator=g, device="cuda") * 0.05 + 0.01
         ws = torch.tensor([1.7], device="cuda")
-        fn = lambda: ops.ternary_linear(tile, n, k, q, mode="linear", rowsum=rs, act_scale=sc, w_scale=ws, out_dtype=torch.bfloat16, algo=args.algo)  # noqa: E731
+        fn = lambda: ops.ternary_linear(tile, n, k, q, mode="linear", rowsum=rs, act_scale=sc, w_scale=ws, out_dtype=torch.bfloat16, algo=args.algo, layout=args.layout)  # noqa: E731
         ms = timed(fn, args.iters)
         opsn = 2.0 * M * n * k
         out[name] = {"N": n, "K": k, "ms": round(ms, 4), "TOPs": round(opsn / ms / 1e9, 1)}
@@ -60,6 +66,9 @@ def main():
     out["layer_TOPs"] = round(total_ops / total_ms / 1e9, 1)
     out["prefill_30_layers_ms"] = round(30 * total_ms, 2)
     out["prefill_tok_s_linears_only"] = round(M / (30 * total_ms * 1e-3), 0)
+    if args.only:
+        print(json.dumps(out))
+        return
     a = torch.randint(-127, 128, (8192, 8192), device="cuda", dtype=torch.int8)
     b = torch.randint(-127, 128, (8192, 8192), device="cuda", dtype=torch.int8).t()
     try:

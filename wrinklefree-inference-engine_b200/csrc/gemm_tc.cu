@@ -5,23 +5,27 @@
 //    signature src/wrinklefree_inference/kernels/bitnet_patch.py:73).  Used where the shape is a real dense
 //   contraction (M >= 128 tokens: prefill, 8 x 2048 tokens => 6.8e13 int8 MACs for the 2B shape).
 //
-// B200 mapping (one persistent CTA per SM, 10 warps, warp-specialised):
+// B200 mapping (one persistent CTA per SM, 4 + 4*NU + 2 warps, warp-specialised):
 //   * D tile = 128 weight rows (UMMA M = TMEM lanes) x 128 tokens (UMMA N), int32, double-buffered in TMEM
 //     (2 x 128 columns) so the epilogue of tile i overlaps the main loop of tile i+1;
-//   * the WEIGHT operand never touches shared memory: four "unpack" warps (one per TMEM lane quarter) read
-//     their row's 32 packed bytes per 128-k block straight from global/L2 into registers (prefetched 4 blocks
+//   * the WEIGHT operand never touches shared memory: NU groups of four "unpack" warps (one per TMEM lane quarter)
+//     read their row's 32 packed bytes per 128-k block straight from global/L2 into registers (prefetched 4 blocks
 //     ahead), expand 2-bit -> u8 with shift+mask and write the 128 codes into a TMEM operand ring
 //     (tcgen05.st 32x32b.x32, 8 stages x 32 columns).  tcgen05.mma reads A from TMEM ("TS" form), so shared
-//     memory only carries the activation operand: 64 B/clk/SM at the int8 peak instead of >128 B/clk for an
-//     SS kernel that would also have to write the unpacked weights through shared memory;
+//     memory only carries the activation operand (16 KB written by TMA + 16 KB read by the MMAs per stage);
 //   * int8 activations [M,K] are the B operand: TMA (cp.async.bulk.tensor.2d, 128-byte swizzle) into an
 //     8-stage x 16 KB ring; one mbarrier per stage collects the TMA transaction bytes AND the four unpack
 //     warps' arrivals, one tcgen05.commit per stage releases both halves;
 //   * one elected thread issues 4 x tcgen05.mma.cta_group::1.kind::i8 (M128 N128 K32) per stage;
-//   * epilogue warps: tcgen05.ld 32x32b.x32 (lane = weight row, columns = tokens) -> the shared linear
-//     epilogue (Sigma-a correction, scales, residual, relu^2*up) -> stores that are coalesced along n.
+//   * epilogue warps: tcgen05.ld 32x32b.x32 (lane = weight row, columns = tokens) -> per-warp smem transpose ->
+//     the linear epilogue (Sigma-a correction, scales, residual, relu^2*up) on 8 consecutive n -> 16-byte stores.
+// Measured (r01, profiles/): 1.58 PTOP/s on the 2B layer at M = 16384 = 54 % of cuBLASLt int8 on the same box;
+// the stage rate sits at the 256-clk tensor floor, what is left is shared-memory bandwidth (TMA write + MMA read =
+// 128 B/clk at the floor, so the epilogue's transpose traffic serialises) — the cta_group::2 form (each SM holds
+// half of the activation tile) is the next step.
 #include "linear_common.cuh"
 #include <cuda.h>
+#include <stdlib.h>
 
 namespace wf {
 
@@ -34,14 +38,16 @@ constexpr int TC_A_COLS = TC_BK / 4;               // TMEM columns per weight st
 constexpr int TC_A_COL0 = 2 * TC_BN;               // weight ring starts after the two accumulator buffers
 constexpr int TC_TMEM_COLS = 512;
 constexpr int TC_PF = 4;                           // weight prefetch distance (stages, in registers)
-constexpr int TC_THREADS = 320;                    // warps 0-3 epilogue, 4-7 unpack, 8 TMA, 9 MMA
-constexpr int TC_SMEM = TC_STAGES * TC_STAGE_BYTES + 1024;
+constexpr int TC_MAX_THREADS = 576;                // warps 0-3 epilogue, 4..4+4*NU-1 unpack (NU groups of 4), then TMA, MMA
+constexpr int TC_EP_STRIDE = 32 * 4 + 16;             // bytes per token row of an epilogue transpose patch (padded: conflict-free)
+constexpr int TC_SMEM = TC_STAGES * TC_STAGE_BYTES + 4 * 32 * TC_EP_STRIDE + 1024;
 
 struct TcParams {
     const uint8_t* w;
     int w_layout;
     int M, N, K, KB;
     int tiles_n, tiles_m;
+    int dbg;   // timing experiments only (WF_TC_DBG): 1 = epilogue skips math/stores, 2 = also skips the TMEM loads
     EpiParams ep;
 };
 
@@ -96,7 +102,14 @@ constexpr uint32_t tc_idesc(int m, int n) {
                    "=r"(v[30]), "=r"(v[31])                                                                             \
                  : "r"(taddr) : "memory")
 
-__global__ void __launch_bounds__(TC_THREADS, 1) ternary_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const TcParams p) {
+// CL = thread-block-cluster size: the CL CTAs of a cluster work on the SAME 128 tokens and CL consecutive 128-row
+// weight tiles; each CTA TMA-loads 128/CL tokens of the activation stage and multicasts them to all CL CTAs, so the
+// L2 -> SM activation traffic (the limiter of this kernel: ~6300 B/clk chip-wide) drops by CL.
+// NU = unpack warp groups (4 warps each, one per TMEM lane quarter); group g expands the stages with item % NU == g.
+// One warp issues ~190 instructions per stage at IPC ~0.3, so a single group paces the kernel at ~850 clk per stage
+// (measured) against the 256-clk tensor floor; three groups bring the unpack under the floor.
+template <int CL, int NU>
+__global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const TcParams p) {
     extern __shared__ unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[TC_STAGES];    // TMA bytes + 4 unpack-warp arrivals
     __shared__ __align__(8) uint64_t empty_bar[TC_STAGES];   // tcgen05.commit: MMAs of the stage retired
@@ -106,155 +119,327 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ternary_gemm_tc_kernel(const __
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;   // 128B-swizzle atoms need 1024-B alignment
-    const int total_tiles = p.tiles_n * p.tiles_m;
-    const int my_tiles = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-    const long long n_items = (long long)my_tiles * p.KB;
+    const int crank = (CL > 1) ? (int)(blockIdx.x % CL) : 0;          // 1-D cluster: rank == blockIdx.x % CL
+    const int cluster_id = blockIdx.x / CL, n_clusters = gridDim.x / CL;
+    const int ngroups = (p.tiles_n + CL - 1) / CL;                    // groups of CL weight-row tiles
+    const int total_tiles = ngroups * p.tiles_m;                      // cluster tiles
+    const int my_tiles = (total_tiles - cluster_id + n_clusters - 1) / n_clusters;
+    const int n_items = my_tiles * p.KB;
+    auto tile_coords = [&](int tl, int& m_blk, int& n_blk) {
+        const int ct = cluster_id + tl * n_clusters;
+        m_blk = ct / ngroups;
+        n_blk = (ct - m_blk * ngroups) * CL + crank;                  // may be >= tiles_n (padding tile: epilogue masks it)
+    };
 
     if (tid == 0) {
-        for (int s = 0; s < TC_STAGES; ++s) { mbar_init(&full_bar[s], 5); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < TC_STAGES; ++s) { mbar_init(&full_bar[s], 5); mbar_init(&empty_bar[s], CL); }
         for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
         fence_mbar_init();
     }
-    if (warp == 9) {
+    constexpr int W_TMA = 4 + 4 * NU, W_MMA = W_TMA + 1;
+    if (warp == W_MMA) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(TC_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
+    if (CL > 1) {   // peers must see initialised barriers before the first multicast / remote commit
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
 
-    if (warp == 8) {
+    if (warp == W_TMA) {
         // ------------------------------------------------------------ TMA producer: int8 activations
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_q) : "memory");
-            long long it = 0;
+            int it = 0;
+            constexpr int SLICE = TC_BN / CL;   // tokens this CTA fetches for the whole cluster
             for (int tl = 0; tl < my_tiles; ++tl) {
-                const int tile = blockIdx.x + tl * gridDim.x;
-                const int m_blk = tile / p.tiles_n;
+                int m_blk, n_blk;
+                tile_coords(tl, m_blk, n_blk);
                 for (int kb = 0; kb < p.KB; ++kb, ++it) {
-                    const int s = (int)(it % TC_STAGES);
-                    mbar_wait(&empty_bar[s], (uint32_t)(((it / TC_STAGES) & 1) ^ 1));
-                    mbar_expect_tx(&full_bar[s], TC_STAGE_BYTES);
-                    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                                 ::"r"(ring + s * TC_STAGE_BYTES), "l"(&tmap_q), "r"(kb * TC_BK), "r"(m_blk * TC_BN), "r"(smem_u32(&full_bar[s])) : "memory");
+                    const int s = it % TC_STAGES;
+                    mbar_wait(&empty_bar[s], (uint32_t)(((it / TC_STAGES) & 1) ^ 1));   // all CL CTAs retired this slot
+                    mbar_expect_tx(&full_bar[s], TC_STAGE_BYTES);                        // own barrier: all CL slices land here
+                    const uint32_t dst = ring + s * TC_STAGE_BYTES + crank * SLICE * TC_BK;
+                    if (CL == 1)
+                        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                                     ::"r"(dst), "l"(&tmap_q), "r"(kb * TC_BK), "r"(m_blk * TC_BN), "r"(smem_u32(&full_bar[s])) : "memory");
+                    else
+                        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%2, %3}], [%4], %5;"
+                                     ::"r"(dst), "l"(&tmap_q), "r"(kb * TC_BK), "r"(m_blk * TC_BN + crank * SLICE), "r"(smem_u32(&full_bar[s])),
+                                       "h"((uint16_t)((1u << CL) - 1)) : "memory");
                 }
             }
         }
-    } else if (warp == 9) {
-        // ------------------------------------------------------------ MMA issuer (one thread)
-        if (lane == 0) {
-            constexpr uint32_t idesc = tc_idesc(TC_BM, TC_BN);
-            long long it = 0;
-            for (int tl = 0; tl < my_tiles; ++tl) {
-                const int buf = tl & 1;
-                mbar_wait(&tempty_bar[buf], (uint32_t)(((tl >> 1) & 1) ^ 1));
-                tc_fence_after();
-                const uint32_t d_tmem = tmem + buf * TC_BN;
-                for (int kb = 0; kb < p.KB; ++kb, ++it) {
-                    const int s = (int)(it % TC_STAGES);
-                    mbar_wait(&full_bar[s], (uint32_t)((it / TC_STAGES) & 1));
-                    tc_fence_after();
-                    const uint32_t a_tmem = tmem + TC_A_COL0 + s * TC_A_COLS;
-                    const uint32_t b_smem = ring + s * TC_STAGE_BYTES;
-#pragma unroll
-                    for (int k4 = 0; k4 < TC_BK / 32; ++k4)
-                        tc_mma_i8_ts(d_tmem, a_tmem + k4 * 8, tc_smem_desc_sw128(b_smem + k4 * 32), idesc, (kb | k4) != 0 ? 1u : 0u);
-                    tc_commit(&empty_bar[s]);
+    } else if (warp == W_MMA) {
+        // ------------------------------------------------------------ MMA issuer (whole warp walks the loop, lane 0 issues)
+        // Everything the issue loop needs is a register + immediate: a long dependent chain of address arithmetic per
+        // tcgen05.mma would pace the tensor pipe (measured: ~850 clk per stage against a 256-clk floor).
+        constexpr uint32_t idesc = tc_idesc(TC_BM, TC_BN);
+        const uint64_t bdesc0 = tc_smem_desc_sw128(ring);
+        const uint32_t a_tmem0 = tmem + TC_A_COL0;
+        const uint32_t full0 = smem_u32(&full_bar[0]), empty0 = smem_u32(&empty_bar[0]);
+        int s = 0;
+        uint32_t ph = 0;
+        for (int tl = 0; tl < my_tiles; ++tl) {
+            const int buf = tl & 1;
+            mbar_wait(&tempty_bar[buf], (uint32_t)(((tl >> 1) & 1) ^ 1));
+            tc_fence_after();
+            const uint32_t d_tmem = tmem + buf * TC_BN;
+            for (int kb = 0; kb < p.KB; ++kb) {
+                {   // wait for the TMA bytes and the four unpack warps of this stage
+                    uint32_t ok;
+                    do {
+                        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                                     : "=r"(ok) : "r"(full0 + s * 8), "r"(ph) : "memory");
+                    } while (!ok);
                 }
-                tc_commit(&tfull_bar[buf]);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint64_t bd = bdesc0 + (uint64_t)(s * (TC_STAGE_BYTES >> 4));
+                    const uint32_t at = a_tmem0 + s * TC_A_COLS;
+                    tc_mma_i8_ts(d_tmem, at, bd, idesc, kb != 0 ? 1u : 0u);
+                    tc_mma_i8_ts(d_tmem, at + 8, bd + 2, idesc, 1u);
+                    tc_mma_i8_ts(d_tmem, at + 16, bd + 4, idesc, 1u);
+                    tc_mma_i8_ts(d_tmem, at + 24, bd + 6, idesc, 1u);
+                    if (CL == 1)
+                        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(empty0 + s * 8) : "memory");
+                    else   // the slot is refilled by every CTA of the cluster: tell all of them
+                        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                                     ::"r"(empty0 + s * 8), "h"((uint16_t)((1u << CL) - 1)) : "memory");
+                }
+                __syncwarp();
+                if (++s == TC_STAGES) { s = 0; ph ^= 1u; }
             }
+            if (lane == 0) tc_commit(&tfull_bar[buf]);
+            __syncwarp();
         }
     } else if (warp >= 4) {
         // ------------------------------------------------------------ unpack warps: 2-bit weights -> u8 codes -> TMEM
-        const int q = warp & 3;
+        const int q = warp & 3, grp = (warp - 4) >> 2;
         const uint32_t lane_base = (uint32_t)(q * 32) << 16;
         const int K4 = p.K / 4;
         uint32_t pre[TC_PF][8];
-        auto load_item = [&](long long item, uint32_t (&r)[8]) {
-            if (item >= n_items) return;
-            const int tl = (int)(item / p.KB), kb = (int)(item - (long long)tl * p.KB);
-            const int tile = blockIdx.x + tl * gridDim.x;
-            const int n_blk = tile % p.tiles_n;
+        int pending = -1;
+        // loads are issued strictly in item order: (tile, k-block) of the next load is tracked incrementally and the
+        // row's base pointer only changes at a tile boundary (keeps divisions out of the per-stage path)
+        int ld_item = grp, ld_kb = grp, ld_tl = 0;   // this group's items: grp, grp + NU, ...
+        const bool i2s = p.w_layout == WF_W_I2S;
+        const uint32_t kb_stride = i2s ? 32u : (uint32_t)WF_TILE_BYTES;
+        const uint8_t* rowbase = p.w;
+        auto set_tile = [&](int tl) {
+            int m_blk, n_blk;
+            tile_coords(tl, m_blk, n_blk);
             int row = n_blk * TC_BM + q * 32 + lane;
             if (row >= p.N) row = p.N - 1;   // padded rows compute garbage that the epilogue masks
-            if (p.w_layout == WF_W_I2S) {
-                const uint4* src = reinterpret_cast<const uint4*>(p.w + (size_t)row * K4 + (size_t)kb * 32);
-                const uint4 a = __ldg(src), b = __ldg(src + 1);
+            // b200_tile_v1: word (16*(r&7) + 4*(j&3) + 2*(j>>2) + (r>>3)) of tile (row/16, kb) holds packed bytes [4j,4j+4) of row r
+            rowbase = i2s ? p.w + (size_t)row * K4
+                          : p.w + (size_t)(row >> 4) * p.KB * WF_TILE_BYTES + (size_t)(16 * (row & 7) + ((row >> 3) & 1)) * 4;
+        };
+        while (ld_kb >= p.KB) { ld_kb -= p.KB; ++ld_tl; }
+        set_tile(ld_tl);
+        auto load_item = [&](uint32_t (&r)[8]) {
+            if (ld_item >= n_items) return;
+            const uint8_t* src = rowbase + (size_t)ld_kb * kb_stride;
+            if (i2s) {
+                const uint4 a = __ldg(reinterpret_cast<const uint4*>(src)), b = __ldg(reinterpret_cast<const uint4*>(src) + 1);
                 r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w; r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
             } else {
-                // b200_tile_v1: word (16*(r&7) + 4*(j&3) + 2*(j>>2) + (r>>3)) of tile (row/16, kb) holds packed bytes [4j,4j+4) of row r
-                const int r16 = row & 15;
-                const uint32_t* src = reinterpret_cast<const uint32_t*>(p.w) + ((size_t)(row >> 4) * p.KB + kb) * 128 + 16 * (r16 & 7) + (r16 >> 3);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) r[j] = __ldg(src + 4 * (j & 3) + 2 * (j >> 2));
+                for (int j = 0; j < 8; ++j) r[j] = __ldg(reinterpret_cast<const uint32_t*>(src) + 4 * (j & 3) + 2 * (j >> 2));
+            }
+            ld_item += NU;
+            ld_kb += NU;
+            if (ld_kb >= p.KB) {
+                do { ld_kb -= p.KB; ++ld_tl; } while (ld_kb >= p.KB);
+                set_tile(ld_tl);
             }
         };
 #pragma unroll
-        for (int u = 0; u < TC_PF; ++u) load_item(u, pre[u]);
-        for (long long item0 = 0; item0 < n_items; item0 += TC_PF) {
+        for (int u = 0; u < TC_PF; ++u) load_item(pre[u]);
+        for (int item0 = grp; item0 < n_items; item0 += TC_PF * NU) {
 #pragma unroll
             for (int u = 0; u < TC_PF; ++u) {
-                const long long item = item0 + u;
+                const int item = item0 + u * NU;
                 if (item < n_items) {
                     uint32_t v[32];
 #pragma unroll
                     for (int g = 0; g < 4; ++g)
 #pragma unroll
                         for (int j = 0; j < 8; ++j) v[8 * g + j] = (pre[u][j] >> (6 - 2 * g)) & 0x03030303u;   // k = 32g + 4j .. +3
-                    load_item(item + TC_PF, pre[u]);
-                    const int s = (int)(item % TC_STAGES);
+                    load_item(pre[u]);
+                    // retire the PREVIOUS stage's tcgen05.st only now: its latency overlapped the unpack above
+                    if (pending >= 0) {
+                        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&full_bar[pending]);
+                    }
+                    const int s = item % TC_STAGES;
                     mbar_wait(&empty_bar[s], (uint32_t)(((item / TC_STAGES) & 1) ^ 1));
                     tc_fence_after();
                     const uint32_t taddr = tmem + lane_base + TC_A_COL0 + s * TC_A_COLS;
                     TC_ST32(taddr, v);
-                    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&full_bar[s]);
+                    pending = s;
                 }
             }
         }
+        if (pending >= 0) {
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full_bar[pending]);
+        }
     } else {
-        // ------------------------------------------------------------ epilogue warps: TMEM -> registers -> global
+        // ------------------------------------------------------------ epilogue warps: TMEM -> registers -> smem transpose -> global
+        // A thread owns one weight row (TMEM lane) and receives 32 tokens per tcgen05.ld, but the output is token-major:
+        // each warp transposes its [32 tokens][32 rows] int32 block through a private padded smem patch, then a thread
+        // finishes 8 consecutive n of one token and writes them with one or two 16-byte stores.
         const int q = warp;
         const uint32_t lane_base = (uint32_t)(q * 32) << 16;
-        const bool relu2 = (p.ep.out_mode == WF_OUT_LINEAR) && (p.ep.epi_flags & WF_EPI_RELU2_MUL);
+        unsigned char* patch = smem_raw + (ring - smem_u32(smem_raw)) + TC_STAGES * TC_STAGE_BYTES + q * (32 * TC_EP_STRIDE);
+        const int oct = lane & 3, rsub = lane >> 2;
+        const int mode = p.ep.out_mode;
+        const bool relu2 = (mode == WF_OUT_LINEAR) && (p.ep.epi_flags & WF_EPI_RELU2_MUL);
+        const bool resid = (mode == WF_OUT_LINEAR) && (p.ep.epi_flags & WF_EPI_RESIDUAL);
+        const bool obf16 = (mode == WF_OUT_LINEAR) && p.ep.out_dtype == WF_BF16;
+        const int esize = obf16 ? 2 : 4;
+        const int ncols = relu2 ? p.N / 2 : p.N;
+        const bool vec_ok = (((size_t)p.ep.ldo * esize) % 16 == 0) && (((uintptr_t)p.ep.out & 15) == 0) &&
+                            (!resid || (((uintptr_t)p.ep.residual & 15) == 0));
         for (int tl = 0; tl < my_tiles; ++tl) {
-            const int tile = blockIdx.x + tl * gridDim.x;
-            const int m_blk = tile / p.tiles_n, n_blk = tile % p.tiles_n;
+            int m_blk, n_blk;
+            tile_coords(tl, m_blk, n_blk);
             const int buf = tl & 1;
             mbar_wait(&tfull_bar[buf], (uint32_t)((tl >> 1) & 1));
             tc_fence_after();
-            const int n = n_blk * TC_BM + q * 32 + lane;
+            const int n0 = n_blk * TC_BM + q * 32 + oct * 8;                       // first weight row of this thread's 8
+            const int c0 = relu2 ? (n0 >> 5) * 16 + (n0 & 15) : n0;                // first output column
+            const int nvalid = min(8, ncols - c0);                                 // <= 0: nothing to store
+            float ws8[8];
+            float wsu = 1.f;
+            if (mode == WF_OUT_LINEAR) {
+                if (relu2) {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) ws8[e] = p.ep.w_scale[0];
+                    wsu = p.ep.w_scale[p.ep.nseg > 1 ? 1 : 0];
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) ws8[e] = seg_scale(p.ep, min(n0 + e, p.N - 1));
+                }
+            }
 #pragma unroll 1
             for (int c = 0; c < TC_BN / 32; ++c) {
                 uint32_t v[32];
-                TC_LD32(tmem + lane_base + buf * TC_BN + c * 32, v);
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (!(p.dbg & 2)) {
+                    TC_LD32(tmem + lane_base + buf * TC_BN + c * 32, v);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                }
                 if (c == TC_BN / 32 - 1) {
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tempty_bar[buf]);
                 }
+                if (p.dbg) continue;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) *reinterpret_cast<uint32_t*>(patch + j * TC_EP_STRIDE + lane * 4) = v[j];
+                __syncwarp();
                 const int m0 = m_blk * TC_BN + c * 32;
-                if (relu2) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const int su = __shfl_down_sync(0xffffffffu, (int)v[j], 16);
-                        if (lane < 16 && n < p.N && m0 + j < p.M) epilogue_store_relu2(p.ep, m0 + j, n, (int)v[j], su);
+                for (int i = 0; i < 4; ++i) {
+                    const int r = rsub + 8 * i, m = m0 + r;
+                    if (m < p.M && nvalid > 0 && !(relu2 && oct >= 2)) {
+                        const int4 sa4 = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + oct * 32);
+                        const int4 sb4 = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + oct * 32 + 16);
+                        const int S[8] = {sa4.x, sa4.y, sa4.z, sa4.w, sb4.x, sb4.y, sb4.z, sb4.w};
+                        const int rs = p.ep.rowsum ? p.ep.rowsum[m] : 0;
+                        const size_t o = (size_t)m * p.ep.ldo + c0;
+                        if (mode == WF_OUT_LINEAR) {
+                            const float sa = p.ep.act_scale[p.ep.act_scale_per_token ? m : 0];
+                            float y[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) y[e] = ((float)(S[e] - rs) * ws8[e]) * sa;
+                            if (relu2) {
+                                const int4 ua = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + (oct + 2) * 32);
+                                const int4 ub = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + (oct + 2) * 32 + 16);
+                                const int U[8] = {ua.x, ua.y, ua.z, ua.w, ub.x, ub.y, ub.z, ub.w};
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) {
+                                    const float g = bf16_round(y[e]);
+                                    const float u = bf16_round(((float)(U[e] - rs) * wsu) * sa);
+                                    const float t = fmaxf(g, 0.f);
+                                    y[e] = bf16_round(bf16_round(t * t) * u);
+                                }
+                            } else if (resid) {
+                                const __nv_bfloat16* rp = p.ep.residual + o;
+                                if (vec_ok && nvalid == 8) {
+                                    const uint4 rv = *reinterpret_cast<const uint4*>(rp);
+                                    const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e) {
+                                        y[2 * e] = bf16lo(rw[e]) + bf16_round(y[2 * e]);
+                                        y[2 * e + 1] = bf16hi(rw[e]) + bf16_round(y[2 * e + 1]);
+                                    }
+                                } else {
+#pragma unroll
+                                    for (int e = 0; e < 8; ++e)
+                                        if (e < nvalid) y[e] = __bfloat162float(rp[e]) + bf16_round(y[e]);
+                                }
+                            }
+                            if (obf16) {
+                                __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.ep.out) + o;
+                                if (vec_ok && nvalid == 8) {
+                                    *reinterpret_cast<uint4*>(op) = make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]), pack_bf16x2(y[6], y[7]));
+                                } else {
+#pragma unroll
+                                    for (int e = 0; e < 8; ++e)
+                                        if (e < nvalid) op[e] = __float2bfloat16_rn(y[e]);
+                                }
+                            } else {
+                                float* op = reinterpret_cast<float*>(p.ep.out) + o;
+                                if (vec_ok && nvalid == 8) {
+                                    *reinterpret_cast<float4*>(op) = make_float4(y[0], y[1], y[2], y[3]);
+                                    *reinterpret_cast<float4*>(op + 4) = make_float4(y[4], y[5], y[6], y[7]);
+                                } else {
+#pragma unroll
+                                    for (int e = 0; e < 8; ++e)
+                                        if (e < nvalid) op[e] = y[e];
+                                }
+                            }
+                        } else {
+                            uint32_t w[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                if (mode == WF_OUT_I32_PLUS1) w[e] = (uint32_t)S[e];
+                                else if (mode == WF_OUT_I32) w[e] = (uint32_t)(S[e] - rs);
+                                else w[e] = __float_as_uint(__fmul_rn((float)S[e], p.ep.host_scale));   // bitnet_gemv/gemm: (float)sumi * scale
+                            }
+                            uint32_t* op = reinterpret_cast<uint32_t*>(p.ep.out) + o;
+                            if (vec_ok && nvalid == 8) {
+                                *reinterpret_cast<uint4*>(op) = make_uint4(w[0], w[1], w[2], w[3]);
+                                *reinterpret_cast<uint4*>(op + 4) = make_uint4(w[4], w[5], w[6], w[7]);
+                            } else {
+#pragma unroll
+                                for (int e = 0; e < 8; ++e)
+                                    if (e < nvalid) op[e] = w[e];
+                            }
+                        }
                     }
-                } else if (n < p.N) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (m0 + j < p.M) epilogue_store(p.ep, m0 + j, n, (int)v[j]);
                 }
+                __syncwarp();
             }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 9) {
+    if (CL > 1) {   // nobody leaves while a peer may still multicast into this CTA's ring or signal its barriers
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
+    if (warp == W_MMA) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TC_TMEM_COLS) : "memory");
     }
@@ -266,24 +451,39 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static EncodeTiledFn g_encode = nullptr;
 static bool g_tc_attr = false;
+static int g_tc_cluster = 0, g_tc_nu = 0;
 
 void gemm_tc_init_attrs() {
-    if (!g_tc_attr && cudaFuncSetAttribute(ternary_gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess) g_tc_attr = true;
+    if (!g_tc_attr) {
+        bool ok = cudaFuncSetAttribute(ternary_gemm_tc_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<1, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
+        g_tc_attr = ok;
+    }
     if (!g_encode) {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult qr;
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess)
             g_encode = (EncodeTiledFn)fn;
     }
+    if (!g_tc_cluster) {
+        const char* e = getenv("WF_TC_CLUSTER");
+        g_tc_cluster = e ? atoi(e) : 1;
+        if (g_tc_cluster != 1 && g_tc_cluster != 2) g_tc_cluster = 1;
+        const char* u = getenv("WF_TC_NU");
+        g_tc_nu = u ? atoi(u) : 3;
+        if (g_tc_nu < 1 || g_tc_nu > 3) g_tc_nu = 3;
+    }
 }
 
-int launch_gemm_tc(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s) {
-    gemm_tc_init_attrs();
-    if (!g_tc_attr || !g_encode) { set_error("gemm_tc: tcgen05 path unavailable (driver entry point / smem attribute)"); return WF_ERR_CUDA; }
+template <int CL, int NU>
+static int launch_tc_cl(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s) {
     CUtensorMap tmap;
     const cuuint64_t gdim[2] = {(cuuint64_t)a->K, (cuuint64_t)a->M};
     const cuuint64_t gstride[1] = {(cuuint64_t)a->ldq};
-    const cuuint32_t box[2] = {TC_BK, TC_BN};
+    const cuuint32_t box[2] = {TC_BK, TC_BN / CL};
     const cuuint32_t estr[2] = {1, 1};
     const CUresult cr = g_encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void*)a->q, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -294,10 +494,38 @@ int launch_gemm_tc(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s)
     p.tiles_n = (a->N + TC_BM - 1) / TC_BM;
     p.tiles_m = (a->M + TC_BN - 1) / TC_BN;
     p.ep = ep;
-    const int total = p.tiles_n * p.tiles_m;
-    const int grid = total < sm_count() ? total : sm_count();
-    ternary_gemm_tc_kernel<<<grid, TC_THREADS, TC_SMEM, s>>>(tmap, p);
-    return launch_check(cudaGetLastError(), "ternary_gemm_tc");
+    { const char* d = getenv("WF_TC_DBG"); p.dbg = d ? atoi(d) : 0; }
+    const int total = ((p.tiles_n + CL - 1) / CL) * p.tiles_m;
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3((4 + 4 * NU + 2) * 32);
+    cfg.dynamicSmemBytes = TC_SMEM;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = CL > 1 ? 1 : 0;
+    static int max_clusters = 0;   // per CL instantiation
+    if (!max_clusters) {
+        max_clusters = sm_count() / CL;
+        if (CL > 1) {
+            cfg.gridDim = dim3(sm_count() / CL * CL);
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, ternary_gemm_tc_kernel<CL, NU>, &cfg) == cudaSuccess && n > 0) max_clusters = n;
+            else cudaGetLastError();
+        }
+    }
+    const int clusters = total < max_clusters ? total : max_clusters;
+    cfg.gridDim = dim3(clusters * CL);
+    return launch_check(cudaLaunchKernelEx(&cfg, ternary_gemm_tc_kernel<CL, NU>, tmap, p), "ternary_gemm_tc");
+}
+
+int launch_gemm_tc(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s) {
+    gemm_tc_init_attrs();
+    if (!g_tc_attr || !g_encode) { set_error("gemm_tc: tcgen05 path unavailable (driver entry point / smem attribute)"); return WF_ERR_CUDA; }
+    if (g_tc_cluster == 2) return g_tc_nu == 2 ? launch_tc_cl<2, 2>(a, ep, s) : launch_tc_cl<2, 3>(a, ep, s);
+    if (g_tc_nu == 1) return launch_tc_cl<1, 1>(a, ep, s);
+    return g_tc_nu == 2 ? launch_tc_cl<1, 2>(a, ep, s) : launch_tc_cl<1, 3>(a, ep, s);
 }
 
 }  // namespace wf
