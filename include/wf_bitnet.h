@@ -235,6 +235,16 @@ int wf_engine_decode(wf_engine* e, const int32_t* host_tokens, int B, int32_t* h
 int wf_engine_decode_device(wf_engine* e, int B, int use_graph);
 int wf_engine_sync(wf_engine* e);
 void* wf_engine_stream(wf_engine* e);
+/* Tensor parallel engines (cfg.tp_size > 1; one process per GPU, SURVEY §8e — the reference has no multi-GPU path,
+ * this is the north star's "TP sharding of QKV/O/MLP with an all-reduce over NVLink").  Each rank creates its engine
+ * with its tp_rank, uploads ITS shard through wf_engine_set_linear (q,k,v,gate,up: this rank's output rows; o,down: this
+ * rank's input columns; norms/embedding replicated), then the ranks exchange wf_engine_tp_export() handles (CUDA IPC,
+ * wf_engine_tp_handle_bytes() each, e.g. with torch.distributed.all_gather) and call wf_engine_tp_attach with all
+ * tp_size handles in rank order.  After that wf_engine_decode* must be called by all ranks in lockstep; the
+ * exchanges are peer-memory stores / REDs fused into the attention and linear kernels (csrc/tp_comm.cuh). */
+size_t wf_engine_tp_handle_bytes(void);
+int wf_engine_tp_export(wf_engine* e, void* handle_out);
+int wf_engine_tp_attach(wf_engine* e, const void* handles);
 /* debug/parity taps (device pointers into engine state) */
 void* wf_engine_buffer(wf_engine* e, const char* name);
 int wf_engine_launches_per_step(const wf_engine* e);

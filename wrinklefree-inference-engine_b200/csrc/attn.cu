@@ -55,7 +55,24 @@ struct AttnParams {
     __nv_bfloat16* pool_w;       // pool, writable (append)
     int* merge_cnt;              // [B][Hkv] arrival counters (zero; self-cleaning)
     float* zero0; int zero0_n;   // accumulator range this phase clears
+    // ---- tensor parallel: this rank's heads land in [B][out_ld] buffers at column out_col0, on every rank
+    void* out_peer[TP_MAX];
+    int n_out, out_ld, out_col0, signal_flag;
+    TpComm tp;
 };
+
+// final output element (b, local head h, d): local buffer, or the attn_full buffer of every rank (the all-gather)
+__device__ __forceinline__ void attn_store(const AttnParams& p, int b, int h, int d, float v) {
+    if (p.n_out <= 1) {
+        const size_t o = (size_t)b * p.out_ld + p.out_col0 + (size_t)h * AT_D + d;
+        if (p.out_dtype == WF_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(v);
+        else reinterpret_cast<float*>(p.out)[o] = v;
+    } else {
+        const size_t o = (size_t)b * p.out_ld + p.out_col0 + (size_t)h * AT_D + d;
+        const __nv_bfloat16 bv = __float2bfloat16_rn(v);
+        for (int r = 0; r < p.n_out; ++r) reinterpret_cast<__nv_bfloat16*>(p.out_peer[r])[o] = bv;
+    }
+}
 
 __device__ __forceinline__ size_t kv_block_offset(int page, int layers, int layer, int kv, int Hkv, int head, int page_size) {
     return ((((size_t)page * layers + layer) * 2 + kv) * Hkv + head) * (size_t)page_size * AT_D;
@@ -79,7 +96,10 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
     const int seq_len = p.seq_lens[b];
     const int nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
     const int blk0 = chunk * p.chunk_blocks;
-    if (blk0 >= nblocks && !(chunk == 0)) return;
+    if (blk0 >= nblocks && !(chunk == 0)) {
+        if (FUSED && p.signal_flag >= 0) tp_signal_grid_done(p.tp, p.signal_flag, gridDim.x * gridDim.y * gridDim.z);
+        return;
+    }
     const int blk1 = min(nblocks, blk0 + p.chunk_blocks);
     const int my_n = (blk1 - blk0 - warp + AT_WARPS - 1) / AT_WARPS;   // blocks blk0 + warp + 4*i
     unsigned char* wsm = smem + warp * (AT_STAGES * AT_STAGE_BYTES);
@@ -294,9 +314,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
             }
             const int h = kvh * p.G + hh;
             if (p.direct) {
-                const float v = (L > 0.f) ? O / L : 0.f;
-                if (p.out_dtype == WF_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[((size_t)b * p.H + h) * AT_D + d] = __float2bfloat16_rn(v);
-                else reinterpret_cast<float*>(p.out)[((size_t)b * p.H + h) * AT_D + d] = v;
+                attn_store(p, b, h, d, (L > 0.f) ? O / L : 0.f);
             } else {
                 const size_t slot = ((size_t)b * p.H + h) * p.max_chunks + chunk;
                 p.part_o[slot * AT_D + d] = O;
@@ -332,12 +350,11 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
                     L += ldcg_f(p.part_ml + (base + c) * 2 + 1) * f;
                     O += ldcg_f(p.part_o + (base + c) * AT_D + d) * f;
                 }
-                const float v = (L > 0.f) ? O / L : 0.f;
-                if (p.out_dtype == WF_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[((size_t)b * p.H + h) * AT_D + d] = __float2bfloat16_rn(v);
-                else reinterpret_cast<float*>(p.out)[((size_t)b * p.H + h) * AT_D + d] = v;
+                attn_store(p, b, h, d, (L > 0.f) ? O / L : 0.f);
             }
         }
     }
+    if (FUSED && p.signal_flag >= 0) tp_signal_grid_done(p.tp, p.signal_flag, gridDim.x * gridDim.y * gridDim.z);
     if (!FUSED) pdl_launch_dependents();
 }
 
@@ -536,6 +553,7 @@ int attn_decode(const void* q, const void* pool, int layers, int layer, int Hkv,
     p.layers = layers; p.layer = layer; p.page_size = page_size; p.max_blocks = max_blocks;
     p.scale_log2e = scale * 1.4426950408889634f;
     p.out = out; p.out_dtype = out_dtype;
+    p.n_out = 1; p.out_ld = H * AT_D; p.out_col0 = 0; p.signal_flag = -1;
     return launch_paged_decode_attn(p, max_seq_hint, ws, ws_bytes, s, pdl);
 }
 
@@ -552,6 +570,9 @@ int attn_decode_fused(const FusedAttnArgs& a, cudaStream_t s, bool pdl) {
     p.qkv_acc = a.qkv_acc; p.qkv_ld = a.qkv_ld; p.qkv_rowsum = a.qkv_rowsum; p.qkv_ascale = a.qkv_ascale; p.qkv_wscale = a.qkv_wscale;
     p.positions = a.positions; p.cos_tab = (const __nv_bfloat16*)a.cos_tab; p.sin_tab = (const __nv_bfloat16*)a.sin_tab; p.max_pos = a.max_pos;
     p.merge_cnt = a.merge_cnt; p.zero0 = a.zero0; p.zero0_n = a.zero0_n;
+    p.n_out = a.n_out < 1 ? 1 : a.n_out; p.out_ld = a.out_ld > 0 ? a.out_ld : a.H * AT_D; p.out_col0 = a.out_col0;
+    for (int r = 0; r < TP_MAX; ++r) p.out_peer[r] = a.out_peer[r];
+    p.signal_flag = a.n_out > 1 ? a.signal_flag : -1; p.tp = a.tp;
     return launch_paged_decode_attn(p, a.max_seq_hint, a.ws, a.ws_bytes, s, pdl);
 }
 

@@ -36,8 +36,18 @@ struct wf_engine {
     cudaStream_t stream = nullptr;
     std::vector<LayerW> layers;
     __nv_bfloat16 *embed = nullptr, *final_norm = nullptr, *cos_tab = nullptr, *sin_tab = nullptr;
-    // local (per TP rank) dims
+    // local (per TP rank) dims: H / Hkv heads, ffn rows, attn_dim = H*D of THIS rank; *_full = the whole model's
     int H, Hkv, D, hidden, ffn, qkv_rows, attn_dim;
+    int attn_full, ffn_full;
+    // tensor parallel state (tp.size == 1: everything below degenerates to local buffers, no flags)
+    TpComm tp;
+    unsigned char* comm = nullptr;           // this rank's exchange buffer (see tp_comm.cuh)
+    size_t comm_bytes = 0, off_attn = 0, off_h = 0, off_acc_o = 0, off_acc_down = 0, off_cand = 0, off_flags = 0;
+    void* peer_opened[TP_MAX] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool tp_attached = false;
+    int* d_step = nullptr;
+    __nv_bfloat16* h_full = nullptr;
+    int v_lo = 0, v_n = 0;                   // this rank's vocab slice of the tied LM head
     // kv
     __nv_bfloat16* pool = nullptr;
     int max_blocks = 0;
@@ -180,91 +190,131 @@ int run_step(wf_engine* e, int B, int feed_back) {
 // NEXT phase applies scales / residual / relu^2*up / norm / re-quantisation in its prologue.
 //   B <= 8 : 5 launches per layer (qkv, attention, o, gate|up, down), each linear = glue prologue + TMA-streamed GEMV
 //   B  > 8 : 9 launches per layer (glue_rows + gemm_oneshot per linear, fused attention)
+// Tensor parallel (tp.size = T > 1): q|k|v and gate|up are split by output rows (whole heads), attention and
+// the KV pool by KV head, o and down by input columns.  The exchanges are fused into the producers (tp_comm.cuh):
+//   B  attention stores its heads into attn_full of every rank            (all-gather, flag 4l+0)
+//   C  o-proj REDs its exact partial sums into acc_o of every rank         (all-reduce, flag 4l+1)
+//   D' relu^2(gate)*up of the local ffn slice goes to h_full of every rank (all-gather, flag 4l+2; one extra launch)
+//   E  down-proj REDs into acc_down of every rank                          (all-reduce, flag 4l+3)
+// and every rank normalises / quantises the gathered FULL vectors exactly like T = 1, so the step is bit-identical.
 int run_step_fused(wf_engine* e, int B, int feed_back) {
     const wf_model_config& c = e->cfg;
     cudaStream_t s = e->stream;
     const bool pdl = e->pdl;
     const long long launches0 = launch_count();
     const int MB = c.max_batch;
+    const int T = e->tp.size;
+    const bool tp = T > 1;
     float* asc[4] = {e->lin_asc, e->lin_asc + MB, e->lin_asc + 2 * MB, e->lin_asc + 3 * MB};
     int32_t* rs[4] = {e->lin_rs, e->lin_rs + MB, e->lin_rs + 2 * MB, e->lin_rs + 3 * MB};
     __nv_bfloat16 *hA = e->hid, *hB = e->hid2;
     int rc;
-    auto phase = [&](GlueParams g, const uint8_t* w, int N, int K, float* acc_out, int slot, bool first) -> int {
-        g.M = B; g.K = K; g.eps = c.eps;
-        if (B <= 8 && linear_small_fits(B, K)) {
+    auto local_dest = [&](float* acc) { TpDest d = {}; d.n = 1; d.acc[0] = acc; d.signal_flag = -1; return d; };
+    auto all_dest = [&](size_t off, int flag) {
+        TpDest d = {};
+        d.n = T; d.signal_flag = tp ? flag : -1;
+        for (int r = 0; r < T; ++r) d.acc[r] = reinterpret_cast<float*>(e->tp.peer[r] + off);
+        return d;
+    };
+    // one linear phase: prologue over the full activation vector of length Kfull, GEMV/GEMM over this rank's K columns
+    auto phase = [&](GlueParams g, const uint8_t* w, int N, int Kfull, int K, int k_off, const TpDest& dest, int slot, bool first) -> int {
+        g.M = B; g.K = Kfull; g.eps = c.eps; g.tp = e->tp;
+        if (B <= 8 && linear_small_fits(B, Kfull)) {
             SmallLinArgs a;
-            a.g = g; a.w = w; a.N = N; a.K = K; a.acc_out = acc_out; a.acc_ld = N; a.lin_ascale = asc[slot]; a.lin_rowsum = rs[slot];
+            a.g = g; a.w = w; a.N = N; a.K = K; a.k_off = k_off; a.dest = dest; a.acc_ld = N; a.lin_ascale = asc[slot]; a.lin_rowsum = rs[slot];
             return launch_linear_small(a, s, pdl && !first);
         }
         g.q_out = e->q8; g.scale_out = asc[slot]; g.rowsum_out = rs[slot];
         int r = launch_glue_rows(g, s, pdl && !first);
         if (r) return r;
         OneshotArgs o;
-        o.w = w; o.N = N; o.K = K; o.q = e->q8; o.M = B; o.acc_out = acc_out; o.acc_ld = N;
+        o.w = w; o.N = N; o.K = K; o.q = e->q8; o.M = B; o.ldq = Kfull; o.k_off = k_off; o.dest = dest; o.acc_ld = N; o.tp = e->tp;
         return launch_gemm_oneshot(o, s, pdl);
     };
     const float attn_scale = 1.0f / sqrtf((float)e->D);
     for (int l = 0; l < c.layers; ++l) {
         LayerW& L = e->layers[l];
-        // ---- A: (embed | hidden + down-proj of the previous layer) -> input_layernorm -> qkv
+        const int fB = 4 * l, fC = 4 * l + 1, fD = 4 * l + 2, fE = 4 * l + 3;
+        // ---- A: (embed | hidden + down-proj of the previous layer) -> input_layernorm -> qkv (this rank's heads)
         {
             GlueParams g = {};
+            g.wait_flag = -1;
             if (l == 0) { g.mode = GL_EMBED; g.embed = e->embed; g.tokens = e->d_tok; }
             else {
                 g.mode = GL_RESID; g.hid_in = hA; g.acc = e->acc_down; g.acc_ld = e->hidden;
                 g.acc_rowsum = rs[3]; g.acc_ascale = asc[3]; g.acc_wscale = e->layers[l - 1].scales + 6;
+                if (tp) g.wait_flag = fE - 4;
             }
             g.hid_out = hB; g.gamma = L.g_in;
             g.zero0 = e->acc_gu; g.zero0_n = B * 2 * e->ffn;
-            if ((rc = phase(g, L.qkv, e->qkv_rows, e->hidden, e->acc_qkv, 0, l == 0))) return rc;
+            if ((rc = phase(g, L.qkv, e->qkv_rows, e->hidden, e->hidden, 0, local_dest(e->acc_qkv), 0, l == 0))) return rc;
         }
-        // ---- B: dequant + RoPE + KV append + paged attention + chunk merge
+        // ---- B: dequant + RoPE + KV append + paged attention + chunk merge (+ all-gather of the heads)
         {
             FusedAttnArgs a = {};
             a.pool = e->pool; a.layers = c.layers; a.layer = l; a.Hkv = e->Hkv; a.page_size = c.page_size;
             a.block_table = e->d_block_table; a.max_blocks = e->max_blocks; a.seq_lens = e->d_len; a.positions = e->d_pos;
             a.B = B; a.H = e->H; a.scale = attn_scale; a.out = e->attn;
+            a.n_out = T; a.out_ld = e->attn_full; a.out_col0 = e->tp.rank * e->attn_dim; a.signal_flag = fB; a.tp = e->tp;
+            for (int r = 0; r < T; ++r) a.out_peer[r] = e->tp.peer[r] + e->off_attn;
             a.qkv_acc = e->acc_qkv; a.qkv_ld = e->qkv_rows; a.qkv_rowsum = rs[0]; a.qkv_ascale = asc[0]; a.qkv_wscale = L.scales;
             a.cos_tab = e->cos_tab; a.sin_tab = e->sin_tab; a.max_pos = c.max_seq;
             a.merge_cnt = e->merge_cnt; a.zero0 = e->acc_down; a.zero0_n = B * e->hidden;
             a.max_seq_hint = e->attn_seq_hint; a.ws = e->ws_attn; a.ws_bytes = e->ws_attn_bytes;
             if ((rc = attn_decode_fused(a, s, pdl))) return rc;
         }
-        // ---- C: attn_sub_norm -> o
+        // ---- C: attn_sub_norm over the FULL attention vector -> o (this rank's input columns; RED = all-reduce)
         {
             GlueParams g = {};
-            g.mode = GL_PLAIN; g.src = e->attn; g.gamma = L.g_attn;
+            g.mode = GL_PLAIN; g.src = e->attn; g.gamma = L.g_attn; g.wait_flag = tp ? fB : -1;
             g.zero0 = e->acc_qkv; g.zero0_n = B * e->qkv_rows;
-            if ((rc = phase(g, L.o, e->hidden, e->attn_dim, e->acc_o, 1, false))) return rc;
+            if ((rc = phase(g, L.o, e->hidden, e->attn_full, e->attn_dim, e->tp.rank * e->attn_dim, all_dest(e->off_acc_o, fC), 1, false))) return rc;
         }
-        // ---- D: hidden + o-proj -> post_attention_layernorm -> gate|up
+        // ---- D: hidden + o-proj -> post_attention_layernorm -> gate|up (this rank's ffn rows)
         {
             GlueParams g = {};
             g.mode = GL_RESID; g.hid_in = hB; g.hid_out = hA; g.acc = e->acc_o; g.acc_ld = e->hidden;
-            g.acc_rowsum = rs[1]; g.acc_ascale = asc[1]; g.acc_wscale = L.scales + 3; g.gamma = L.g_post;
-            if ((rc = phase(g, L.gu, 2 * e->ffn, e->hidden, e->acc_gu, 2, false))) return rc;
+            g.acc_rowsum = rs[1]; g.acc_ascale = asc[1]; g.acc_wscale = L.scales + 3; g.gamma = L.g_post; g.wait_flag = tp ? fC : -1;
+            if ((rc = phase(g, L.gu, 2 * e->ffn, e->hidden, e->hidden, 0, local_dest(e->acc_gu), 2, false))) return rc;
         }
-        // ---- E: relu^2(gate)*up -> ffn_sub_norm -> down
+        // ---- D' (TP only): relu^2(gate)*up of the local slice -> h_full of every rank
+        if (tp) {
+            HExchangeArgs h = {};
+            h.acc = e->acc_gu; h.M = B; h.ffn_local = e->ffn; h.ffn_full = e->ffn_full; h.col0 = e->tp.rank * e->ffn;
+            h.rowsum = rs[2]; h.ascale = asc[2]; h.wscale = L.scales + 4;
+            h.n_dst = T; h.signal_flag = fD; h.tp = e->tp;
+            for (int r = 0; r < T; ++r) h.dst[r] = reinterpret_cast<__nv_bfloat16*>(e->tp.peer[r] + e->off_h);
+            if ((rc = launch_h_exchange(h, s, pdl))) return rc;
+        }
+        // ---- E: relu^2(gate)*up -> ffn_sub_norm over the FULL ffn vector -> down (RED = all-reduce)
         {
             GlueParams g = {};
-            g.mode = GL_RELU2; g.acc = e->acc_gu; g.acc_ld = 2 * e->ffn;
-            g.acc_rowsum = rs[2]; g.acc_ascale = asc[2]; g.acc_wscale = L.scales + 4; g.gamma = L.g_ffn;
+            if (tp) { g.mode = GL_PLAIN; g.src = e->h_full; g.wait_flag = fD; }
+            else {
+                g.mode = GL_RELU2; g.acc = e->acc_gu; g.acc_ld = 2 * e->ffn; g.wait_flag = -1;
+                g.acc_rowsum = rs[2]; g.acc_ascale = asc[2]; g.acc_wscale = L.scales + 4;
+            }
+            g.gamma = L.g_ffn;
             g.zero0 = e->acc_o; g.zero0_n = B * e->hidden;
-            if ((rc = phase(g, L.down, e->hidden, e->ffn, e->acc_down, 3, false))) return rc;
+            if ((rc = phase(g, L.down, e->hidden, e->ffn_full, e->ffn, e->tp.rank * e->ffn, all_dest(e->off_acc_down, fE), 3, false))) return rc;
         }
     }
-    // hidden + down-proj -> final norm -> tied LM head + greedy argmax
+    // hidden + down-proj -> final norm -> tied LM head (this rank's vocab slice) + greedy argmax
+    const int fLM = 4 * c.layers;
     {
         GlueParams g = {};
-        g.mode = GL_RESID; g.M = B; g.K = e->hidden; g.eps = c.eps;
+        g.mode = GL_RESID; g.M = B; g.K = e->hidden; g.eps = c.eps; g.tp = e->tp; g.wait_flag = tp ? fLM - 1 : -1;
         g.hid_in = hA; g.hid_out = hB; g.acc = e->acc_down; g.acc_ld = e->hidden;
         g.acc_rowsum = rs[3]; g.acc_ascale = asc[3]; g.acc_wscale = e->layers[c.layers - 1].scales + 6;
         g.gamma = e->final_norm; g.y_out = e->normed; g.q_out = e->q8;
         if ((rc = launch_glue_rows(g, s, pdl))) return rc;
     }
-    if ((rc = launch_lm_head_argmax(e->normed, e->embed, B, c.vocab, e->hidden, e->logits, e->d_next, e->ws_lm, s))) return rc;
-    if ((rc = launch_advance(e->d_pos, e->d_len, e->d_tok, e->d_next, B, feed_back, s))) return rc;
+    TpLm tl = {};
+    tl.tp = e->tp; tl.signal_flag = fLM;
+    for (int r = 0; r < T; ++r) tl.cand_peer[r] = e->tp.peer[r] + e->off_cand;
+    if ((rc = launch_lm_head_argmax_tp(e->normed, e->embed + (size_t)e->v_lo * e->hidden, B, e->v_n, e->hidden, e->logits + e->v_lo, c.vocab, e->v_lo,
+                                       e->d_next, e->ws_lm, &tl, s))) return rc;
+    if ((rc = launch_advance_tp(e->d_pos, e->d_len, e->d_tok, e->d_next, B, feed_back, e->d_step, &tl, s))) return rc;
     e->launches = (int)(launch_count() - launches0);
     return WF_OK;
 }
@@ -339,7 +389,13 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     if (!cfg || !out) { set_error("wf_engine_create: null argument"); return WF_ERR_INVALID; }
     const wf_model_config& c = *cfg;
     if (c.head_dim != 128) { set_error("engine: head_dim must be 128"); return WF_ERR_UNSUPPORTED; }
-    if (c.tp_size != 1 && c.tp_size != 0) { set_error("engine: tensor parallel engine is driven from the host layer (tp.py); tp_size must be 1 here"); return WF_ERR_UNSUPPORTED; }
+    const int T = c.tp_size <= 0 ? 1 : c.tp_size;
+    if (T > TP_MAX || c.tp_rank < 0 || c.tp_rank >= T) { set_error("engine: tp_size must be 1..%d and 0 <= tp_rank < tp_size", TP_MAX); return WF_ERR_INVALID; }
+    if (c.heads % T || c.kv_heads % T || c.ffn % (16 * T) || (c.ffn / T) % 128) {
+        set_error("engine: heads (%d), kv_heads (%d) and ffn/128 (%d) must be divisible by tp_size %d (SURVEY §8e: the 2B shape only shards over 1 or 5 GPUs)",
+                  c.heads, c.kv_heads, c.ffn / 128, T);
+        return WF_ERR_UNSUPPORTED;
+    }
     if (c.heads % c.kv_heads || c.heads / c.kv_heads > 8) { set_error("engine: heads/kv_heads must be an integer <= 8"); return WF_ERR_UNSUPPORTED; }
     if (c.hidden % 128 || c.ffn % 128 || (c.heads * c.head_dim) % 128) { set_error("engine: hidden, ffn, heads*head_dim must be multiples of 128"); return WF_ERR_UNSUPPORTED; }
     if (c.ffn % 16 || c.page_size % 16 || c.page_size <= 0) { set_error("engine: page_size must be a positive multiple of 16"); return WF_ERR_UNSUPPORTED; }
@@ -347,16 +403,28 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     if (c.max_seq % c.page_size) { set_error("engine: max_seq must be a multiple of page_size"); return WF_ERR_INVALID; }
     wf_engine* e = new wf_engine();
     e->cfg = c;
-    e->cfg.tp_size = 1; e->cfg.tp_rank = 0;
-    e->H = c.heads; e->Hkv = c.kv_heads; e->D = c.head_dim; e->hidden = c.hidden; e->ffn = c.ffn;
+    e->cfg.tp_size = T;
+    e->H = c.heads / T; e->Hkv = c.kv_heads / T; e->D = c.head_dim; e->hidden = c.hidden; e->ffn = c.ffn / T;
     e->qkv_rows = (e->H + 2 * e->Hkv) * e->D;
     e->attn_dim = e->H * e->D;
+    e->attn_full = c.heads * c.head_dim;
+    e->ffn_full = c.ffn;
+    memset(&e->tp, 0, sizeof e->tp);
+    e->tp.rank = c.tp_rank; e->tp.size = T;
+    {   // vocab slice of the tied LM head: whole 128-row CTAs per rank
+        const int slice = (((c.vocab + T - 1) / T) + 127) / 128 * 128;
+        e->v_lo = c.tp_rank * slice;
+        if (e->v_lo > c.vocab) e->v_lo = c.vocab;
+        e->v_n = c.vocab - e->v_lo < slice ? c.vocab - e->v_lo : slice;
+        if (e->v_n <= 0) { delete e; set_error("engine: vocab %d too small for tp_size %d", c.vocab, T); return WF_ERR_UNSUPPORTED; }
+    }
     const char* env_pdl = getenv("WF_PDL");
     e->pdl = env_pdl && atoi(env_pdl) != 0;
     const char* env_algo = getenv("WF_LINEAR_ALGO");
     e->linear_algo = env_algo ? atoi(env_algo) : 0;
     const char* env_fused = getenv("WF_FUSED");
     e->fused = env_fused ? atoi(env_fused) != 0 : 1;
+    if (T > 1) e->fused = 1;                   // the exchanges live in the phase kernels
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
     int rc = WF_OK;
     auto fail = [&](int r) { wf_engine_destroy(e); return r; };
@@ -375,8 +443,8 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
         if ((rc = dalloc(e, &L.scales, 8))) return fail(rc);
         if ((rc = dalloc(e, &L.g_in, e->hidden))) return fail(rc);
         if ((rc = dalloc(e, &L.g_post, e->hidden))) return fail(rc);
-        if ((rc = dalloc(e, &L.g_attn, e->attn_dim))) return fail(rc);
-        if ((rc = dalloc(e, &L.g_ffn, e->ffn))) return fail(rc);
+        if ((rc = dalloc(e, &L.g_attn, e->attn_full))) return fail(rc);
+        if ((rc = dalloc(e, &L.g_ffn, e->ffn_full))) return fail(rc);
     }
     if ((rc = dalloc(e, &e->embed, (size_t)c.vocab * c.hidden))) return fail(rc);
     if ((rc = dalloc(e, &e->final_norm, c.hidden))) return fail(rc);
@@ -409,18 +477,46 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     if (cuda_check(cudaMallocHost(&e->h_tok_pinned, B * 4), "pinned") || cuda_check(cudaMallocHost(&e->h_next_pinned, B * 4), "pinned") ||
         cuda_check(cudaMallocHost(&e->h_pos_pinned, 2 * B * 4), "pinned")) return fail(WF_ERR_CUDA);
     // activations
-    const int maxK = e->ffn > e->hidden ? (e->ffn > e->attn_dim ? e->ffn : e->attn_dim) : (e->hidden > e->attn_dim ? e->hidden : e->attn_dim);
+    int maxK = e->hidden;
+    if (e->attn_full > maxK) maxK = e->attn_full;
+    if (e->ffn_full > maxK) maxK = e->ffn_full;
+    // exchange buffer: everything a peer writes into (tp_comm.cuh).  One cudaMalloc so that one IPC handle exports it.
+    {
+        auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+        size_t off = 0;
+        e->off_attn = off; off = up(off + (size_t)B * e->attn_full * 2);
+        e->off_h = off; off = up(off + (size_t)B * e->ffn_full * 2);
+        e->off_acc_o = off; off = up(off + (size_t)B * e->hidden * 4);
+        e->off_acc_down = off; off = up(off + (size_t)B * e->hidden * 4);
+        e->off_cand = off; off = up(off + (size_t)B * TP_MAX * 8);
+        e->off_flags = off; off = up(off + (size_t)(4 * c.layers + 1) * TP_MAX * 4);
+        e->comm_bytes = off;
+        if ((rc = dalloc(e, &e->comm, e->comm_bytes))) return fail(rc);
+        if (cuda_check(cudaMemset(e->comm, 0, e->comm_bytes), "comm memset")) return fail(WF_ERR_CUDA);
+        e->attn = reinterpret_cast<__nv_bfloat16*>(e->comm + e->off_attn);
+        e->h_full = reinterpret_cast<__nv_bfloat16*>(e->comm + e->off_h);
+        e->acc_o = reinterpret_cast<float*>(e->comm + e->off_acc_o);
+        e->acc_down = reinterpret_cast<float*>(e->comm + e->off_acc_down);
+        e->tp.peer[c.tp_rank] = e->comm;
+        e->tp.off_flags = e->off_flags;
+        int* cnt = nullptr;
+        if ((rc = dalloc(e, &cnt, (size_t)4 * c.layers + 1)) || (rc = dalloc(e, &e->d_step, 1))) return fail(rc);
+        if (cuda_check(cudaMemset(cnt, 0, ((size_t)4 * c.layers + 1) * 4), "cnt memset") || cuda_check(cudaMemset(e->d_step, 0, 4), "step memset")) return fail(WF_ERR_CUDA);
+        e->tp.done_cnt = cnt;
+        e->tp.step = e->d_step;
+        e->tp_attached = (T == 1);
+    }
     if ((rc = dalloc(e, &e->hid, (size_t)B * e->hidden)) || (rc = dalloc(e, &e->normed, (size_t)B * e->hidden)) ||
         (rc = dalloc(e, &e->qkv, (size_t)B * e->qkv_rows)) || (rc = dalloc(e, &e->qrot, (size_t)B * e->attn_dim)) ||
-        (rc = dalloc(e, &e->attn, (size_t)B * e->attn_dim)) || (rc = dalloc(e, &e->gu, (size_t)B * e->ffn)) ||
+        (rc = dalloc(e, &e->gu, (size_t)B * e->ffn)) ||
         (rc = dalloc(e, &e->q8, (size_t)B * maxK)) || (rc = dalloc(e, &e->a_scale, B)) || (rc = dalloc(e, &e->rowsum, B)) ||
         (rc = dalloc(e, &e->logits, (size_t)B * c.vocab))) return fail(rc);
-    if ((rc = dalloc(e, &e->acc_qkv, (size_t)B * e->qkv_rows)) || (rc = dalloc(e, &e->acc_o, (size_t)B * e->hidden)) ||
-        (rc = dalloc(e, &e->acc_gu, (size_t)B * 2 * e->ffn)) || (rc = dalloc(e, &e->acc_down, (size_t)B * e->hidden)) ||
+    if ((rc = dalloc(e, &e->acc_qkv, (size_t)B * e->qkv_rows)) ||
+        (rc = dalloc(e, &e->acc_gu, (size_t)B * 2 * e->ffn)) ||
         (rc = dalloc(e, &e->lin_asc, (size_t)4 * B)) || (rc = dalloc(e, &e->lin_rs, (size_t)4 * B)) ||
         (rc = dalloc(e, &e->hid2, (size_t)B * e->hidden)) || (rc = dalloc(e, &e->merge_cnt, (size_t)B * e->Hkv))) return fail(rc);
-    if (cuda_check(cudaMemset(e->acc_qkv, 0, (size_t)B * e->qkv_rows * 4), "acc memset") || cuda_check(cudaMemset(e->acc_o, 0, (size_t)B * e->hidden * 4), "acc memset") ||
-        cuda_check(cudaMemset(e->acc_gu, 0, (size_t)B * 2 * e->ffn * 4), "acc memset") || cuda_check(cudaMemset(e->acc_down, 0, (size_t)B * e->hidden * 4), "acc memset") ||
+    if (cuda_check(cudaMemset(e->acc_qkv, 0, (size_t)B * e->qkv_rows * 4), "acc memset") ||
+        cuda_check(cudaMemset(e->acc_gu, 0, (size_t)B * 2 * e->ffn * 4), "acc memset") ||
         cuda_check(cudaMemset(e->merge_cnt, 0, (size_t)B * e->Hkv * 4), "cnt memset")) return fail(WF_ERR_CUDA);
     const int maxN = 2 * e->ffn > e->qkv_rows ? 2 * e->ffn : e->qkv_rows;
     e->ws_lin_bytes = wf_linear_workspace_bytes(B, maxN, maxK) + (size_t)maxN * 4;
@@ -443,6 +539,8 @@ extern "C" void wf_engine_destroy(wf_engine* e) {
     if (!e) return;
     cudaDeviceSynchronize();
     invalidate_graphs(e);
+    for (int r = 0; r < TP_MAX; ++r)
+        if (e->peer_opened[r]) cudaIpcCloseMemHandle(e->peer_opened[r]);
     for (void* p : e->allocs) cudaFree(p);
     for (auto& L : e->layers)
         for (int i = 0; i < 7; ++i)
@@ -489,8 +587,8 @@ extern "C" int wf_engine_set_tensor(wf_engine* e, int layer, const char* name, c
         LayerW& L = e->layers[layer];
         if (n == "input_layernorm") { dst = L.g_in; expect = e->hidden; }
         else if (n == "post_attention_layernorm") { dst = L.g_post; expect = e->hidden; }
-        else if (n == "attn_sub_norm") { dst = L.g_attn; expect = e->attn_dim; }
-        else if (n == "ffn_sub_norm") { dst = L.g_ffn; expect = e->ffn; }
+        else if (n == "attn_sub_norm") { dst = L.g_attn; expect = e->attn_full; }
+        else if (n == "ffn_sub_norm") { dst = L.g_ffn; expect = e->ffn_full; }
     }
     if (!dst) { set_error("wf_engine_set_tensor: unknown tensor '%s' (layer %d)", name, layer); return WF_ERR_INVALID; }
     if (count != expect) { set_error("wf_engine_set_tensor: '%s' expects %zu elements, got %zu", name, expect, count); return WF_ERR_INVALID; }
@@ -548,10 +646,11 @@ extern "C" int wf_engine_init_synthetic(wf_engine* e, uint64_t seed) {
     for (int l = 0; l < e->cfg.layers; ++l) {
         LayerW& L = e->layers[l];
         const uint64_t sd = seed * 1000003ull + (uint64_t)l * 7919ull;
-        if ((rc = launch_fill_ternary(L.qkv, wf_tile_bytes(e->qkv_rows, e->hidden), sd + 1, s))) return rc;
-        if ((rc = launch_fill_ternary(L.o, wf_tile_bytes(e->hidden, e->attn_dim), sd + 2, s))) return rc;
-        if ((rc = launch_fill_ternary(L.gu, wf_tile_bytes(2 * e->ffn, e->hidden), sd + 3, s))) return rc;
-        if ((rc = launch_fill_ternary(L.down, wf_tile_bytes(e->hidden, e->ffn), sd + 4, s))) return rc;
+        const uint64_t sr = sd + (uint64_t)e->tp.rank * 0x9E3779B97F4A7C15ull;   // sharded matrices differ per rank, replicated tensors do not
+        if ((rc = launch_fill_ternary(L.qkv, wf_tile_bytes(e->qkv_rows, e->hidden), sr + 1, s))) return rc;
+        if ((rc = launch_fill_ternary(L.o, wf_tile_bytes(e->hidden, e->attn_dim), sr + 2, s))) return rc;
+        if ((rc = launch_fill_ternary(L.gu, wf_tile_bytes(2 * e->ffn, e->hidden), sr + 3, s))) return rc;
+        if ((rc = launch_fill_ternary(L.down, wf_tile_bytes(e->hidden, e->ffn), sr + 4, s))) return rc;
         // weight_scale ~ U(0.5, 2.5); deterministic LCG on the host
         uint64_t st = sd ^ 0xD1B54A32D192ED03ull;
         for (int i = 0; i < 7; ++i) {
@@ -562,8 +661,8 @@ extern "C" int wf_engine_init_synthetic(wf_engine* e, uint64_t seed) {
         cudaStreamSynchronize(s);
         if ((rc = launch_fill_bf16(L.g_in, e->hidden, sd + 5, 1.0f, 0.1f, s))) return rc;
         if ((rc = launch_fill_bf16(L.g_post, e->hidden, sd + 6, 1.0f, 0.1f, s))) return rc;
-        if ((rc = launch_fill_bf16(L.g_attn, e->attn_dim, sd + 7, 1.0f, 0.1f, s))) return rc;
-        if ((rc = launch_fill_bf16(L.g_ffn, e->ffn, sd + 8, 1.0f, 0.1f, s))) return rc;
+        if ((rc = launch_fill_bf16(L.g_attn, e->attn_full, sd + 7, 1.0f, 0.1f, s))) return rc;
+        if ((rc = launch_fill_bf16(L.g_ffn, e->ffn_full, sd + 8, 1.0f, 0.1f, s))) return rc;
     }
     if ((rc = launch_fill_bf16(e->embed, (size_t)e->cfg.vocab * e->hidden, seed + 11, 0.0f, 0.02f, s))) return rc;
     if ((rc = launch_fill_bf16(e->final_norm, e->hidden, seed + 12, 1.0f, 0.1f, s))) return rc;
@@ -623,6 +722,7 @@ extern "C" int wf_engine_set_context(wf_engine* e, int slot, int len, int fill_r
 extern "C" int wf_engine_decode_device(wf_engine* e, int B, int use_graph) {
     if (!e || B < 1 || B > e->cfg.max_batch) { set_error("wf_engine_decode_device: bad batch %d", B); return WF_ERR_INVALID; }
     if (!e->finalized) { set_error("engine weights not finalized"); return WF_ERR_INVALID; }
+    if (!e->tp_attached) { set_error("tensor-parallel engine: wf_engine_tp_attach has not been called"); return WF_ERR_INVALID; }
     int rc = prepare_pages(e, B);
     if (rc) return rc;
     rc = step_graph(e, B, /*feed_back=*/1, use_graph);
@@ -634,6 +734,7 @@ extern "C" int wf_engine_decode_device(wf_engine* e, int B, int use_graph) {
 extern "C" int wf_engine_decode(wf_engine* e, const int32_t* host_tokens, int B, int32_t* host_next_tokens) {
     if (!e || !host_tokens || !host_next_tokens || B < 1 || B > e->cfg.max_batch) { set_error("wf_engine_decode: bad arguments"); return WF_ERR_INVALID; }
     if (!e->finalized) { set_error("engine weights not finalized"); return WF_ERR_INVALID; }
+    if (!e->tp_attached) { set_error("tensor-parallel engine: wf_engine_tp_attach has not been called"); return WF_ERR_INVALID; }
     int rc = prepare_pages(e, B);
     if (rc) return rc;
     memcpy(e->h_tok_pinned, host_tokens, (size_t)B * 4);
@@ -644,6 +745,35 @@ extern "C" int wf_engine_decode(wf_engine* e, const int32_t* host_tokens, int B,
     if (cuda_check(cudaStreamSynchronize(e->stream), "decode sync")) return WF_ERR_CUDA;
     memcpy(host_next_tokens, e->h_next_pinned, (size_t)B * 4);
     for (int b = 0; b < B; ++b) e->h_pos[b] += 1;
+    return WF_OK;
+}
+
+// ---- tensor parallel attach: one process per GPU, comm buffers exchanged as CUDA IPC handles ------------------------
+extern "C" size_t wf_engine_tp_handle_bytes(void) { return sizeof(cudaIpcMemHandle_t); }
+
+extern "C" int wf_engine_tp_export(wf_engine* e, void* handle_out) {
+    if (!e || !handle_out) { set_error("wf_engine_tp_export: null argument"); return WF_ERR_INVALID; }
+    cudaIpcMemHandle_t h;
+    if (cuda_check(cudaIpcGetMemHandle(&h, e->comm), "cudaIpcGetMemHandle")) return WF_ERR_CUDA;
+    memcpy(handle_out, &h, sizeof h);
+    return WF_OK;
+}
+
+extern "C" int wf_engine_tp_attach(wf_engine* e, const void* handles) {
+    if (!e || !handles) { set_error("wf_engine_tp_attach: null argument"); return WF_ERR_INVALID; }
+    const int T = e->tp.size;
+    for (int r = 0; r < T; ++r) {
+        if (r == e->tp.rank) continue;
+        if (e->peer_opened[r]) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char*)handles + (size_t)r * sizeof h, sizeof h);
+        void* p = nullptr;
+        if (cuda_check(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess), "cudaIpcOpenMemHandle")) return WF_ERR_CUDA;
+        e->peer_opened[r] = p;
+        e->tp.peer[r] = (unsigned char*)p;
+    }
+    e->tp_attached = true;
+    invalidate_graphs(e);
     return WF_OK;
 }
 
@@ -669,6 +799,7 @@ extern "C" void* wf_engine_buffer(wf_engine* e, const char* name) {
 // engine stream; `iters` launches cycling over the layers so the working set exceeds L2).
 extern "C" int wf_engine_time_kernel(wf_engine* e, const char* which, int B, int iters, float* ms_out) {
     if (!e || !which || !ms_out || B < 1 || B > e->cfg.max_batch || iters < 1) { set_error("wf_engine_time_kernel: bad arguments"); return WF_ERR_INVALID; }
+    if (e->tp.size > 1) { set_error("wf_engine_time_kernel: single-GPU engines only"); return WF_ERR_UNSUPPORTED; }
     int rc = prepare_pages(e, B);
     if (rc) return rc;
     e->attn_seq_hint = seq_hint_for(e, B);

@@ -11,6 +11,7 @@
 // rounding points are the reference's (every torch op on a bf16 tensor rounds).
 #pragma once
 #include "common.cuh"
+#include "tp_comm.cuh"
 #include "wf_bitnet.h"
 
 namespace wf {
@@ -43,6 +44,17 @@ struct GlueParams {
     float* scale_out;               // [M]
     int32_t* rowsum_out;            // [M]
     __nv_bfloat16* y_out;           // [M][K] normalised activations (final norm -> LM head), optional
+    // tensor parallel: the source of this phase was produced by an exchange — wait for every rank's flag first
+    int wait_flag;                  // flag id, -1 = none
+    TpComm tp;
+};
+
+// where a linear's partial sums go: the local accumulator, or (row-parallel o / down under TP) the same accumulator
+// on every rank — the all-reduce is the RED itself
+struct TpDest {
+    int n;                          // destinations (1 = local only)
+    float* acc[TP_MAX];
+    int signal_flag;                // flag id published when the whole grid has finished its REDs, -1 = none
 };
 
 __device__ __forceinline__ float4 ldcg_f4(const float* p) {
@@ -231,10 +243,11 @@ __device__ __forceinline__ void glue_zero_duty(const GlueParams& p) {
 
 // launchers (host)
 struct SmallLinArgs {
-    GlueParams g;
-    const uint8_t* w;        // b200_tile_v1
-    int N, K;
-    float* acc_out;          // fp32 [M][acc_ld], zero on entry
+    GlueParams g;            // g.K = length of the (full) activation vector the prologue normalises / quantises
+    const uint8_t* w;        // b200_tile_v1 [N][K]
+    int N, K;                // K = columns of THIS rank's weight slice (== g.K without tensor parallelism)
+    int k_off;               // first activation column of the slice
+    TpDest dest;             // fp32 [M][acc_ld] accumulators, zero on entry
     int acc_ld;
     float* lin_ascale;       // [M] out: activation scale of THIS linear's input
     int32_t* lin_rowsum;     // [M] out: Sigma a
@@ -245,11 +258,24 @@ int launch_glue_rows(const GlueParams& g, cudaStream_t s, bool pdl);
 struct OneshotArgs {
     const uint8_t* w;
     int N, K;
-    const int8_t* q;         // [M][K]
-    int M;
-    float* acc_out;
+    const int8_t* q;         // [M][ldq], the slice starts at column k_off
+    int M, ldq, k_off;
+    TpDest dest;
     int acc_ld;
+    TpComm tp;
 };
+// relu^2(gate)*up of the local ffn slice, stored into h_full of every rank (tensor parallel phase D')
+struct HExchangeArgs {
+    const float* acc;        // [M][2*ffn_local] gate|up interleaved in 16-row blocks
+    int M, ffn_local, ffn_full, col0;
+    const int32_t* rowsum;
+    const float* ascale;
+    const float* wscale;     // device [2]
+    __nv_bfloat16* dst[TP_MAX];
+    int n_dst, signal_flag;
+    TpComm tp;
+};
+int launch_h_exchange(const HExchangeArgs& a, cudaStream_t s, bool pdl);
 int launch_gemm_oneshot(const OneshotArgs& a, cudaStream_t s, bool pdl);
 void fused_init_attrs();
 struct FusedAttnArgs {
@@ -261,7 +287,10 @@ struct FusedAttnArgs {
     const int32_t* positions;
     int B, H;
     float scale;
-    void* out;                 // bf16 [B][H][128]
+    void* out;                 // bf16 [B][out_ld], this rank's heads start at column out_col0
+    void* out_peer[TP_MAX];    // the same buffer on every rank (n_out entries; [0] unused when n_out <= 1)
+    int n_out, out_ld, out_col0, signal_flag;
+    TpComm tp;
     const float* qkv_acc;
     int qkv_ld;
     const int32_t* qkv_rowsum;

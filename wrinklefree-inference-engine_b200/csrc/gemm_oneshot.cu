@@ -21,8 +21,10 @@ struct OneshotParams {
     const uint8_t* w;
     const int8_t* q;
     int M, N, K, KB, RB, KC;
-    float* acc_out;
+    int ldq, k_off;
+    TpDest dest;
     int acc_ld;
+    TpComm tp;
 };
 
 template <int RBW>
@@ -59,7 +61,7 @@ __global__ void __launch_bounds__(GO_T) gemm_oneshot_kernel(const OneshotParams 
         for (int g = tid; g < GO_MT * gran_per_row; g += GO_T) {
             const int m = g / gran_per_row, gi = g - m * gran_per_row;
             const bool ok = m < p.M;
-            const int8_t* src = p.q + (size_t)(ok ? m : 0) * p.K + (size_t)kb0 * 128 + (size_t)gi * 16;
+            const int8_t* src = p.q + (size_t)(ok ? m : 0) * p.ldq + p.k_off + (size_t)kb0 * 128 + (size_t)gi * 16;
             cp_async16_zfill(as + (size_t)m * a_stride + (size_t)gi * 16, src, ok ? 16 : 0);
         }
         cp_async_commit();
@@ -125,9 +127,12 @@ __global__ void __launch_bounds__(GO_T) gemm_oneshot_kernel(const OneshotParams 
         const int n = row0 + 4 * c;
         if (n >= p.N) continue;
         const float4 v = *reinterpret_cast<const float4*>(St + ml * SS + 4 * c);
-        if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f)
-            red_add_v4_f32(p.acc_out + (size_t)ml * p.acc_ld + n, v.x, v.y, v.z, v.w);
+        if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) {
+            // row-parallel linears under TP: the RED into every rank's accumulator IS the all-reduce
+            for (int d = 0; d < p.dest.n; ++d) red_add_v4_f32(p.dest.acc[d] + (size_t)ml * p.acc_ld + n, v.x, v.y, v.z, v.w);
+        }
     }
+    if (p.dest.signal_flag >= 0) tp_signal_grid_done(p.tp, p.dest.signal_flag, gridDim.x * gridDim.y);
 }
 
 template <int RBW>
@@ -158,7 +163,9 @@ int launch_gemm_oneshot(const OneshotArgs& a, cudaStream_t s, bool pdl) {
     p.w = a.w; p.q = a.q; p.M = a.M; p.N = a.N; p.K = a.K;
     p.KB = a.K / WF_QK;
     p.RB = (a.N + 15) / 16;
-    p.acc_out = a.acc_out; p.acc_ld = a.acc_ld;
+    p.ldq = a.ldq; p.k_off = a.k_off;
+    p.dest = a.dest; p.acc_ld = a.acc_ld; p.tp = a.tp;
+    if (a.ldq % 16 || a.k_off % WF_QK) { set_error("gemm_oneshot: ldq %% 16 and k_off %% 128 must be 0"); return WF_ERR_INVALID; }
     if (!g_kc_max) {
         const char* e = getenv("WF_ONESHOT_KC");
         g_kc_max = e ? atoi(e) : 6;

@@ -4,7 +4,9 @@
 // Reference: scripts/direct_inference_full.py:290 (embedding row), :297-300 (F.linear(hidden, embed) in
 // bf16), :305-306 (argmax sampling at temperature 0).
 #include "common.cuh"
+#include "tp_comm.cuh"
 #include "wf_bitnet.h"
+#include "kernels.cuh"
 
 namespace wf {
 
@@ -27,7 +29,7 @@ constexpr int LM_STAGES = 4;
 
 template <int NT>
 __global__ void __launch_bounds__(256) lm_head_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* __restrict__ E,
-                                                      int B, int V, int K, float* __restrict__ logits_out,
+                                                      int B, int V, int K, float* __restrict__ logits_out, int ldl, int v_off,
                                                       float* __restrict__ part_val, int* __restrict__ part_idx) {
     constexpr int MT = NT * 8;
     constexpr int E_STAGE = LM_ROWS * 128;
@@ -123,7 +125,7 @@ __global__ void __launch_bounds__(256) lm_head_kernel(const __nv_bfloat16* __res
     if (logits_out) {
         for (int i = tid; i < mcount * LM_ROWS; i += 256) {
             const int ml = i / LM_ROWS, nl = i % LM_ROWS;
-            if (v0 + nl < V) logits_out[(size_t)(m0 + ml) * V + v0 + nl] = St[ml * SS + nl];
+            if (v0 + nl < V) logits_out[(size_t)(m0 + ml) * ldl + v0 + nl] = St[ml * SS + nl];
         }
     }
     // per batch row: max / lowest index over this CTA's 128 vocab rows (warp w handles rows w, w+8, ...)
@@ -145,14 +147,14 @@ __global__ void __launch_bounds__(256) lm_head_kernel(const __nv_bfloat16* __res
         }
         if (lane == 0) {
             part_val[(size_t)(m0 + ml) * gridDim.x + blockIdx.x] = best;
-            part_idx[(size_t)(m0 + ml) * gridDim.x + blockIdx.x] = bi;
+            part_idx[(size_t)(m0 + ml) * gridDim.x + blockIdx.x] = bi + v_off;   // global vocab index (vocab-split LM head)
         }
     }
     pdl_launch_dependents();
 }
 
 __global__ void __launch_bounds__(256) argmax_reduce_kernel(const float* __restrict__ part_val, const int* __restrict__ part_idx,
-                                                            int nparts, int32_t* __restrict__ next) {
+                                                            int nparts, int32_t* __restrict__ next, const TpLm tpl) {
     __shared__ float sv[8];
     __shared__ int si[8];
     const int b = blockIdx.x;
@@ -175,20 +177,50 @@ __global__ void __launch_bounds__(256) argmax_reduce_kernel(const float* __restr
     if (threadIdx.x == 0) {
         for (int w = 1; w < 8; ++w)
             if (sv[w] > best || (sv[w] == best && si[w] < bi)) { best = sv[w]; bi = si[w]; }
-        next[b] = bi;
+        if (tpl.tp.size > 1) {
+            // vocab-split LM head: publish this rank's candidate on every rank; advance_kernel picks the winner
+            for (int r = 0; r < tpl.tp.size; ++r) {
+                float2* c = reinterpret_cast<float2*>(tpl.cand_peer[r]) + (size_t)b * TP_MAX + tpl.tp.rank;
+                *c = make_float2(best, __int_as_float(bi));
+            }
+        } else {
+            next[b] = bi;
+        }
     }
+    if (tpl.tp.size > 1) tp_signal_grid_done(tpl.tp, tpl.signal_flag, gridDim.x);
     pdl_launch_dependents();
 }
 
 // positions / seq_lens advance + feed the sampled token back (device-resident decode loop)
-__global__ void advance_kernel(int32_t* positions, int32_t* seq_lens, int32_t* tokens, const int32_t* next, int B, int feed_back) {
+// (one CTA: B <= 64).  Under TP it first waits for every rank's LM-head candidate and reduces them (highest logit,
+// lowest index on ties — torch.argmax).  It also closes the step: the device step counter drives the TP flags.
+__global__ void advance_kernel(int32_t* positions, int32_t* seq_lens, int32_t* tokens, int32_t* next, int B, int feed_back, int* step,
+                               const TpLm tpl) {
     pdl_wait_prior();
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tpl.tp.size > 1) {
+        if (threadIdx.x < 32) tp_wait_flags_warp(tpl.tp, tpl.signal_flag);
+        __syncthreads();
+    }
+    const int b = threadIdx.x;
     if (b < B) {
+        if (tpl.tp.size > 1) {
+            float best = -INFINITY;
+            int bi = 0x7fffffff;
+            const float2* c = reinterpret_cast<const float2*>(tpl.cand_peer[tpl.tp.rank]) + (size_t)b * TP_MAX;
+            for (int r = 0; r < tpl.tp.size; ++r) {
+                float2 v;
+                asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(c + r));
+                const int vi = __float_as_int(v.y);
+                if (v.x > best || (v.x == best && vi < bi)) { best = v.x; bi = vi; }
+            }
+            next[b] = bi;
+        }
         positions[b] += 1;
         seq_lens[b] += 1;
         if (feed_back) tokens[b] = next[b];
     }
+    __syncthreads();
+    if (threadIdx.x == 0 && step) *step += 1;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -229,9 +261,16 @@ int launch_embed(const void* table, const int32_t* tokens, int B, int H, void* o
     return launch_check(cudaGetLastError(), "embed");
 }
 
-int launch_advance(int32_t* positions, int32_t* seq_lens, int32_t* tokens, const int32_t* next, int B, int feed_back, cudaStream_t s) {
-    advance_kernel<<<(B + 127) / 128, 128, 0, s>>>(positions, seq_lens, tokens, next, B, feed_back);
+int launch_advance_tp(int32_t* positions, int32_t* seq_lens, int32_t* tokens, int32_t* next, int B, int feed_back, int* step, const TpLm* tpl,
+                      cudaStream_t s) {
+    if (B > 128) { set_error("advance: B > 128"); return WF_ERR_UNSUPPORTED; }
+    TpLm t = {};
+    if (tpl) t = *tpl; else { t.tp.size = 1; t.signal_flag = -1; }
+    advance_kernel<<<1, 128, 0, s>>>(positions, seq_lens, tokens, next, B, feed_back, step, t);
     return launch_check(cudaGetLastError(), "advance");
+}
+int launch_advance(int32_t* positions, int32_t* seq_lens, int32_t* tokens, const int32_t* next, int B, int feed_back, cudaStream_t s) {
+    return launch_advance_tp(positions, seq_lens, tokens, const_cast<int32_t*>(next), B, feed_back, nullptr, nullptr, s);
 }
 
 int launch_fill_ternary(void* out, size_t bytes, uint64_t seed, cudaStream_t s) {
@@ -244,7 +283,7 @@ int launch_fill_bf16(void* out, size_t n, uint64_t seed, float mean, float std, 
 }
 
 template <int NT>
-static int launch_lm(const void* h, const void* E, int B, int V, int K, float* logits_out, float* pv, int* pi, int nparts, cudaStream_t s) {
+static int launch_lm(const void* h, const void* E, int B, int V, int K, float* logits_out, int ldl, int v_off, float* pv, int* pi, int nparts, cudaStream_t s) {
     constexpr int MT = NT * 8;
     constexpr int STAGE = LM_ROWS * 128 + MT * 128;
     constexpr int SM_PIPE = STAGE * LM_STAGES;
@@ -257,23 +296,31 @@ static int launch_lm(const void* h, const void* E, int B, int V, int K, float* l
         attr = true;
     }
     dim3 grid(nparts, (B + MT - 1) / MT);
-    kern<<<grid, 256, SMEM, s>>>((const __nv_bfloat16*)h, (const __nv_bfloat16*)E, B, V, K, logits_out, pv, pi);
+    kern<<<grid, 256, SMEM, s>>>((const __nv_bfloat16*)h, (const __nv_bfloat16*)E, B, V, K, logits_out, ldl, v_off, pv, pi);
     return launch_check(cudaGetLastError(), "lm_head");
 }
 
 int launch_lm_head_argmax(const void* h, const void* E, int B, int V, int K, float* logits_out, int32_t* next_out, void* workspace,
                           cudaStream_t s) {
+    return launch_lm_head_argmax_tp(h, E, B, V, K, logits_out, V, 0, next_out, workspace, nullptr, s);
+}
+
+// E points at this rank's first vocab row, V = its row count, v_off = that row's global index, ldl = logits row stride
+int launch_lm_head_argmax_tp(const void* h, const void* E, int B, int V, int K, float* logits_out, int ldl, int v_off, int32_t* next_out,
+                             void* workspace, const TpLm* tpl, cudaStream_t s) {
     const int nparts = (V + LM_ROWS - 1) / LM_ROWS;
     float* pv = (float*)workspace;
     int* pi = (int*)(pv + (size_t)B * nparts);
     int rc;
-    if (B <= 8) rc = launch_lm<1>(h, E, B, V, K, logits_out, pv, pi, nparts, s);
-    else if (B <= 16) rc = launch_lm<2>(h, E, B, V, K, logits_out, pv, pi, nparts, s);
-    else if (B <= 32) rc = launch_lm<4>(h, E, B, V, K, logits_out, pv, pi, nparts, s);
-    else rc = launch_lm<8>(h, E, B, V, K, logits_out, pv, pi, nparts, s);
+    if (B <= 8) rc = launch_lm<1>(h, E, B, V, K, logits_out, ldl, v_off, pv, pi, nparts, s);
+    else if (B <= 16) rc = launch_lm<2>(h, E, B, V, K, logits_out, ldl, v_off, pv, pi, nparts, s);
+    else if (B <= 32) rc = launch_lm<4>(h, E, B, V, K, logits_out, ldl, v_off, pv, pi, nparts, s);
+    else rc = launch_lm<8>(h, E, B, V, K, logits_out, ldl, v_off, pv, pi, nparts, s);
     if (rc) return rc;
     if (next_out) {
-        argmax_reduce_kernel<<<B, 256, 0, s>>>(pv, pi, nparts, next_out);
+        TpLm t = {};
+        if (tpl) t = *tpl; else { t.tp.size = 1; t.signal_flag = -1; }
+        argmax_reduce_kernel<<<B, 256, 0, s>>>(pv, pi, nparts, next_out, t);
         return launch_check(cudaGetLastError(), "argmax_reduce");
     }
     return WF_OK;

@@ -1,7 +1,18 @@
 // Cross-file launcher declarations used by the decode engine.
 #pragma once
 #include "linear_common.cuh"
+#include "tp_comm.cuh"
 namespace wf {
+// vocab-split LM head under tensor parallelism: where every rank's argmax candidate goes
+struct TpLm {
+    TpComm tp;
+    void* cand_peer[TP_MAX];   // {f32 logit, i32 index} [MB][TP_MAX] on every rank
+    int signal_flag;
+};
+int launch_lm_head_argmax_tp(const void* h, const void* E, int B, int V, int K, float* logits_out, int ldl, int v_off, int32_t* next_out,
+                             void* workspace, const TpLm* tpl, cudaStream_t s);
+int launch_advance_tp(int32_t* positions, int32_t* seq_lens, int32_t* tokens, int32_t* next, int B, int feed_back, int* step, const TpLm* tpl,
+                      cudaStream_t s);
 int launch_rmsnorm_quant(const void* x, const void* gamma, float eps, int M, int K, void* y_out, int8_t* q, float* scale_out,
                          int32_t* rowsum_out, cudaStream_t s, bool pdl);
 int rope_append(const void* qkv, int B, int H, int Hkv, int D, void* pool, int layers, int layer, int page_size,

@@ -30,11 +30,12 @@ constexpr int LS_THREADS = LS_CT + 32;
 struct SmallLinParams {
     GlueParams g;
     const uint8_t* w;
-    int N, K, KB;
+    int N, K, KB;         // K / KB: columns of this rank's weight slice
+    int k_off;            // first activation column of the slice
     long long T;
-    int act_stride;       // bytes per activation row in smem (K + 16: 16-B skew => conflict-free ldmatrix)
+    int act_stride;       // bytes per activation row in smem (g.K + 16: 16-B skew => conflict-free ldmatrix)
     int sacc_rbs;         // row-blocks of smem accumulators
-    float* acc_out;
+    TpDest dest;
     int acc_ld;
     float* lin_ascale;
     int32_t* lin_rowsum;
@@ -44,8 +45,8 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* ring = smem;                                         // LS_STAGES * LS_STAGE_BYTES
     unsigned char* acts = ring + LS_STAGES * LS_STAGE_BYTES;            // M * act_stride
-    __nv_bfloat16* ys = reinterpret_cast<__nv_bfloat16*>(acts + ((p.g.M * p.act_stride + 127) & ~127));   // K bf16
-    int* sacc = reinterpret_cast<int*>(reinterpret_cast<unsigned char*>(ys) + ((p.K * 2 + 127) & ~127));   // [rbl][8][16]
+    __nv_bfloat16* ys = reinterpret_cast<__nv_bfloat16*>(acts + ((p.g.M * p.act_stride + 127) & ~127));   // g.K bf16
+    int* sacc = reinterpret_cast<int*>(reinterpret_cast<unsigned char*>(ys) + ((p.g.K * 2 + 127) & ~127));   // [rbl][8][16]
     __shared__ __align__(8) uint64_t full_bar[LS_STAGES];
     __shared__ __align__(8) uint64_t empty_bar[LS_STAGES];
     __shared__ float fs[32];
@@ -86,6 +87,10 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
     } else {
         // ------------------------------------------------ consumer warps
         pdl_wait_prior();          // everything below reads what the previous phase wrote
+        if (p.g.wait_flag >= 0) {  // ... and, under tensor parallelism, what the peers wrote into this rank's buffers
+            if (warp == 0) tp_wait_flags_warp(p.g.tp, p.g.wait_flag);
+            group_bar<1, LS_CT>();
+        }
         glue_zero_duty<LS_CT>(p.g);
         for (int m = 0; m < M; ++m) {
             float sc; int rsum;
@@ -101,7 +106,7 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
             for (int j = 0; j < 4; ++j) acc[g][j] = 0;
         int cur_rb = -1;
         const int arow = min(lane & 7, M - 1);
-        const unsigned char* abase = acts + arow * p.act_stride + (lane >> 3) * 16;
+        const unsigned char* abase = acts + arow * p.act_stride + p.k_off + (lane >> 3) * 16;
 
         auto flush = [&](int rb) {
             if (rb < 0) return;
@@ -157,10 +162,14 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
                 const int rbl = i >> 7, m = (i >> 4) & 7, r = i & 15;
                 const int n = (rb_first + rbl) * 16 + r;
                 const int v = sacc[i];
-                if (m < M && n < p.N && v) red_add_f32(p.acc_out + (size_t)m * p.acc_ld + n, (float)v);
+                if (m < M && n < p.N && v) {
+                    // row-parallel linears under TP: the RED into every rank's accumulator IS the all-reduce
+                    for (int d = 0; d < p.dest.n; ++d) red_add_f32(p.dest.acc[d] + (size_t)m * p.acc_ld + n, (float)v);
+                }
             }
         }
     }
+    if (p.dest.signal_flag >= 0) tp_signal_grid_done(p.g.tp, p.dest.signal_flag, gridDim.x);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -173,6 +182,10 @@ __global__ void __launch_bounds__(GR_T) glue_rows_kernel(const GlueParams p) {
     __shared__ int is[32];
     pdl_launch_dependents();
     pdl_wait_prior();
+    if (p.wait_flag >= 0) {
+        if (threadIdx.x < 32) tp_wait_flags_warp(p.tp, p.wait_flag);
+        __syncthreads();
+    }
     glue_zero_duty<GR_T>(p);
     const int m = blockIdx.x;
     float sc; int rsum;
@@ -190,7 +203,7 @@ static void set_pdl(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* at, bool pdl) 
     cfg.numAttrs = pdl ? 1 : 0;
 }
 
-bool linear_small_fits(int M, int K) {
+bool linear_small_fits(int M, int K) {   // K = length of the full activation vector
     if (M < 1 || M > 8) return false;
     const size_t smem = (size_t)LS_STAGES * LS_STAGE_BYTES + (((size_t)M * (K + 16) + 127) & ~(size_t)127) + (((size_t)K * 2 + 127) & ~(size_t)127) + 16 * 1024;
     return smem <= 220 * 1024;
@@ -198,14 +211,14 @@ bool linear_small_fits(int M, int K) {
 
 int launch_linear_small(const SmallLinArgs& a, cudaStream_t s, bool pdl) {
     if (a.g.M < 1 || a.g.M > 8) { set_error("linear_small: M=%d outside 1..8", a.g.M); return WF_ERR_UNSUPPORTED; }
-    if (a.K % WF_QK || a.g.K != a.K) { set_error("linear_small: bad K"); return WF_ERR_INVALID; }
+    if (a.K % WF_QK || a.g.K % WF_QK || a.k_off % WF_QK || a.k_off + a.K > a.g.K) { set_error("linear_small: bad K / k_off"); return WF_ERR_INVALID; }
     SmallLinParams p;
     p.g = a.g;
-    p.w = a.w; p.N = a.N; p.K = a.K; p.KB = a.K / WF_QK;
+    p.w = a.w; p.N = a.N; p.K = a.K; p.KB = a.K / WF_QK; p.k_off = a.k_off;
     const int RB = (a.N + 15) / 16;
     p.T = (long long)p.KB * RB;
-    p.act_stride = a.K + 16;
-    p.acc_out = a.acc_out; p.acc_ld = a.acc_ld;
+    p.act_stride = a.g.K + 16;
+    p.dest = a.dest; p.acc_ld = a.acc_ld;
     p.lin_ascale = a.lin_ascale; p.lin_rowsum = a.lin_rowsum;
     int grid = sm_count();
     const long long min_tiles = 4;
@@ -214,8 +227,8 @@ int launch_linear_small(const SmallLinArgs& a, cudaStream_t s, bool pdl) {
     const long long max_tiles = (p.T + grid - 1) / grid + 1;
     p.sacc_rbs = (int)(max_tiles / p.KB) + 3;
     const size_t smem = (size_t)LS_STAGES * LS_STAGE_BYTES + (((size_t)a.g.M * p.act_stride + 127) & ~(size_t)127) +
-                        (((size_t)a.K * 2 + 127) & ~(size_t)127) + (size_t)p.sacc_rbs * 512;
-    if (smem > 220 * 1024) { set_error("linear_small: M*K=%d*%d does not fit in shared memory", a.g.M, a.K); return WF_ERR_UNSUPPORTED; }
+                        (((size_t)a.g.K * 2 + 127) & ~(size_t)127) + (size_t)p.sacc_rbs * 512;
+    if (smem > 220 * 1024) { set_error("linear_small: M*K=%d*%d does not fit in shared memory", a.g.M, a.g.K); return WF_ERR_UNSUPPORTED; }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(LS_THREADS);
@@ -236,6 +249,48 @@ int launch_glue_rows(const GlueParams& g, cudaStream_t s, bool pdl) {
     cudaLaunchAttribute at[1];
     set_pdl(cfg, at, pdl);
     return launch_check(cudaLaunchKernelEx(&cfg, glue_rows_kernel, g), "glue_rows");
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Tensor parallel phase D': h = relu^2(gate) * up of this rank's ffn slice (direct_inference_full.py:259, with the
+// reference's bf16 rounding points), stored into h_full of EVERY rank — the all-gather is the store itself.
+__global__ void __launch_bounds__(256) h_exchange_kernel(const HExchangeArgs a) {
+    pdl_launch_dependents();
+    pdl_wait_prior();
+    const int m = blockIdx.y;
+    const int k = (blockIdx.x * 256 + threadIdx.x) * 8;
+    if (k < a.ffn_local) {
+        const int rs = a.rowsum[m];
+        const float sa = a.ascale[m], wg = a.wscale[0], wu = a.wscale[1];
+        const float* arow = a.acc + (size_t)m * 2 * a.ffn_local;
+        const int ng = (k >> 4) * 32 + (k & 15);
+        const float4 g0 = ldcg_f4(arow + ng), g1 = ldcg_f4(arow + ng + 4);
+        const float4 u0 = ldcg_f4(arow + ng + 16), u1 = ldcg_f4(arow + ng + 20);
+        const float G[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float U[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+        float x[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float g = bf16_round(lin_value(G[i], rs, wg, sa));
+            const float u = bf16_round(lin_value(U[i], rs, wu, sa));
+            const float r = fmaxf(g, 0.f);
+            x[i] = bf16_round(bf16_round(r * r) * u);
+        }
+        const uint4 v = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
+        for (int d = 0; d < a.n_dst; ++d) *reinterpret_cast<uint4*>(a.dst[d] + (size_t)m * a.ffn_full + a.col0 + k) = v;
+    }
+    if (a.signal_flag >= 0) tp_signal_grid_done(a.tp, a.signal_flag, gridDim.x * gridDim.y);
+}
+
+int launch_h_exchange(const HExchangeArgs& a, cudaStream_t s, bool pdl) {
+    if (a.M < 1 || a.ffn_local % 16 || a.ffn_full % 8 || a.col0 % 8) { set_error("h_exchange: bad shape"); return WF_ERR_INVALID; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((a.ffn_local / 8 + 255) / 256, a.M);
+    cfg.blockDim = dim3(256);
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    set_pdl(cfg, at, pdl);
+    return launch_check(cudaLaunchKernelEx(&cfg, h_exchange_kernel, a), "h_exchange");
 }
 
 void linear_small_init_attrs() {

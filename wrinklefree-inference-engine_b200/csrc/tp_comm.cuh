@@ -1,0 +1,81 @@
+// Tensor-parallel exchange over NVLink peer memory (north-star item 6).
+//
+// One process per GPU.  Every rank owns one "comm" allocation (cudaMalloc, exported with cudaIpcGetMemHandle and
+// opened by the peers) that holds the buffers other ranks write INTO:
+//   attn_full  bf16 [MB][H*D]      all-gather target of the attention outputs  (each rank stores its heads into all)
+//   h_full     bf16 [MB][ffn]      all-gather target of relu^2(gate)*up
+//   acc_o      f32  [MB][hidden]   all-reduce target of the o-proj partial sums    (each rank REDs into all)
+//   acc_down   f32  [MB][hidden]   all-reduce target of the down-proj partial sums
+//   cand       {f32,i32} [MB][8]   per-rank argmax candidates of the vocab-split LM head
+//   flags      i32  [n_flags][8]   flags[id][r] = last step in which rank r finished exchange `id`
+// The collective is fused into the producing kernel: attention / linear CTAs store or RED straight into every
+// peer's buffer (st/red.global over NVLink), and the LAST CTA of the grid publishes the rank's flag to all peers
+// (membar.sys + st.release.sys).  The consuming kernel's prologue spins on its LOCAL flags (ld.acquire.sys).
+// All values exchanged by RED are integers < 2^24 held in fp32, so the all-reduce is exact and order-independent:
+// TP = N is bit-identical to TP = 1 (every rank quantises the gathered full vectors exactly like TP = 1 does).
+// Flag values are the 1-based decode step (a device-side counter the graph-captured step increments itself), so a
+// captured CUDA graph can be replayed without patching kernel parameters.
+#pragma once
+#include "common.cuh"
+
+namespace wf {
+
+constexpr int TP_MAX = 8;
+
+struct TpComm {
+    int rank, size;
+    unsigned char* peer[TP_MAX];   // base of every rank's comm buffer in THIS process' address space (peer[rank] = local)
+    size_t off_flags;              // byte offsets inside a comm buffer
+    const int* step;               // local device counter: number of completed decode steps
+    int* done_cnt;                 // local, zero-initialised: one grid-arrival counter per flag id
+};
+
+__device__ __forceinline__ int* tp_flag_ptr(const TpComm& c, int dst_rank, int id, int src_rank) {
+    return reinterpret_cast<int*>(c.peer[dst_rank] + c.off_flags) + id * TP_MAX + src_rank;
+}
+__device__ __forceinline__ void st_release_sys(int* p, int v) {
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_sys(const int* p) {
+    int v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ int ld_relaxed_gpu(const int* p) {
+    int v;
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Called by EVERY thread of EVERY CTA of the producing grid after its last peer store / RED.  The CTA that arrives
+// last publishes flag `id` = step + 1 on all ranks.  `nblocks` = total CTAs of the grid.
+__device__ __forceinline__ void tp_signal_grid_done(const TpComm& c, int id, int nblocks) {
+    if (c.size <= 1) return;
+    __threadfence_system();          // this thread's peer writes are visible system-wide ...
+    __syncthreads();                 // ... for all threads of the CTA, before the CTA's arrival
+    if (threadIdx.x == 0) {
+        const int prev = atomicAdd(c.done_cnt + id, 1);
+        if (prev == nblocks - 1) {
+            c.done_cnt[id] = 0;      // self-cleaning for the next step
+            __threadfence_system();
+            const int val = ld_relaxed_gpu(c.step) + 1;
+            for (int r = 0; r < c.size; ++r) st_release_sys(tp_flag_ptr(c, r, id, c.rank), val);
+        }
+    }
+}
+
+// Consumer side: returns when every rank has published flag `id` for the current step.  Call from ONE warp (all
+// 32 lanes), then synchronise the CTA.
+__device__ __forceinline__ void tp_wait_flags_warp(const TpComm& c, int id) {
+    if (c.size <= 1) return;
+    const int lane = threadIdx.x & 31;
+    const int want = ld_relaxed_gpu(c.step) + 1;
+    if (lane < c.size) {
+        const int* f = tp_flag_ptr(c, c.rank, id, lane);
+        while (ld_acquire_sys(f) < want) { __nanosleep(20); }
+    }
+    __syncwarp();
+    __threadfence_system();
+}
+
+}  // namespace wf

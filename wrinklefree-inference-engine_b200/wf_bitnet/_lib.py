@@ -95,6 +95,9 @@ SYMBOLS = {
     "wf_engine_decode_device": (_i, [_vp, _i, _i]),
     "wf_engine_sync": (_i, [_vp]),
     "wf_engine_stream": (_vp, [_vp]),
+    "wf_engine_tp_handle_bytes": (_sz, []),
+    "wf_engine_tp_export": (_i, [_vp, _vp]),
+    "wf_engine_tp_attach": (_i, [_vp, _vp]),
     "wf_engine_buffer": (_vp, [_vp, C.c_char_p]),
     "wf_engine_launches_per_step": (_i, [_vp]),
     "wf_engine_time_kernel": (_i, [_vp, C.c_char_p, _i, _i, C.POINTER(_f)]),

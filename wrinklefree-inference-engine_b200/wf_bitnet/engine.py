@@ -50,12 +50,15 @@ NORMS = ("input_layernorm", "post_attention_layernorm", "attn_sub_norm", "ffn_su
 
 
 class Engine:
-    def __init__(self, cfg: EngineConfig):
+    def __init__(self, cfg: EngineConfig, tp_rank: int = 0, tp_size: int = 1):
+        """tp_size > 1: this process holds shard tp_rank of a tensor-parallel engine; weights passed to load_weights
+        must already be this rank's shard (wf_bitnet.tp.shard_weights) and wf_bitnet.tp.attach() must run before decode."""
         _lib.require_gpu()
         self.cfg = cfg
+        self.tp_rank, self.tp_size = tp_rank, tp_size
         max_pages = cfg.max_pages or cfg.max_batch * (cfg.max_seq // cfg.page_size)
         c = _CConfig(cfg.hidden, cfg.layers, cfg.heads, cfg.kv_heads, cfg.head_dim, cfg.ffn, cfg.vocab, cfg.rope_theta, cfg.eps,
-                     cfg.max_seq, cfg.page_size, cfg.max_batch, max_pages, 0, 1)
+                     cfg.max_seq, cfg.page_size, cfg.max_batch, max_pages, tp_rank, tp_size)
         h = C.c_void_p()
         check(lib().wf_engine_create(C.byref(c), C.byref(h)))
         self._h = h
@@ -94,6 +97,17 @@ class Engine:
             check(lib().wf_engine_set_tensor(self._h, layer, name.encode(), t.data_ptr(), t.numel(), 0))
         else:
             check(lib().wf_engine_set_tensor(self._h, layer, name.encode(), t.data_ptr(), t.numel(), 1))
+
+    # ------------------------------------------------------------------ tensor parallel
+    def tp_export(self) -> bytes:
+        n = int(lib().wf_engine_tp_handle_bytes())
+        buf = C.create_string_buffer(n)
+        check(lib().wf_engine_tp_export(self._h, buf))
+        return buf.raw
+
+    def tp_attach(self, handles: Sequence[bytes]) -> None:
+        blob = b"".join(handles)
+        check(lib().wf_engine_tp_attach(self._h, C.c_char_p(blob)))
 
     def init_synthetic(self, seed: int = 1234) -> None:
         check(lib().wf_engine_init_synthetic(self._h, seed))
