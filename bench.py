@@ -42,6 +42,112 @@ KV_BYTES_PER_TOKEN_LAYER = 2 * 5 * 128 * 2
 LM_HEAD_BYTES = 128256 * 2560 * 2
 METRIC = "decode tok/s, BitNet-2B-4T-shaped, batch 64, 4K paged KV, 1 B200 (replicas for N>1)"
 
+# tensor-parallel workloads (BASELINE.json configs[3], configs[4]): N GPUs = TP degree, strong scaling
+TP_WORKLOADS = {
+    "8b_bs1": dict(shape="llama3_8b", batch=1, ctx=512, name="BASELINE.json configs[3]: Llama-3-8B-shaped 1.58-bit model, random-init, batch=1 decode, 512-token context, TP = n_gpus"),
+    "8b_bs32": dict(shape="llama3_8b", batch=32, ctx=2048, name="BASELINE.json configs[3]: Llama-3-8B-shaped 1.58-bit model, random-init, batch=32 decode, 2K-token paged KV, TP = n_gpus"),
+    "70b_bs16": dict(shape="llama3_70b", batch=16, ctx=8192, name="BASELINE.json configs[4]: Llama-3-70B-shaped 1.58-bit model, random-init, batch=16 decode, 8K-token paged KV, TP = n_gpus"),
+}
+
+
+def run_gpu_tp(args):
+    """Tensor-parallel decode: one rank per GPU, the model sharded over all ranks (wf_bitnet.tp), strong scaling."""
+    import torch.distributed as dist
+    from wf_bitnet import _lib, tp
+    from wf_bitnet.engine import Engine, EngineConfig
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    wl = TP_WORKLOADS[args.workload]
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    _lib.require_gpu()
+    batch, ctx = wl["batch"], wl["ctx"]
+    K, W = args.steps, max(3, args.warmup)
+    page = 16
+    extra = ((2 * (W + K) + 16 + page - 1) // page) * page + page
+    cfg = getattr(EngineConfig, wl["shape"])(max_seq=ctx + extra, page_size=page, max_batch=batch)
+    eng = Engine(cfg, tp_rank=rank, tp_size=world)
+    eng.init_synthetic(4321)                      # same seed on every rank: replicated tensors agree, shards differ by rank
+    if world > 1:
+        tp.attach(eng)
+    for slot in range(batch):
+        eng.set_context(slot, ctx, fill_random=True)
+    tokens = np.random.default_rng(0).integers(0, cfg.vocab, size=batch).astype(np.int32)
+    ext = torch.cuda.ExternalStream(eng.stream)
+
+    def barrier():
+        eng.sync()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    tokens = eng.decode(tokens)
+    for _ in range(W):
+        eng.decode_device(batch)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(ext)
+    for _ in range(K):
+        eng.decode_device(batch)
+    e1.record(ext)
+    e1.synchronize()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    launches = eng.launches_per_step()
+    for slot in range(batch):
+        eng.set_context(slot, ctx, fill_random=False)
+    barrier()
+    for _ in range(W):
+        tokens = eng.decode(tokens)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        tokens = eng.decode(tokens)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+    eng.close()
+    t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, e2e_ms = float(t[0]), float(t[1])
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        hd, ffn, hid, L = cfg.head_dim, cfg.ffn, cfg.hidden, cfg.layers
+        w_bytes = L * ((cfg.heads + 2 * cfg.kv_heads) * hd * hid + hid * cfg.heads * hd + 3 * ffn * hid) // 4
+        kv_bytes = 2 * cfg.kv_heads * hd * 2 * L * batch * (ctx + 1)
+        lm_bytes = cfg.vocab * hid * 2
+        per_gpu = (w_bytes + kv_bytes + lm_bytes) / world
+        ms_step = ms_total / K
+        achieved = per_gpu / (ms_step * 1e-3) / 1e9
+        line = {
+            "metric": f"decode tok/s, {wl['shape']}-shaped 1.58-bit model, batch {batch}, {ctx}-token KV, TP={world}", "value": batch * K / (ms_total * 1e-3),
+            "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "i8 x i2 -> i32, bf16 glue", "data": "synthetic",
+            "config": {"workload": wl["name"], "batch": batch, "ctx": ctx, "page_size": page, "tp": world,
+                       "l2": "inputs larger than L2: every step streams the rank's weight shard, vocab slice and KV heads",
+                       "multi_gpu": "tensor parallel: q|k|v, gate|up by output rows, o/down by input columns, KV by head; all-gather/all-reduce = NVLink peer stores/REDs fused into the attention and linear kernels (no NCCL on the data path)",
+                       "graph": "CUDA graph replay, 1 graph launch per step per rank"},
+            "clocks": clocks,
+            "e2e": {"value": batch * K / (e2e_ms * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": 4 * batch * world, "d2h_bytes_per_step": 4 * batch * world,
+                    "call": "wf_engine_decode(host token ids) -> host greedy next ids on every rank, sync every step"},
+            "gpu_launches": launches * K * world, "gpu_launches_per_step": launches,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "whole decode step, per GPU (weight shard + vocab slice + KV heads streamed once per step)",
+                         "algorithmic_bytes_per_launch": per_gpu, "avg_launch_ms": ms_step},
+            "cpu_baseline": None,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
 
 def measured_peaks():
     f = ROOT / "MEASURED_PEAKS.json"
@@ -369,10 +475,15 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="bs64", choices=["bs64", "bs1"])
+    ap.add_argument("--workload", default="bs64", choices=["bs64", "bs1"] + sorted(TP_WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-aux", action="store_true", help="skip the batch-1 aux measurement")
     args = ap.parse_args()
+    if args.workload in TP_WORKLOADS:
+        if args.impl == "reference":
+            print(json.dumps({"impl": "reference", "unavailable": "the reference arm is defined for the 2B workloads (bs64 / bs1) only"}))
+            return 0
+        return run_gpu_tp(args)
     if args.impl == "reference":
         return run_reference(args)
     return run_gpu(args)

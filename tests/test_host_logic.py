@@ -102,3 +102,20 @@ def test_oracle_model_runs_tiny_config():
     m2 = OM.OracleModel(cfg, w, use_ref=True)          # reference SIMD kernel inside the same forward
     toks2, _ = m2.generate_greedy([1, 2, 3], 4)
     assert toks2 == toks
+
+
+def test_act_scale_needs_no_fp64():
+    """csrc/common.cuh act_scale_from_absmax evaluates the reference's scale = fl32(fl64(max) / 127.0)
+    (tests/test_bitnet_core.py:139-146) in fp32 only.  127 = 2^7 - 1 makes the quotient's expansion 7-periodic, so the
+    double rounding can never differ from one fp32 rounding; and (double)max < 1e-6 <=> max <= fl32(1e-6)."""
+    import numpy as np
+    rng = np.random.default_rng(0)
+    bits = rng.integers(0x00800000, 0x7F000000, size=4_000_000, dtype=np.int64).astype(np.uint32)
+    a = np.concatenate([bits.view(np.float32), np.arange(1, 300000, dtype=np.float32) * np.float32(127.0),
+                        np.float32(2.0) ** np.arange(-100, 100, dtype=np.float32), np.linspace(1e-7, 1e-5, 200001).astype(np.float32)])
+    ref = (a.astype(np.float64) / 127.0).astype(np.float32)
+    one = a / np.float32(127.0)
+    assert np.array_equal(ref, one)
+    lim = np.float32(1e-6)
+    assert float(lim) < 1e-6 < float(np.nextafter(lim, np.float32(1)))
+    assert np.array_equal(a.astype(np.float64) < 1e-6, a <= lim)

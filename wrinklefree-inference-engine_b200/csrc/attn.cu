@@ -59,6 +59,7 @@ struct AttnParams {
     void* out_peer[TP_MAX];
     int n_out, out_ld, out_col0, signal_flag;
     TpComm tp;
+    unsigned long long* trace;
 };
 
 // final output element (b, local head h, d): local buffer, or the attn_full buffer of every rank (the all-gather)
@@ -85,25 +86,60 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
     const int chunk = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
     const int g = lane >> 2, t = lane & 3;
 
+    const bool tr = FUSED && p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0;
+    if (tr) p.trace[0] = gtimer();
     if (FUSED) pdl_launch_dependents();
+    // Everything up to griddepcontrol.wait only touches state that is stable during a decode step (sequence lengths, block
+    // table, the KV of OLD tokens): the first pipeline stages of this warp's K/V stream are in flight before the producer
+    // of q (the qkv linear / the RoPE kernel) has finished.  Only the 16-token block that receives the new token waits.
+    const int seq_len = p.seq_lens[b];
+    const int nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
+    const int blk_pos = (seq_len - 1) / AT_BLK;          // block of the token appended in this step (pos = seq_len - 1)
+    const int blk0 = chunk * p.chunk_blocks;
+    const bool active = !(blk0 >= nblocks && chunk != 0);
+    const int blk1 = min(nblocks, blk0 + p.chunk_blocks);
+    const int my_n = active ? (blk1 - blk0 - warp + AT_WARPS - 1) / AT_WARPS : 0;   // blocks blk0 + warp + 4*i
+    unsigned char* wsm = smem + warp * (AT_STAGES * AT_STAGE_BYTES);
+    const int32_t* bt = p.block_table + (size_t)b * p.max_blocks;
+
+    auto issue = [&](int i) {   // i-th block of this warp -> stage i % AT_STAGES
+        if (i < my_n) {
+            const int blk = blk0 + warp + AT_WARPS * i;
+            const int tok0 = blk * AT_BLK;
+            const int page = bt[tok0 / p.page_size];
+            const int slot0 = tok0 % p.page_size;
+            const __nv_bfloat16* kb = p.pool + kv_block_offset(page, p.layers, p.layer, 0, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
+            const __nv_bfloat16* vb = p.pool + kv_block_offset(page, p.layers, p.layer, 1, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
+            unsigned char* ks = wsm + (i % AT_STAGES) * AT_STAGE_BYTES;
+            unsigned char* vs = ks + AT_BLK * AT_ROW;
+            const int valid = seq_len - tok0;   // tokens >= valid are zero-filled (pool slots may be uninitialised)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int gi = lane + 32 * j;
+                const int r = gi >> 4, c = gi & 15;
+                const int dst = r * AT_ROW + ((c ^ (r & 7)) << 4);
+                const int nb = (r < valid) ? 16 : 0;
+                cp_async16_zfill(ks + dst, reinterpret_cast<const unsigned char*>(kb) + gi * 16, nb);
+                cp_async16_zfill(vs + dst, reinterpret_cast<const unsigned char*>(vb) + gi * 16, nb);
+            }
+        }
+        cp_async_commit();
+    };
+    int pre = 0;   // stages issued before the dependency wait
+    while (pre < AT_STAGES - 1 && (pre >= my_n || blk0 + warp + AT_WARPS * pre < blk_pos)) { issue(pre); ++pre; }
+
     pdl_wait_prior();
+    if (tr) p.trace[1] = gtimer();
     if (FUSED && p.zero0) {
         const int nb = gridDim.x * gridDim.y * gridDim.z;
         const int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
         for (int i = (bid * AT_WARPS * 32 + tid) * 4; i < p.zero0_n; i += nb * AT_WARPS * 32 * 4)
             *reinterpret_cast<float4*>(p.zero0 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    const int seq_len = p.seq_lens[b];
-    const int nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
-    const int blk0 = chunk * p.chunk_blocks;
-    if (blk0 >= nblocks && !(chunk == 0)) {
+    if (!active) {
         if (FUSED && p.signal_flag >= 0) tp_signal_grid_done(p.tp, p.signal_flag, gridDim.x * gridDim.y * gridDim.z);
         return;
     }
-    const int blk1 = min(nblocks, blk0 + p.chunk_blocks);
-    const int my_n = (blk1 - blk0 - warp + AT_WARPS - 1) / AT_WARPS;   // blocks blk0 + warp + 4*i
-    unsigned char* wsm = smem + warp * (AT_STAGES * AT_STAGE_BYTES);
-    const int32_t* bt = p.block_table + (size_t)b * p.max_blocks;
 
     // ---- Q fragments (rows g < G valid; rows 8..15 are zero padding)
     uint32_t qa[8][2];
@@ -127,26 +163,37 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
         {
             const float wq = p.qkv_wscale[0];
             const float* hq = arow + ((size_t)kvh * p.G + g) * AT_D;
+            // all 16 loads are issued before the first use: one L2 round trip instead of sixteen
+            float2 xa[8], xb[8];
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) {
-#pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    const int d = ks * 16 + half * 8 + 2 * t;   // < 64; partner at d + 64
-                    float o1[2], o2[2];
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        float x1 = 0.f, x2 = 0.f;
-                        if (g < p.G) {
-                            x1 = bf16_round(lin_value(ldcg_f(hq + d + e), rs, wq, sa));
-                            x2 = bf16_round(lin_value(ldcg_f(hq + d + e + 64), rs, wq, sa));
-                        }
-                        const float c = __bfloat162float(ct[d + e]), s = __bfloat162float(st[d + e]);
-                        o1[e] = bf16_round(x1 * c) - bf16_round(x2 * s);
-                        o2[e] = bf16_round(x1 * s) + bf16_round(x2 * c);
-                    }
-                    qa[ks][half] = pack_bf16x2(o1[0], o1[1]);
-                    qa[ks + 4][half] = pack_bf16x2(o2[0], o2[1]);
+            for (int i = 0; i < 8; ++i) {
+                const int d = (i >> 1) * 16 + (i & 1) * 8 + 2 * t;   // < 64; partner at d + 64
+                xa[i] = make_float2(0.f, 0.f);
+                xb[i] = make_float2(0.f, 0.f);
+                if (g < p.G) {
+                    asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(xa[i].x), "=f"(xa[i].y) : "l"(hq + d));
+                    asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(xb[i].x), "=f"(xb[i].y) : "l"(hq + d + 64));
                 }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int ks = i >> 1, half = i & 1;
+                const int d = ks * 16 + half * 8 + 2 * t;
+                const float a[2] = {xa[i].x, xa[i].y}, bq[2] = {xb[i].x, xb[i].y};
+                float o1[2], o2[2];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    float x1 = 0.f, x2 = 0.f;
+                    if (g < p.G) {
+                        x1 = bf16_round(lin_value(a[e], rs, wq, sa));
+                        x2 = bf16_round(lin_value(bq[e], rs, wq, sa));
+                    }
+                    const float c = __bfloat162float(ct[d + e]), sn = __bfloat162float(st[d + e]);
+                    o1[e] = bf16_round(x1 * c) - bf16_round(x2 * sn);
+                    o2[e] = bf16_round(x1 * sn) + bf16_round(x2 * c);
+                }
+                qa[ks][half] = pack_bf16x2(o1[0], o1[1]);
+                qa[ks + 4][half] = pack_bf16x2(o2[0], o2[1]);
             }
         }
         // the CTA whose chunk holds the new token appends k (RoPE'd) and v before it streams that block
@@ -176,37 +223,13 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
         }
     }
 
-    auto issue = [&](int i) {   // i-th block of this warp -> stage i % AT_STAGES
-        if (i < my_n) {
-            const int blk = blk0 + warp + AT_WARPS * i;
-            const int tok0 = blk * AT_BLK;
-            const int page = bt[tok0 / p.page_size];
-            const int slot0 = tok0 % p.page_size;
-            const __nv_bfloat16* kb = p.pool + kv_block_offset(page, p.layers, p.layer, 0, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
-            const __nv_bfloat16* vb = p.pool + kv_block_offset(page, p.layers, p.layer, 1, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
-            unsigned char* ks = wsm + (i % AT_STAGES) * AT_STAGE_BYTES;
-            unsigned char* vs = ks + AT_BLK * AT_ROW;
-            const int valid = seq_len - tok0;   // tokens >= valid are zero-filled (pool slots may be uninitialised)
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int gi = lane + 32 * j;
-                const int r = gi >> 4, c = gi & 15;
-                const int dst = r * AT_ROW + ((c ^ (r & 7)) << 4);
-                const int nb = (r < valid) ? 16 : 0;
-                cp_async16_zfill(ks + dst, reinterpret_cast<const unsigned char*>(kb) + gi * 16, nb);
-                cp_async16_zfill(vs + dst, reinterpret_cast<const unsigned char*>(vb) + gi * 16, nb);
-            }
-        }
-        cp_async_commit();
-    };
-
+    if (tr) p.trace[2] = gtimer();
     float o[16][4];
 #pragma unroll
     for (int j = 0; j < 16; ++j) { o[j][0] = 0.f; o[j][1] = 0.f; o[j][2] = 0.f; o[j][3] = 0.f; }
     float m_run = -INFINITY, l_run = 0.f;   // row g (replicated over the 4 lanes of a group)
 
-#pragma unroll
-    for (int s = 0; s < AT_STAGES - 1; ++s) issue(s);
+    for (int s = pre; s < AT_STAGES - 1; ++s) issue(s);
 
     for (int i = 0; i < my_n; ++i) {
         issue(i + AT_STAGES - 1);
@@ -283,6 +306,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
     }
     cp_async_wait<0>();
     __syncthreads();
+    if (tr) p.trace[3] = gtimer();
 
     // ---- merge the 4 warps through shared memory: [warp][G][D] fp32 + [warp][G][2]
     float* mo = reinterpret_cast<float*>(smem);                       // AT_WARPS * 8 * 128 floats = 16 KB
@@ -322,6 +346,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
             }
         }
     }
+    if (tr) p.trace[4] = gtimer();
     if (FUSED && !p.direct) {
         // the last chunk to arrive for this (sequence, kv head) merges all of them — no separate merge launch
         __shared__ int s_last;
@@ -337,23 +362,51 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
         __syncthreads();
         if (s_last) {
             __threadfence();
+            // (m, l) of every (head, chunk) pair: one parallel round of loads into smem, factors computed once
+            float* fml = reinterpret_cast<float*>(smem);            // [G][nch][2] -> factor, unused
+            float* fL = fml + 2 * 8 * p.max_chunks;                 // [G] total l
+            for (int i = tid; i < p.G * nch; i += AT_WARPS * 32) {
+                const int hh = i / nch, c = i - hh * nch;
+                const size_t slot = ((size_t)b * p.H + kvh * p.G + hh) * p.max_chunks + c;
+                float2 ml;
+                asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(ml.x), "=f"(ml.y) : "l"(p.part_ml + slot * 2));
+                fml[(hh * p.max_chunks + c) * 2] = ml.x;
+                fml[(hh * p.max_chunks + c) * 2 + 1] = ml.y;
+            }
+            __syncthreads();
+            if (tid < p.G) {
+                const int hh = tid;
+                float M = -INFINITY;
+                for (int c = 0; c < nch; ++c) M = fmaxf(M, fml[(hh * p.max_chunks + c) * 2]);
+                float L = 0.f;
+                for (int c = 0; c < nch; ++c) {
+                    const float mc = fml[(hh * p.max_chunks + c) * 2];
+                    const float f = (mc == -INFINITY) ? 0.f : exp2f(mc - M);
+                    L += fml[(hh * p.max_chunks + c) * 2 + 1] * f;
+                    fml[(hh * p.max_chunks + c) * 2] = f;
+                }
+                fL[hh] = L;
+            }
+            __syncthreads();
             const int d = tid;
             for (int hh = 0; hh < p.G; ++hh) {
                 const int h = kvh * p.G + hh;
                 const size_t base = ((size_t)b * p.H + h) * p.max_chunks;
-                float M = -INFINITY;
-                for (int c = 0; c < nch; ++c) M = fmaxf(M, ldcg_f(p.part_ml + (base + c) * 2));
-                float L = 0.f, O = 0.f;
-                for (int c = 0; c < nch; ++c) {
-                    const float mc = ldcg_f(p.part_ml + (base + c) * 2);
-                    const float f = (mc == -INFINITY) ? 0.f : exp2f(mc - M);
-                    L += ldcg_f(p.part_ml + (base + c) * 2 + 1) * f;
-                    O += ldcg_f(p.part_o + (base + c) * AT_D + d) * f;
+                float O = 0.f;
+                for (int c0 = 0; c0 < nch; c0 += 8) {   // 8 independent loads in flight
+                    float v[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) v[u] = (c0 + u < nch) ? ldcg_f(p.part_o + (base + c0 + u) * AT_D + d) : 0.f;
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (c0 + u < nch) O += v[u] * fml[(hh * p.max_chunks + c0 + u) * 2];
                 }
+                const float L = fL[hh];
                 attn_store(p, b, h, d, (L > 0.f) ? O / L : 0.f);
             }
         }
     }
+    if (tr) p.trace[5] = gtimer();
     if (FUSED && p.signal_flag >= 0) tp_signal_grid_done(p.tp, p.signal_flag, gridDim.x * gridDim.y * gridDim.z);
     if (!FUSED) pdl_launch_dependents();
 }
@@ -487,7 +540,8 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     int chunks = (int)((want + pairs - 1) / pairs);
     if (chunks < 1) chunks = 1;
     int chunk_blocks = (max_blocks16 + chunks - 1) / chunks;
-    if (chunk_blocks < 4) chunk_blocks = 4;
+    // a chunk split costs a partial write + an atomic + a merge (~4 us of dependent round trips): never split below 512 tokens
+    if (chunk_blocks < 32) chunk_blocks = 32;
     chunk_blocks = (chunk_blocks + 3) & ~3;
     const int nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
     p.chunk_blocks = chunk_blocks;
@@ -572,7 +626,7 @@ int attn_decode_fused(const FusedAttnArgs& a, cudaStream_t s, bool pdl) {
     p.merge_cnt = a.merge_cnt; p.zero0 = a.zero0; p.zero0_n = a.zero0_n;
     p.n_out = a.n_out < 1 ? 1 : a.n_out; p.out_ld = a.out_ld > 0 ? a.out_ld : a.H * AT_D; p.out_col0 = a.out_col0;
     for (int r = 0; r < TP_MAX; ++r) p.out_peer[r] = a.out_peer[r];
-    p.signal_flag = a.n_out > 1 ? a.signal_flag : -1; p.tp = a.tp;
+    p.signal_flag = a.n_out > 1 ? a.signal_flag : -1; p.tp = a.tp; p.trace = a.trace;
     return launch_paged_decode_attn(p, a.max_seq_hint, a.ws, a.ws_bytes, s, pdl);
 }
 

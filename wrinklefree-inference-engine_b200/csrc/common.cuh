@@ -211,13 +211,40 @@ __device__ __forceinline__ int block_sum_i(int v, int* scratch) {
 // The reference's activation quantiser (tests/test_bitnet_core.py:139-146):
 //   scale = fl32( double(max) / 127.0 )  (1.0 substituted when max < 1e-6);  q = clamp(rint(x / scale), -128, 127)
 // true IEEE division, ties-to-even; a reciprocal multiply would differ by one LSB on some inputs.
+// Evaluated WITHOUT fp64 (the B200 fp64 pipe would put ~1 us on the decode critical path per normalisation):
+//  * 127 = 2^7 - 1, so the binary expansion of max/127 is periodic with period 7: it can never sit within 2^-53 of an
+//    fp32 rounding boundary unless it is exact, hence fl32(fl64(max/127)) == fl32(max/127) == __fdiv_rn(max, 127.f);
+//  * (double)max < 1e-6  <=>  max <= fl32(1e-6) = 0x358637BD (the largest float below 1e-6).
 __device__ __forceinline__ float act_scale_from_absmax(float amax) {
-    double mv = (double)amax;
-    if (mv < 1e-6) mv = 1.0;
-    return (float)(mv / 127.0);
+    if (amax <= 1e-6f) amax = 1.0f;
+    return __fdiv_rn(amax, 127.0f);
 }
-__device__ __forceinline__ int quant_i8(float x, float scale) {
-    float r = rintf(__fdiv_rn(x, scale));
+// q = clamp(rint(x / scale), -128, 127) with x / scale CORRECTLY ROUNDED (true IEEE division, as the reference's
+// torch x / scale) for a divisor that is shared by a whole row: Markstein's correction.  With y = RN(1/scale) and
+// q0 = RN(x*y), q = RN(q0 + RN(x - scale*q0)*y) is the correctly rounded quotient unless scale's significand is all
+// ones (then: plain __fdiv_rn).  3 instructions per element instead of a ~40-instruction division subroutine — the
+// quantisation pass sits on the decode critical path of every linear.
+struct QDiv {
+    float scale, rcp;
+    int slow;
+};
+__device__ __forceinline__ QDiv make_qdiv(float scale) {
+    QDiv d;
+    d.scale = scale;
+    d.rcp = __frcp_rn(scale);
+    d.slow = ((__float_as_uint(scale) & 0x007fffffu) == 0x007fffffu) ? 1 : 0;
+    return d;
+}
+__device__ __forceinline__ int quant_i8(float x, const QDiv& d) {
+    float q;
+    if (d.slow) {
+        q = __fdiv_rn(x, d.scale);
+    } else {
+        const float q0 = __fmul_rn(x, d.rcp);
+        const float e = __fmaf_rn(-d.scale, q0, x);
+        q = __fmaf_rn(e, d.rcp, q0);
+    }
+    float r = rintf(q);
     r = fminf(fmaxf(r, -128.f), 127.f);
     return (int)r;
 }

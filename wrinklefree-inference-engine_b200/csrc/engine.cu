@@ -48,6 +48,7 @@ struct wf_engine {
     int* d_step = nullptr;
     __nv_bfloat16* h_full = nullptr;
     int v_lo = 0, v_n = 0;                   // this rank's vocab slice of the tied LM head
+    unsigned long long* trace = nullptr;     // WF_TRACE=1: 16 globaltimer stamps per linear_small launch
     // kv
     __nv_bfloat16* pool = nullptr;
     int max_blocks = 0;
@@ -70,6 +71,7 @@ struct wf_engine {
     bool finalized = false;
     bool pdl = false;
     int linear_algo = 0;
+    int hx = 1;              // relu^2(gate)*up in its own small kernel instead of every down-proj CTA's prologue (WF_HX=0 to fold it back)
     int fused = 1;           // 1: phase kernels (linear_small / glue_rows + gemm_oneshot / fused attention); 0: one kernel per op
     // fused path state: raw fp32 accumulators of the four linears, their per-token activation scale / Sigma a,
     // a second hidden buffer (residual ping-pong) and the attention merge counters
@@ -205,10 +207,12 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
     const int MB = c.max_batch;
     const int T = e->tp.size;
     const bool tp = T > 1;
+    const bool hx = tp || e->hx;   // relu^2*up as its own small kernel (always under TP; optional otherwise)
     float* asc[4] = {e->lin_asc, e->lin_asc + MB, e->lin_asc + 2 * MB, e->lin_asc + 3 * MB};
     int32_t* rs[4] = {e->lin_rs, e->lin_rs + MB, e->lin_rs + 2 * MB, e->lin_rs + 3 * MB};
     __nv_bfloat16 *hA = e->hid, *hB = e->hid2;
     int rc;
+    int trace_slot = 0;
     auto local_dest = [&](float* acc) { TpDest d = {}; d.n = 1; d.acc[0] = acc; d.signal_flag = -1; return d; };
     auto all_dest = [&](size_t off, int flag) {
         TpDest d = {};
@@ -219,6 +223,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
     // one linear phase: prologue over the full activation vector of length Kfull, GEMV/GEMM over this rank's K columns
     auto phase = [&](GlueParams g, const uint8_t* w, int N, int Kfull, int K, int k_off, const TpDest& dest, int slot, bool first) -> int {
         g.M = B; g.K = Kfull; g.eps = c.eps; g.tp = e->tp;
+        if (e->trace) { g.trace = e->trace + (size_t)trace_slot * 32; ++trace_slot; }
         if (B <= 8 && linear_small_fits(B, Kfull)) {
             SmallLinArgs a;
             a.g = g; a.w = w; a.N = N; a.K = K; a.k_off = k_off; a.dest = dest; a.acc_ld = N; a.lin_ascale = asc[slot]; a.lin_rowsum = rs[slot];
@@ -261,6 +266,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
             a.cos_tab = e->cos_tab; a.sin_tab = e->sin_tab; a.max_pos = c.max_seq;
             a.merge_cnt = e->merge_cnt; a.zero0 = e->acc_down; a.zero0_n = B * e->hidden;
             a.max_seq_hint = e->attn_seq_hint; a.ws = e->ws_attn; a.ws_bytes = e->ws_attn_bytes;
+            if (e->trace) a.trace = e->trace + (size_t)32 * (4 * c.layers + 4 + l);
             if ((rc = attn_decode_fused(a, s, pdl))) return rc;
         }
         // ---- C: attn_sub_norm over the FULL attention vector -> o (this rank's input columns; RED = all-reduce)
@@ -278,18 +284,18 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
             if ((rc = phase(g, L.gu, 2 * e->ffn, e->hidden, e->hidden, 0, local_dest(e->acc_gu), 2, false))) return rc;
         }
         // ---- D' (TP only): relu^2(gate)*up of the local slice -> h_full of every rank
-        if (tp) {
+        if (hx) {
             HExchangeArgs h = {};
             h.acc = e->acc_gu; h.M = B; h.ffn_local = e->ffn; h.ffn_full = e->ffn_full; h.col0 = e->tp.rank * e->ffn;
             h.rowsum = rs[2]; h.ascale = asc[2]; h.wscale = L.scales + 4;
-            h.n_dst = T; h.signal_flag = fD; h.tp = e->tp;
+            h.n_dst = T; h.signal_flag = tp ? fD : -1; h.tp = e->tp;
             for (int r = 0; r < T; ++r) h.dst[r] = reinterpret_cast<__nv_bfloat16*>(e->tp.peer[r] + e->off_h);
             if ((rc = launch_h_exchange(h, s, pdl))) return rc;
         }
         // ---- E: relu^2(gate)*up -> ffn_sub_norm over the FULL ffn vector -> down (RED = all-reduce)
         {
             GlueParams g = {};
-            if (tp) { g.mode = GL_PLAIN; g.src = e->h_full; g.wait_flag = fD; }
+            if (hx) { g.mode = GL_PLAIN; g.src = e->h_full; g.wait_flag = tp ? fD : -1; }
             else {
                 g.mode = GL_RELU2; g.acc = e->acc_gu; g.acc_ld = 2 * e->ffn; g.wait_flag = -1;
                 g.acc_rowsum = rs[2]; g.acc_ascale = asc[2]; g.acc_wscale = L.scales + 4;
@@ -425,6 +431,7 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     const char* env_fused = getenv("WF_FUSED");
     e->fused = env_fused ? atoi(env_fused) != 0 : 1;
     if (T > 1) e->fused = 1;                   // the exchanges live in the phase kernels
+    { const char* x = getenv("WF_HX"); if (x) e->hx = atoi(x) != 0; }
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
     int rc = WF_OK;
     auto fail = [&](int r) { wf_engine_destroy(e); return r; };
@@ -527,6 +534,10 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
         if ((rc = dalloc(e, &a, e->ws_lin_bytes)) || (rc = dalloc(e, &b2, e->ws_attn_bytes)) || (rc = dalloc(e, &c2, e->ws_lm_bytes))) return fail(rc);
         e->ws_lin = a; e->ws_attn = b2; e->ws_lm = c2;
         if (cuda_check(cudaMemset(e->ws_lin, 0, e->ws_lin_bytes), "ws memset")) return fail(WF_ERR_CUDA);
+    }
+    if (getenv("WF_TRACE") && atoi(getenv("WF_TRACE"))) {
+        if ((rc = dalloc(e, &e->trace, (size_t)32 * (5 * c.layers + 8)))) return fail(rc);
+        cudaMemset(e->trace, 0, (size_t)32 * (5 * c.layers + 8) * 8);
     }
     e->h_block_table.assign((size_t)B * e->max_blocks, -1);
     e->h_pos.assign(B, 0);
@@ -792,6 +803,7 @@ extern "C" void* wf_engine_buffer(wf_engine* e, const char* name) {
     if (n == "pool") return e->pool;
     if (n == "block_table") return e->d_block_table;
     if (n == "q8") return e->q8;
+    if (n == "trace") return e->trace;
     return nullptr;
 }
 

@@ -47,7 +47,13 @@ struct GlueParams {
     // tensor parallel: the source of this phase was produced by an exchange — wait for every rank's flag first
     int wait_flag;                  // flag id, -1 = none
     TpComm tp;
+    unsigned long long* trace;      // timeline taps (WF_TRACE=1 debugging): 8 globaltimer stamps per launch, or null
 };
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 // where a linear's partial sums go: the local accumulator, or (row-parallel o / down under TP) the same accumulator
 // on every rank — the all-reduce is the RED itself
@@ -121,51 +127,116 @@ __device__ __forceinline__ int group_sum_i(int v, int* scratch) {
     return warp_sum_i(t);
 }
 
+// Single-barrier reductions over the NT-thread group: every warp drops its partial into its OWN scratch slot, one
+// barrier, every thread folds the NT/32 partials itself.  The caller gives each reduction of a row a distinct scratch
+// range, so no second "scratch free" barrier is needed (the next reuse is separated by the following barriers).
+template <int ID, int NT>
+__device__ __forceinline__ float group_sum1(float v, float* scratch) {
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) scratch[threadIdx.x >> 5] = v;
+    group_bar<ID, NT>();
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < NT / 32; ++w) t += scratch[w];
+    return t;
+}
+template <int ID, int NT>
+__device__ __forceinline__ float group_max1(float v, float* scratch) {
+    v = warp_max(v);
+    if ((threadIdx.x & 31) == 0) scratch[threadIdx.x >> 5] = v;
+    group_bar<ID, NT>();
+    float t = 0.f;   // non-negative values
+#pragma unroll
+    for (int w = 0; w < NT / 32; ++w) t = fmaxf(t, scratch[w]);
+    return t;
+}
+template <int ID, int NT>
+__device__ __forceinline__ int group_sum_i1(int v, int* scratch) {
+    v = warp_sum_i(v);
+    if ((threadIdx.x & 31) == 0) scratch[threadIdx.x >> 5] = v;
+    group_bar<ID, NT>();
+    int t = 0;
+#pragma unroll
+    for (int w = 0; w < NT / 32; ++w) t += scratch[w];
+    return t;
+}
+
+// Norm weights do not depend on the previous kernel: pull them towards the SM before the dependency wait.
+template <int NT>
+__device__ __forceinline__ void glue_prefetch_gamma(const GlueParams& p) {
+    const char* g = reinterpret_cast<const char*>(p.gamma);
+    for (int o = threadIdx.x * 128; o < p.K * 2; o += NT * 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(g + o));
+}
+
 // One activation row through the glue: source -> (residual / relu^2*up) -> RMSNorm -> per-token int8.
 // Executed by the NT-thread group (thread ids 0..NT-1).  ys: K bf16 of scratch (shared); qdst: K int8
 // (shared or global, 8-byte aligned); fs/is: >= 32 floats / ints of shared scratch.
 // Returns the activation scale and Sigma q through the references (identical in every thread).
 template <int ID, int NT>
 __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat16* ys, int8_t* qdst, float* fs, int* is,
-                                         bool write_side, float& scale_ret, int& rowsum_ret) {
+                                         bool write_side, float& scale_ret, int& rowsum_ret, unsigned long long* tr = nullptr) {
     const int K = p.K;
     const int tid = threadIdx.x;
     float ss = 0.f;
-    // ---- pass 1: x (bf16) -> ys, sum of squares
+    // ---- pass 1: x (bf16) -> ys, sum of squares.  All global loads of GU iterations are issued before the first use:
+    //      this pass is a chain of L2 round trips (~0.7 us each) on the layer's critical path.
+    constexpr int GU = 2;
     if (p.mode == GL_EMBED || p.mode == GL_PLAIN) {
         const __nv_bfloat16* row = (p.mode == GL_EMBED) ? p.embed + (size_t)p.tokens[m] * K : p.src + (size_t)m * K;
-        for (int k = tid * 8; k < K; k += NT * 8) {
-            const uint4 t = ldcg_u4(row + k);
-            *reinterpret_cast<uint4*>(ys + k) = t;
-            if (write_side && p.hid_out && p.mode == GL_EMBED) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = t;
-            const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+        for (int k0 = tid * 8; k0 < K; k0 += NT * 8 * GU) {
+            uint4 t[GU];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { const float a = bf16lo(w[i]), b = bf16hi(w[i]); ss += a * a + b * b; }
+            for (int u = 0; u < GU; ++u) {
+                const int k = k0 + u * NT * 8;
+                if (k < K) t[u] = ldcg_u4(row + k);
+            }
+#pragma unroll
+            for (int u = 0; u < GU; ++u) {
+                const int k = k0 + u * NT * 8;
+                if (k < K) {
+                    *reinterpret_cast<uint4*>(ys + k) = t[u];
+                    if (write_side && p.hid_out && p.mode == GL_EMBED) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = t[u];
+                    const uint32_t w[4] = {t[u].x, t[u].y, t[u].z, t[u].w};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { const float a = bf16lo(w[i]), b = bf16hi(w[i]); ss += a * a + b * b; }
+                }
+            }
         }
     } else if (p.mode == GL_RESID) {
         const int rs = p.acc_rowsum[m];
         const float sa = p.acc_ascale[m], ws = p.acc_wscale[0];
         const float* arow = p.acc + (size_t)m * p.acc_ld;
         const __nv_bfloat16* hrow = p.hid_in + (size_t)m * K;
-        for (int k = tid * 8; k < K; k += NT * 8) {
-            const uint4 t = ldcg_u4(hrow + k);
-            const float4 a0 = ldcg_f4(arow + k), a1 = ldcg_f4(arow + k + 4);
-            const float S[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const uint32_t hw[4] = {t.x, t.y, t.z, t.w};
-            uint32_t o[4];
+        for (int k0 = tid * 8; k0 < K; k0 += NT * 8 * GU) {
+            uint4 t[GU];
+            float4 a0[GU], a1[GU];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                // hidden + proj, both bf16 tensors: one rounding of the projection, one of the sum
-                const float x0 = bf16_round(bf16lo(hw[i]) + bf16_round(lin_value(S[2 * i], rs, ws, sa)));
-                const float x1 = bf16_round(bf16hi(hw[i]) + bf16_round(lin_value(S[2 * i + 1], rs, ws, sa)));
-                ss += x0 * x0 + x1 * x1;
-                o[i] = pack_bf16x2(x0, x1);
+            for (int u = 0; u < GU; ++u) {
+                const int k = k0 + u * NT * 8;
+                if (k < K) { t[u] = ldcg_u4(hrow + k); a0[u] = ldcg_f4(arow + k); a1[u] = ldcg_f4(arow + k + 4); }
             }
-            const uint4 ov = make_uint4(o[0], o[1], o[2], o[3]);
-            *reinterpret_cast<uint4*>(ys + k) = ov;
-            if (write_side && p.hid_out) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = ov;
+#pragma unroll
+            for (int u = 0; u < GU; ++u) {
+                const int k = k0 + u * NT * 8;
+                if (k < K) {
+                    const float S[8] = {a0[u].x, a0[u].y, a0[u].z, a0[u].w, a1[u].x, a1[u].y, a1[u].z, a1[u].w};
+                    const uint32_t hw[4] = {t[u].x, t[u].y, t[u].z, t[u].w};
+                    uint32_t o[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        // hidden + proj, both bf16 tensors: one rounding of the projection, one of the sum
+                        const float x0 = bf16_round(bf16lo(hw[i]) + bf16_round(lin_value(S[2 * i], rs, ws, sa)));
+                        const float x1 = bf16_round(bf16hi(hw[i]) + bf16_round(lin_value(S[2 * i + 1], rs, ws, sa)));
+                        ss += x0 * x0 + x1 * x1;
+                        o[i] = pack_bf16x2(x0, x1);
+                    }
+                    const uint4 ov = make_uint4(o[0], o[1], o[2], o[3]);
+                    *reinterpret_cast<uint4*>(ys + k) = ov;
+                    if (write_side && p.hid_out) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = ov;
+                }
+            }
         }
-    } else {  // GL_RELU2
+    } else {  // GL_RELU2 (4 independent 16-byte loads per iteration already; batching two iterations would spill)
         const int rs = p.acc_rowsum[m];
         const float sa = p.acc_ascale[m], wg = p.acc_wscale[0], wu = p.acc_wscale[1];
         const float* arow = p.acc + (size_t)m * p.acc_ld;
@@ -179,16 +250,19 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const float g = bf16_round(lin_value(G[i], rs, wg, sa));
-                const float u = bf16_round(lin_value(U[i], rs, wu, sa));
+                const float uu = bf16_round(lin_value(U[i], rs, wu, sa));
                 const float r = fmaxf(g, 0.f);
-                x[i] = bf16_round(bf16_round(r * r) * u);
+                x[i] = bf16_round(bf16_round(r * r) * uu);
                 ss += x[i] * x[i];
             }
             *reinterpret_cast<uint4*>(ys + k) =
                 make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
         }
     }
-    ss = group_sum<ID, NT>(ss, fs);
+    static_assert(NT / 32 <= 16, "scratch layout: 16 slots per reduction");
+    if (tr) tr[0] = gtimer();
+    ss = group_sum1<ID, NT>(ss, fs);
+    if (tr) tr[1] = gtimer();
     const float var = ss / (float)K;
     const float r = bf16_round(1.0f / sqrtf(var + p.eps));
     // ---- pass 2: y = bf16(bf16(x*r)*gamma) in place, absmax
@@ -209,8 +283,11 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
         *reinterpret_cast<uint4*>(ys + k) = ov;
         if (write_side && p.y_out) *reinterpret_cast<uint4*>(p.y_out + (size_t)m * K + k) = ov;
     }
-    amax = group_max<ID, NT>(amax, fs);
+    if (tr) tr[2] = gtimer();
+    amax = group_max1<ID, NT>(amax, fs + 16);
+    if (tr) tr[3] = gtimer();
     const float scale = act_scale_from_absmax(amax);
+    const QDiv qd = make_qdiv(scale);
     // ---- pass 3: int8 codes (each thread re-reads exactly what it wrote)
     int psum = 0;
     for (int k = tid * 8; k < K; k += NT * 8) {
@@ -219,14 +296,15 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
         uint32_t w0 = 0, w1 = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const int q0 = quant_i8(bf16lo(yw[i]), scale), q1 = quant_i8(bf16hi(yw[i]), scale);
+            const int q0 = quant_i8(bf16lo(yw[i]), qd), q1 = quant_i8(bf16hi(yw[i]), qd);
             psum += q0 + q1;
             const uint32_t pr = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8);
             if (i < 2) w0 |= pr << (16 * i); else w1 |= pr << (16 * (i - 2));
         }
         *reinterpret_cast<uint2*>(qdst + k) = make_uint2(w0, w1);
     }
-    const int total = group_sum_i<ID, NT>(psum, is);
+    if (tr) tr[4] = gtimer();
+    const int total = group_sum_i1<ID, NT>(psum, is);
     scale_ret = scale;
     rowsum_ret = total;
 }
@@ -299,6 +377,7 @@ struct FusedAttnArgs {
     const void *cos_tab, *sin_tab;
     int max_pos;
     int* merge_cnt;            // [B][Hkv], zero
+    unsigned long long* trace; // WF_TRACE timeline taps or null
     float* zero0;
     int zero0_n;
     int max_seq_hint;

@@ -23,7 +23,7 @@ namespace wf {
 constexpr int LS_STAGE_TILES = 16;                        // 8 KB per stage
 constexpr int LS_STAGE_BYTES = LS_STAGE_TILES * WF_TILE_BYTES;
 constexpr int LS_STAGES = 8;                              // 64 KB ring
-constexpr int LS_CW = 8;                                  // consumer warps
+constexpr int LS_CW = 12;                                 // consumer warps (3 per scheduler: the per-tile LDS -> ldmatrix -> mma chain needs the TLP; 2 CTAs/SM must still fit)
 constexpr int LS_CT = LS_CW * 32;                         // consumer threads
 constexpr int LS_THREADS = LS_CT + 32;
 
@@ -61,6 +61,9 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
     const int rb_first = (int)(t0 / p.KB);
 
     pdl_launch_dependents();   // let the next phase's CTAs in: their weight stream overlaps this phase
+    const bool tr = p.g.trace != nullptr && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1) && tid == 0;
+    unsigned long long* trp = tr ? p.g.trace + (blockIdx.x == 0 ? 0 : 16) : nullptr;
+    if (tr) trp[0] = gtimer();
     if (tid == 0) {
         for (int s = 0; s < LS_STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
@@ -86,18 +89,22 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
         }
     } else {
         // ------------------------------------------------ consumer warps
+        glue_prefetch_gamma<LS_CT>(p.g);   // weights: no dependency on the previous phase
         pdl_wait_prior();          // everything below reads what the previous phase wrote
+        if (tr) trp[1] = gtimer();
         if (p.g.wait_flag >= 0) {  // ... and, under tensor parallelism, what the peers wrote into this rank's buffers
             if (warp == 0) tp_wait_flags_warp(p.g.tp, p.g.wait_flag);
             group_bar<1, LS_CT>();
         }
+        if (tr) trp[2] = gtimer();
         glue_zero_duty<LS_CT>(p.g);
         for (int m = 0; m < M; ++m) {
             float sc; int rsum;
-            glue_row<1, LS_CT>(p.g, m, ys, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, blockIdx.x == 0, sc, rsum);
+            glue_row<1, LS_CT>(p.g, m, ys, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, blockIdx.x == 0, sc, rsum, (tr && m == 0) ? trp + 8 : nullptr);
             if (blockIdx.x == 0 && tid == 0) { p.lin_ascale[m] = sc; p.lin_rowsum[m] = rsum; }
         }
         group_bar<1, LS_CT>();     // activations complete
+        if (tr) trp[3] = gtimer();
 
         int acc[4][4];
 #pragma unroll
@@ -130,13 +137,17 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
             }
         };
 
+        // Tile -> warp mapping: tile i of the slab belongs to warp i % LS_CW; (row-block, k-block) of the warp's next tile
+        // are tracked incrementally (no division on the per-tile path).
+        int i_next = warp;
+        int kb = (int)(t0 - (long long)rb_first * p.KB) + warp, rb = rb_first;
+        while (kb >= p.KB) { kb -= p.KB; ++rb; }
         for (int it = 0; it < nstages; ++it) {
             const int s = it % LS_STAGES;
             mbar_wait(&full_bar[s], (it / LS_STAGES) & 1);
-            const int tiles = min(LS_STAGE_TILES, ntiles - it * LS_STAGE_TILES);
-            for (int tl = warp; tl < tiles; tl += LS_CW) {
-                const long long tg = t0 + (long long)it * LS_STAGE_TILES + tl;
-                const int rb = (int)(tg / p.KB), kb = (int)(tg - (long long)rb * p.KB);
+            const int lim = min(ntiles, (it + 1) * LS_STAGE_TILES);
+            while (i_next < lim) {
+                const int tl = i_next - it * LS_STAGE_TILES;
                 if (rb != cur_rb) { flush(cur_rb); cur_rb = rb; }
                 const uint4 Wv = *reinterpret_cast<const uint4*>(ring + s * LS_STAGE_BYTES + tl * WF_TILE_BYTES + lane * 16);
                 uint32_t b[8];
@@ -148,12 +159,16 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
                     const uint32_t mask = 0x03030303u << (6 - 2 * g);   // k-group g sits in bits (7-2g .. 6-2g)
                     mma_u8s8_16832(acc[g], Wv.x & mask, Wv.y & mask, Wv.z & mask, Wv.w & mask, b[2 * g], b[2 * g + 1]);
                 }
+                i_next += LS_CW;
+                kb += LS_CW;
+                while (kb >= p.KB) { kb -= p.KB; ++rb; }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[s]);
         }
         flush(cur_rb);
         group_bar<1, LS_CT>();
+        if (tr) trp[4] = gtimer();
         // ------------------------------------------------ exact fp32 RED of this CTA's partial sums
         if (ntiles > 0) {
             const int rb_last = (int)((t1 - 1) / p.KB);
@@ -169,7 +184,9 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
             }
         }
     }
+    if (tr) trp[5] = gtimer();
     if (p.dest.signal_flag >= 0) tp_signal_grid_done(p.g.tp, p.dest.signal_flag, gridDim.x);
+    if (tr) trp[6] = gtimer();
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -57,12 +57,13 @@ __device__ __forceinline__ int row_quant(const T* row, int K, float scale, int8_
     constexpr int VN = Vec<T>::N;
     int psum = 0;
     float v[8];
+    const QDiv qd = make_qdiv(scale);
     for (int k = threadIdx.x * VN; k < K; k += QT * VN) {
         Vec<T>::load(row + k, v);
         uint32_t w[2] = {0, 0};
 #pragma unroll
         for (int i = 0; i < VN; ++i) {
-            const int qi = quant_i8(v[i], scale);
+            const int qi = quant_i8(v[i], qd);
             psum += qi;
             w[i >> 2] |= (uint32_t)(qi & 0xff) << (8 * (i & 3));
         }
