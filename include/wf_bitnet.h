@@ -249,6 +249,12 @@ int wf_engine_tp_attach(wf_engine* e, const void* handles);
 void* wf_engine_buffer(wf_engine* e, const char* name);
 int wf_engine_launches_per_step(const wf_engine* e);
 int wf_engine_time_kernel(wf_engine* e, const char* which, int B, int iters, float* ms_out);
+/* Kernel-level GEMV measurement in the style of the reference's scripts/benchmark_kernels.py:28-66 (a loop of
+ * bitnet_gemv calls, bytes = N*K/4 + M*K + out), but rotating over > L2 worth of independent weight copies so the
+ * figure is an HBM figure.  flags: 1 = programmatic dependent launch between the calls, 2 = stream only (no math),
+ * 4 = fused dequant epilogue (WF_OUT_LINEAR, bf16) instead of raw int32, 8 = force the mma.sync path, 16 / 32 = force 16 / 8 consumer warps, bits 8..15 = TMA
+ * ring depth in 8 KB stages (0 = default).  ms_out = average per launch. */
+int wf_bench_gemv(int N, int K, int M, int iters, int flags, float* ms_out);
 
 #ifdef __cplusplus
 }

@@ -101,6 +101,7 @@ SYMBOLS = {
     "wf_engine_buffer": (_vp, [_vp, C.c_char_p]),
     "wf_engine_launches_per_step": (_i, [_vp]),
     "wf_engine_time_kernel": (_i, [_vp, C.c_char_p, _i, _i, C.POINTER(_f)]),
+    "wf_bench_gemv": (_i, [_i, _i, _i, _i, _i, C.POINTER(_f)]),
 }
 
 _lib = None
