@@ -37,7 +37,7 @@ def main():
                 out_b = (2 if fl & 4 else 4) * M * N
                 byt = N * K // 4 + M * K + out_b
                 gbs = byt / (ms.value * 1e-3) / 1e9
-                print(json.dumps({"shape": name, "N": N, "K": K, "M": M, "pdl": bool(fl & 1), "stream_only": bool(fl & 2), "fused_epilogue": bool(fl & 4), "mma_path": bool(fl & 8), "cw": 16 if fl & 16 else (8 if fl & 32 else 0), "stages": (fl >> 8) & 255,
+                print(json.dumps({"shape": name, "N": N, "K": K, "M": M, "pdl": bool(fl & 1), "stream_only": bool(fl & 2), "fused_epilogue": bool(fl & 4), "mma_path": bool(fl & 8), "cw": 16 if fl & 16 else (8 if fl & 32 else 0), "l2_ahead": bool(fl & 64), "grid_mult": ((fl >> 16) & 15) or (2 if fl & 128 else 1), "stages": (fl >> 8) & 255,
                                   "us_per_launch": round(ms.value * 1e3, 3), "bytes": byt, "GBs": round(gbs, 1), "frac_of_hbm_peak": round(gbs / peak, 4)}), flush=True)
 
 if __name__ == "__main__":

@@ -8,7 +8,7 @@ using namespace wf;
 
 namespace wf {
 int g_gemv_debug = 0;   // bit0: consumers skip the math (stream-only ceiling of the TMA ring)
-extern int g_gemv_stages, g_gemv_path, g_gemv_cw;
+extern int g_gemv_stages, g_gemv_path, g_gemv_l2_ahead, g_gemv_grid_mult;
 }
 
 extern "C" int wf_bench_gemv(int N, int K, int M, int iters, int flags, float* ms_out) {
@@ -57,7 +57,9 @@ extern "C" int wf_bench_gemv(int N, int K, int M, int iters, int flags, float* m
     a.workspace = ws; a.workspace_bytes = ws_bytes; a.host_scale = 1.f;
     g_gemv_debug = (flags & 2) ? 1 : 0;
     g_gemv_path = (flags & 8) ? 0 : -1;
-    g_gemv_cw = (flags & 16) ? 16 : ((flags & 32) ? 8 : 0);
+    g_gemv_l2_ahead = (flags & 64) ? 16 : 0;
+    g_gemv_grid_mult = (flags & 128) ? 2 : 0;
+    if ((flags >> 16) & 0xf) g_gemv_grid_mult = (flags >> 16) & 0xf;
     if ((flags >> 8) & 0xff) g_gemv_stages = (flags >> 8) & 0xff;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     cudaEventCreate(&e0);
@@ -96,8 +98,9 @@ extern "C" int wf_bench_gemv(int N, int K, int M, int iters, int flags, float* m
     }
     g_gemv_debug = 0;
     g_gemv_path = -1;
-    g_gemv_cw = 0;
-    g_gemv_stages = 8;
+    g_gemv_l2_ahead = 0;
+    g_gemv_grid_mult = 0;
+    g_gemv_stages = 5;
     cudaStreamSynchronize(s);
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);

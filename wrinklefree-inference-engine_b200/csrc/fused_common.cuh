@@ -174,7 +174,8 @@ __device__ __forceinline__ void glue_prefetch_gamma(const GlueParams& p) {
 // Returns the activation scale and Sigma q through the references (identical in every thread).
 template <int ID, int NT>
 __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat16* ys, int8_t* qdst, float* fs, int* is,
-                                         bool write_side, float& scale_ret, int& rowsum_ret, unsigned long long* tr = nullptr) {
+                                         bool write_side, float& scale_ret, int& rowsum_ret, unsigned long long* tr = nullptr,
+                                         bool perm = false) {
     const int K = p.K;
     const int tid = threadIdx.x;
     float ss = 0.f;
@@ -301,7 +302,15 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
             const uint32_t pr = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8);
             if (i < 2) w0 |= pr << (16 * i); else w1 |= pr << (16 * (i - 2));
         }
-        *reinterpret_cast<uint2*>(qdst + k) = make_uint2(w0, w1);
+        if (!perm) {
+            *reinterpret_cast<uint2*>(qdst + k) = make_uint2(w0, w1);
+        } else {
+            // dp4a staging order (gemv_stream.cu): word (8g + 4h + t) of a 128-k block goes to word (8t + 2g + h)
+            const int w = k >> 2, wi = w & 31;
+            const int d = (w & ~31) + 8 * (wi & 3) + 2 * (wi >> 3) + ((wi >> 2) & 1);
+            reinterpret_cast<uint32_t*>(qdst)[d] = w0;
+            reinterpret_cast<uint32_t*>(qdst)[d + 8] = w1;   // w + 1: t + 1
+        }
     }
     if (tr) tr[4] = gtimer();
     const int total = group_sum_i1<ID, NT>(psum, is);

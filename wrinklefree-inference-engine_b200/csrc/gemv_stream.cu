@@ -25,6 +25,7 @@ namespace wf {
 
 extern int g_gemv_debug;
 
+constexpr int SV_TPW = 4;                                // tiles per consumer warp per stage
 constexpr int SV_MAX_STAGES = 24;                        // ring depth is a launch parameter (p.stages), default 8 = 64 KB
 
 // unsigned (weight field, left at its bit position) x signed (int8 activation) 4-way dot product
@@ -45,7 +46,9 @@ struct StreamParams {
     int sacc_rbs;         // row-blocks of smem accumulators
     int* ws_acc;
     int* ws_cnt;
+    int aligned;          // 1: CTA slabs are whole finalisation groups (no split-K, no workspace traffic)
     int stages;           // ring depth (<= SV_MAX_STAGES)
+    int l2_ahead;         // producer prefetches this many stages beyond the ring into L2 (0 = off)
     int debug;            // bit0: stream-only (wf_bench_gemv: the ceiling of the TMA ring without the math)
     EpiParams ep;
 };
@@ -61,18 +64,26 @@ struct StreamParams {
 template <int MR, int CW>
 __global__ void __launch_bounds__((CW + 1) * 32, CW <= 8 ? 2 : 1) ternary_gemv_stream_kernel(const StreamParams p) {
     constexpr int NT = (CW + 1) * 32, CT = CW * 32;
-    constexpr int SV_STAGE_TILES = 2 * CW, SV_STAGE_BYTES = SV_STAGE_TILES * WF_TILE_BYTES;   // a stage = one tile pair per consumer warp
+    constexpr int SV_STAGE_TILES = SV_TPW * CW, SV_STAGE_BYTES = SV_STAGE_TILES * WF_TILE_BYTES;   // a stage = SV_TPW adjacent tiles per consumer warp
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* ring = smem;                                        // stages * SV_STAGE_BYTES
     unsigned char* acts = ring + p.stages * SV_STAGE_BYTES;            // M * act_stride
     int* sacc = reinterpret_cast<int*>(acts + ((p.M * p.act_stride + 127) & ~127));   // [rbl][8][16]
     __shared__ __align__(8) uint64_t full_bar[SV_MAX_STAGES];
     __shared__ __align__(8) uint64_t empty_bar[SV_MAX_STAGES];
-    __shared__ int s_last;
+    __shared__ int s_fin[2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long t0 = (long long)blockIdx.x * p.T / gridDim.x;
-    const long long t1 = (long long)(blockIdx.x + 1) * p.T / gridDim.x;
+    long long t0, t1;
+    if (p.aligned) {   // whole groups of row-blocks per CTA
+        const int G = (p.RB + p.grp - 1) / p.grp;
+        t0 = ((long long)blockIdx.x * G / gridDim.x) * p.grp * p.KB;
+        t1 = ((long long)(blockIdx.x + 1) * G / gridDim.x) * p.grp * p.KB;
+        if (t1 > p.T) t1 = p.T;
+    } else {           // even tile split (split-K across CTA boundaries)
+        t0 = (long long)blockIdx.x * p.T / gridDim.x;
+        t1 = (long long)(blockIdx.x + 1) * p.T / gridDim.x;
+    }
     const int ntiles = (int)(t1 - t0);
     const int nstages = (ntiles + SV_STAGE_TILES - 1) / SV_STAGE_TILES;
     const int rb_first = (int)(t0 / p.KB);
@@ -95,6 +106,13 @@ __global__ void __launch_bounds__((CW + 1) * 32, CW <= 8 ? 2 : 1) ternary_gemv_s
         if (lane == 0) {
             int s = 0, ph = 1;
             for (int it = 0; it < nstages; ++it) {
+                if (p.l2_ahead > 0) {
+                    const int pf = it + S + p.l2_ahead - 1;   // first pass also covers [S, S + l2_ahead)
+                    for (int j = (it == 0 ? S : pf); j <= pf && j < nstages; ++j) {
+                        const int tl = min(SV_STAGE_TILES, ntiles - j * SV_STAGE_TILES);
+                        bulk_prefetch_l2(p.w + (size_t)(t0 + (long long)j * SV_STAGE_TILES) * WF_TILE_BYTES, (uint32_t)tl * WF_TILE_BYTES);
+                    }
+                }
                 mbar_wait(&empty_bar[s], ph);
                 const int tiles = min(SV_STAGE_TILES, ntiles - it * SV_STAGE_TILES);
                 const uint32_t bytes = (uint32_t)tiles * WF_TILE_BYTES;
@@ -172,14 +190,16 @@ __global__ void __launch_bounds__((CW + 1) * 32, CW <= 8 ? 2 : 1) ternary_gemv_s
             }
         };
 
-        // Tile -> warp mapping: a stage holds 2*CW tiles and warp w owns the adjacent pair (2w, 2w+1) of every stage — both
-        // weight loads are issued before any math, the pair almost always shares a row-block (one flush per KB tiles), and
+        // Tile -> warp mapping: a stage holds SV_TPW*CW tiles and warp w owns the SV_TPW adjacent tiles starting at
+        // SV_TPW*w of every stage — all weight loads are issued before any math, the run almost always stays inside one
+        // row-block (one flush per KB tiles), the per-stage bookkeeping is amortised over SV_TPW tiles and
         // (row-block, k-block) are tracked incrementally (no division on the per-tile path).
-        constexpr int ST = 2 * CW;
-        int kb0 = (int)(t0 - (long long)rb_first * p.KB) + 2 * warp, rb0 = rb_first;
+        constexpr int ST = SV_TPW * CW;
+        int kb0 = (int)(t0 - (long long)rb_first * p.KB) + SV_TPW * warp, rb0 = rb_first;
         while (kb0 >= p.KB) { kb0 -= p.KB; ++rb0; }
         const int arow = min(lane & 7, p.M - 1);
         const unsigned char* abase = MR == 0 ? acts + arow * p.act_stride + (lane >> 3) * 16 : acts + (lane & 3) * 32;
+        const int KB = p.KB;
 
         auto tile_math = [&](const uint4& Wv, int kb) {
             if (MR == 0) {
@@ -202,7 +222,7 @@ __global__ void __launch_bounds__((CW + 1) * 32, CW <= 8 ? 2 : 1) ternary_gemv_s
                 }
 #pragma unroll
                 for (int m = 0; m < MR; ++m) {
-                    const unsigned char* ap = abase + min(m, p.M - 1) * p.act_stride + kb * 128;
+                    const unsigned char* ap = abase + (m < p.M ? m : 0) * p.act_stride + kb * 128;
                     const uint4 a0 = *reinterpret_cast<const uint4*>(ap);        // (g0,h0) (g0,h1) (g1,h0) (g1,h1)
                     const uint4 a1 = *reinterpret_cast<const uint4*>(ap + 16);   // (g2,h0) (g2,h1) (g3,h0) (g3,h1)
                     const uint32_t A[4][2] = {{a0.x, a0.y}, {a0.z, a0.w}, {a1.x, a1.y}, {a1.z, a1.w}};
@@ -220,27 +240,41 @@ __global__ void __launch_bounds__((CW + 1) * 32, CW <= 8 ? 2 : 1) ternary_gemv_s
         };
 
         int s = 0, ph = 0;
-        const unsigned char* wbase = ring + warp * (2 * WF_TILE_BYTES) + lane * 16;
+        const unsigned char* wbase = ring + warp * (SV_TPW * WF_TILE_BYTES) + lane * 16;
         for (int it = 0; it < nstages; ++it) {
             mbar_wait(&full_bar[s], ph);
-            const int i0 = it * ST + 2 * warp;
+            const int i0 = it * ST + SV_TPW * warp;
             if (i0 < ntiles && !(p.debug & 1)) {
                 const unsigned char* wp = wbase + s * (ST * WF_TILE_BYTES);
-                const bool two = i0 + 1 < ntiles;
-                const uint4 W0 = *reinterpret_cast<const uint4*>(wp);
-                uint4 W1 = make_uint4(0, 0, 0, 0);
-                if (two) W1 = *reinterpret_cast<const uint4*>(wp + WF_TILE_BYTES);
-                int kb1 = kb0 + 1, rb1 = rb0;
-                if (kb1 >= p.KB) { kb1 = 0; ++rb1; }
-                if (rb0 != cur_rb) { flush(cur_rb); cur_rb = rb0; }
-                tile_math(W0, kb0);
-                if (two) {
-                    if (rb1 != cur_rb) { flush(cur_rb); cur_rb = rb1; }
-                    tile_math(W1, kb1);
+                uint4 W[SV_TPW];
+                if (i0 + SV_TPW <= ntiles) {
+#pragma unroll
+                    for (int j = 0; j < SV_TPW; ++j) W[j] = *reinterpret_cast<const uint4*>(wp + j * WF_TILE_BYTES);
+                    if (kb0 + SV_TPW <= KB && rb0 == cur_rb) {
+                        // fast path: the whole run sits in the current row-block
+#pragma unroll
+                        for (int j = 0; j < SV_TPW; ++j) tile_math(W[j], kb0 + j);
+                    } else {
+                        int kb = kb0, rb = rb0;
+#pragma unroll
+                        for (int j = 0; j < SV_TPW; ++j) {
+                            if (rb != cur_rb) { flush(cur_rb); cur_rb = rb; }
+                            tile_math(W[j], kb);
+                            if (++kb == KB) { kb = 0; ++rb; }
+                        }
+                    }
+                } else {
+                    int kb = kb0, rb = rb0;
+                    for (int j = 0; j < SV_TPW && i0 + j < ntiles; ++j) {
+                        const uint4 Wv = *reinterpret_cast<const uint4*>(wp + j * WF_TILE_BYTES);
+                        if (rb != cur_rb) { flush(cur_rb); cur_rb = rb; }
+                        tile_math(Wv, kb);
+                        if (++kb == KB) { kb = 0; ++rb; }
+                    }
                 }
             }
             kb0 += ST;
-            while (kb0 >= p.KB) { kb0 -= p.KB; ++rb0; }
+            while (kb0 >= KB) { kb0 -= KB; ++rb0; }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[s]);
             if (++s == S) { s = 0; ph ^= 1; }
@@ -249,36 +283,57 @@ __global__ void __launch_bounds__((CW + 1) * 32, CW <= 8 ? 2 : 1) ternary_gemv_s
     }
     __syncthreads();
 
-    // ------------------------------------------------ combine + fused epilogue, one finalisation group at a time
+    // ------------------------------------------------ combine + fused epilogue
+    // Row-block groups cut by a CTA boundary (at most the first and the last of the slab) are combined through the
+    // self-cleaning int32 workspace; whoever completes a group finalises it.  All groups this CTA finalises then go
+    // through the fused epilogue in ONE parallel pass.
     if (ntiles > 0) {
         const int rb_last = (int)((t1 - 1) / p.KB);
         const int grp_tiles = p.grp * p.KB;
         const int rows_per_grp = p.grp * 16;
         const bool relu2 = (p.ep.out_mode == WF_OUT_LINEAR) && (p.ep.epi_flags & WF_EPI_RELU2_MUL);
-        for (int grp = rb_first / p.grp; grp <= rb_last / p.grp; ++grp) {
-            const long long g0 = (long long)grp * grp_tiles, g1 = g0 + grp_tiles;
-            const int contrib = (int)((t1 < g1 ? t1 : g1) - (t0 > g0 ? t0 : g0));
-            int* sg = sacc + (grp * p.grp - rb_base) * 128;   // [grp rb][m][16]
-            const int nbase = grp * rows_per_grp;
-            bool fin = true;
-            if (contrib != grp_tiles) {
-                for (int i = tid; i < p.grp * 128; i += NT) {
-                    const int rbl = i >> 7, m = (i >> 4) & 7, r = i & 15;
-                    const int n = nbase + rbl * 16 + r;
-                    const int v = sg[i];
-                    if (m < p.M && n < p.N && v) atomicAdd(p.ws_acc + (size_t)m * p.N + n, v);
+        const int gfirst = rb_first / p.grp, glast = rb_last / p.grp;
+        bool fin_first = true, fin_last = true;
+        if (!p.aligned) {
+            // both boundary groups go through ONE round of (partial sums -> fence -> arrival counter -> read back)
+            int contrib[2], gid[2];
+            bool part[2];
+            for (int e = 0; e < 2; ++e) {
+                gid[e] = e == 0 ? gfirst : glast;
+                const long long g0 = (long long)gid[e] * grp_tiles, g1 = g0 + grp_tiles;
+                contrib[e] = (int)((t1 < g1 ? t1 : g1) - (t0 > g0 ? t0 : g0));
+                const long long gt = (g1 < p.T ? g1 : p.T) - g0;          // tiles the group really has (last group may be short)
+                part[e] = contrib[e] != (int)gt && !(e == 1 && glast == gfirst);
+            }
+            if (part[0] || part[1]) {
+                for (int e = 0; e < 2; ++e) {
+                    if (!part[e]) continue;
+                    const int* sg = sacc + (gid[e] * p.grp - rb_base) * 128;   // [grp rb][m][16]
+                    const int nbase = gid[e] * rows_per_grp;
+                    for (int i = tid; i < p.grp * 128; i += NT) {
+                        const int rbl = i >> 7, m = (i >> 4) & 7, r = i & 15;
+                        const int n = nbase + rbl * 16 + r;
+                        const int v = sg[i];
+                        if (m < p.M && n < p.N && v) atomicAdd(p.ws_acc + (size_t)m * p.N + n, v);
+                    }
                 }
                 __threadfence();
                 __syncthreads();
-                if (tid == 0) {
-                    const int prev = atomicAdd(p.ws_cnt + grp, contrib);
-                    s_last = (prev + contrib == grp_tiles);
-                    if (s_last) p.ws_cnt[grp] = 0;
+                if (tid < 2 && part[tid]) {
+                    const long long g0 = (long long)gid[tid] * grp_tiles;
+                    const int gt = (int)((g0 + grp_tiles < p.T ? g0 + grp_tiles : p.T) - g0);
+                    const int prev = atomicAdd(p.ws_cnt + gid[tid], contrib[tid]);
+                    s_fin[tid] = (prev + contrib[tid] == gt);
+                    if (s_fin[tid]) p.ws_cnt[gid[tid]] = 0;
                 }
                 __syncthreads();
-                fin = s_last != 0;
-                if (fin) {
-                    __threadfence();
+                if (part[0]) fin_first = s_fin[0] != 0;
+                if (part[1]) fin_last = s_fin[1] != 0;
+                if ((part[0] && fin_first) || (part[1] && fin_last)) __threadfence();
+                for (int e = 0; e < 2; ++e) {
+                    if (!part[e] || !(e == 0 ? fin_first : fin_last)) continue;
+                    int* sg = sacc + (gid[e] * p.grp - rb_base) * 128;
+                    const int nbase = gid[e] * rows_per_grp;
                     for (int i = tid; i < p.grp * 128; i += NT) {
                         const int rbl = i >> 7, m = (i >> 4) & 7, r = i & 15;
                         const int n = nbase + rbl * 16 + r;
@@ -291,49 +346,49 @@ __global__ void __launch_bounds__((CW + 1) * 32, CW <= 8 ? 2 : 1) ternary_gemv_s
                 }
                 __syncthreads();
             }
-            if (fin) {
-                if (relu2) {
-                    for (int i = tid; i < p.M * 16; i += NT) {
-                        const int m = i >> 4, r = i & 15;
-                        epilogue_store_relu2(p.ep, m, nbase + r, sg[m * 16 + r], sg[128 + m * 16 + r]);
-                    }
-                } else {
-                    for (int i = tid; i < p.M * rows_per_grp; i += NT) {
-                        const int m = i / rows_per_grp, rr = i % rows_per_grp;
-                        const int n = nbase + rr;
-                        if (n < p.N) epilogue_store(p.ep, m, n, sg[(rr >> 4) * 128 + m * 16 + (rr & 15)]);
-                    }
-                }
+        }
+        if (glast == gfirst) fin_last = fin_first;
+        const int ngrp = glast - gfirst + 1;
+        if (relu2) {
+            for (int i = tid; i < ngrp * p.M * 16; i += NT) {
+                const int gl = i / (p.M * 16), rem = i - gl * (p.M * 16);
+                const int m = rem >> 4, r = rem & 15;
+                const int grp = gfirst + gl;
+                if ((grp == gfirst && !fin_first) || (grp == glast && !fin_last)) continue;
+                const int* sg = sacc + (grp * 2 - rb_base) * 128;
+                epilogue_store_relu2(p.ep, m, grp * 32 + r, sg[m * 16 + r], sg[128 + m * 16 + r]);
+            }
+        } else {   // grp == 1: groups are row-blocks
+            for (int i = tid; i < ngrp * p.M * 16; i += NT) {
+                const int gl = i / (p.M * 16), rem = i - gl * (p.M * 16);
+                const int m = rem >> 4, r = rem & 15;
+                const int grp = gfirst + gl;
+                if ((grp == gfirst && !fin_first) || (grp == glast && !fin_last)) continue;
+                const int n = grp * 16 + r;
+                if (n < p.N) epilogue_store(p.ep, m, n, sacc[(grp - rb_base) * 128 + m * 16 + r]);
             }
         }
     }
 }
 
-int g_gemv_stages = 8;    // ring depth override (wf_bench_gemv)
+int g_gemv_stages = 5;    // ring depth (16 KB stages) — wf_bench_gemv can override
 int g_gemv_path = -1;     // -1 auto, 0 force the mma path
-int g_gemv_cw = 0;        // 0 auto, 8 / 16 force the consumer-warp count
+int g_gemv_l2_ahead = 0;  // L2 prefetch distance in stages
+int g_gemv_grid_mult = 0; // CTAs per SM, 0 = auto
+int g_gemv_aligned = 1;   // 0: always use the even tile split
 
 typedef void (*stream_kernel_t)(const StreamParams);
-template <int CW>
-static stream_kernel_t pick_mr(int M) {
-    if (g_gemv_path == 0 || M > 4) return ternary_gemv_stream_kernel<0, CW>;
-    if (M == 1) return ternary_gemv_stream_kernel<1, CW>;
-    if (M == 2) return ternary_gemv_stream_kernel<2, CW>;
-    return ternary_gemv_stream_kernel<4, CW>;
-}
-// small slabs (a few KB per SM) are latency-bound: 8 consumer warps, 8 KB stages, two CTAs per SM can co-reside so that
-// the next launch's weight stream overlaps under PDL; large slabs are issue-bound: 16 consumer warps, 16 KB stages.
-static stream_kernel_t pick_kernel(int M, long long tiles_per_cta, int* cw) {
-    int c = g_gemv_cw ? g_gemv_cw : (tiles_per_cta >= 256 ? 16 : 8);
-    *cw = c;
-    return c == 16 ? pick_mr<16>(M) : pick_mr<8>(M);
+constexpr int SV_CW = 8;   // consumer warps per CTA; large matrices run two CTAs per SM (two independent TMA streams)
+static stream_kernel_t pick_kernel(int M) {
+    // one activation row: CUDA cores (dp4a); 2..8 rows: the tensor path costs the same for any M <= 8
+    if (g_gemv_path == 0 || M > 1) return ternary_gemv_stream_kernel<0, SV_CW>;
+    return ternary_gemv_stream_kernel<1, SV_CW>;
 }
 
 static size_t g_stream_attr_smem = 0;
 void gemv_stream_init_attrs() {
     bool ok = true;
-    const stream_kernel_t all[8] = {ternary_gemv_stream_kernel<0, 8>, ternary_gemv_stream_kernel<1, 8>, ternary_gemv_stream_kernel<2, 8>, ternary_gemv_stream_kernel<4, 8>,
-                                    ternary_gemv_stream_kernel<0, 16>, ternary_gemv_stream_kernel<1, 16>, ternary_gemv_stream_kernel<2, 16>, ternary_gemv_stream_kernel<4, 16>};
+    const stream_kernel_t all[2] = {ternary_gemv_stream_kernel<0, SV_CW>, ternary_gemv_stream_kernel<1, SV_CW>};
     for (stream_kernel_t k : all) ok &= cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024) == cudaSuccess;
     if (ok) g_stream_attr_smem = 220 * 1024;
 }
@@ -351,24 +406,47 @@ int launch_gemv_stream(const wf_linear_args* a, const EpiParams& ep, cudaStream_
     p.act_stride = a->K + 16;
     p.ep = ep;
     p.debug = g_gemv_debug;
-    int grid = sm_count();
-    const long long min_tiles = 4;
-    if (p.T / min_tiles < grid) grid = (int)((p.T + min_tiles - 1) / min_tiles);
-    if (grid < 1) grid = 1;
-    const long long max_tiles = (p.T + grid - 1) / grid + 1;
-    p.sacc_rbs = (int)(max_tiles / p.KB) + 2 + 2 * p.grp;
+    p.l2_ahead = g_gemv_l2_ahead;
+    // Grid: two CTAs per SM (two independent TMA streams per SM: +15 % stream rate, measured) once every CTA still gets a few
+    // stages and both fit in shared memory; one per SM otherwise.  Slabs: whole row-block groups per CTA when there are
+    // enough of them and the matrix is small (no split-K: saves three dependent L2 round trips), an even tile split else.
+    const int sms = sm_count();
+    const size_t act_bytes = (((size_t)p.M * p.act_stride + 127) & ~(size_t)127);
+    const size_t stage_bytes = (size_t)SV_TPW * SV_CW * WF_TILE_BYTES;
+    int mult = g_gemv_grid_mult > 0 ? g_gemv_grid_mult : (p.T >= (long long)2 * sms * 3 * SV_TPW * SV_CW ? 2 : 1);
+    p.stages = g_gemv_stages < 2 ? 2 : (g_gemv_stages > SV_MAX_STAGES ? SV_MAX_STAGES : g_gemv_stages);
+    const int G = (p.RB + p.grp - 1) / p.grp;
+    int grid = 0;
+    size_t smem = 0;
+    for (;;) {
+        grid = sms * mult;
+        const long long min_tiles = 4;
+        if (p.T / min_tiles < grid) grid = (int)((p.T + min_tiles - 1) / min_tiles);
+        if (grid < 1) grid = 1;
+        // whole groups per CTA when that costs <= 12.5 % balance (the split-K round costs ~3 us of dependent L2 round trips)
+        if (g_gemv_aligned && G < grid && G >= sms) grid = G;   // one whole group per CTA
+        p.aligned = (g_gemv_aligned != 0) && G >= grid &&
+                    ((p.T / grid) < (long long)8 * SV_TPW * SV_CW || (long long)((G + grid - 1) / grid) * grid * 8 <= (long long)G * 9);
+        const long long max_tiles = p.aligned ? (long long)((G + grid - 1) / grid + 1) * p.grp * p.KB : (p.T + grid - 1) / grid + 1;
+        p.sacc_rbs = (int)(max_tiles / p.KB) + 2 + 2 * p.grp;
+        const size_t fixed = act_bytes + (size_t)p.sacc_rbs * 512;
+        if (mult == 2 && g_gemv_grid_mult == 0) {
+            // both CTAs of an SM must fit: shrink the ring down to 3 stages before giving up the second CTA
+            int st = p.stages;
+            while (st > 3 && 2 * (st * stage_bytes + fixed + 1024) > 226 * 1024) --st;
+            if (2 * (st * stage_bytes + fixed + 1024) > 226 * 1024) { mult = 1; p.stages = 8; continue; }
+            p.stages = st;
+        }
+        while (p.stages > 2 && p.stages * stage_bytes + fixed > 220 * 1024) --p.stages;
+        smem = p.stages * stage_bytes + fixed;
+        break;
+    }
     const size_t need_ws = (size_t)a->M * a->N * 4 + (size_t)p.RB * 4;
     if (!a->workspace || a->workspace_bytes < need_ws) { set_error("gemv_stream: workspace too small (%zu < %zu)", a->workspace_bytes, need_ws); return WF_ERR_INVALID; }
     p.ws_acc = (int*)a->workspace;
     p.ws_cnt = (int*)((char*)a->workspace + (size_t)a->M * a->N * 4);
-    p.stages = g_gemv_stages < 2 ? 2 : (g_gemv_stages > SV_MAX_STAGES ? SV_MAX_STAGES : g_gemv_stages);
-    int cw = 8;
-    stream_kernel_t kern = pick_kernel(a->M, max_tiles, &cw);
-    const int threads = (cw + 1) * 32;
-    const size_t stage_bytes = (size_t)2 * cw * WF_TILE_BYTES;
-    auto smem_for = [&](int st) { return (size_t)st * stage_bytes + (((size_t)p.M * p.act_stride + 127) & ~(size_t)127) + (size_t)p.sacc_rbs * 512; };
-    while (p.stages > 4 && smem_for(p.stages) > 220 * 1024) --p.stages;
-    const size_t smem = smem_for(p.stages);
+    stream_kernel_t kern = pick_kernel(a->M);
+    const int threads = (SV_CW + 1) * 32;
     if (smem > 220 * 1024) { set_error("gemv_stream: M*K=%d*%d does not fit in shared memory", a->M, a->K); return WF_ERR_UNSUPPORTED; }
     if (smem > g_stream_attr_smem) {
         gemv_stream_init_attrs();

@@ -20,10 +20,11 @@
 
 namespace wf {
 
-constexpr int LS_STAGE_TILES = 16;                        // 8 KB per stage
+constexpr int LS_CW = 12;                                 // consumer warps (3 per scheduler; 2 CTAs/SM must still fit)
+constexpr int LS_TPW = 2;                                 // adjacent tiles per consumer warp per stage (both weight loads issued before the math)
+constexpr int LS_STAGE_TILES = LS_TPW * LS_CW;            // 12 KB per stage
 constexpr int LS_STAGE_BYTES = LS_STAGE_TILES * WF_TILE_BYTES;
-constexpr int LS_STAGES = 8;                              // 64 KB ring
-constexpr int LS_CW = 12;                                 // consumer warps (3 per scheduler: the per-tile LDS -> ldmatrix -> mma chain needs the TLP; 2 CTAs/SM must still fit)
+constexpr int LS_STAGES = 5;                              // 60 KB ring
 constexpr int LS_CT = LS_CW * 32;                         // consumer threads
 constexpr int LS_THREADS = LS_CT + 32;
 
@@ -41,6 +42,15 @@ struct SmallLinParams {
     int32_t* lin_rowsum;
 };
 
+__device__ __forceinline__ int ls_dp4a_us(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// MR = 1: one activation row, CUDA-core path (dp4a on the tile words, int8 codes staged in the permuted order — see
+// gemv_stream.cu); MR = 0: up to 8 rows on mma.sync.m16n8k32 (the batch is the n dimension).
+template <int MR>
 __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const SmallLinParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* ring = smem;                                         // LS_STAGES * LS_STAGE_BYTES
@@ -100,56 +110,59 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
         glue_zero_duty<LS_CT>(p.g);
         for (int m = 0; m < M; ++m) {
             float sc; int rsum;
-            glue_row<1, LS_CT>(p.g, m, ys, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, blockIdx.x == 0, sc, rsum, (tr && m == 0) ? trp + 8 : nullptr);
+            glue_row<1, LS_CT>(p.g, m, ys, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, blockIdx.x == 0, sc, rsum, (tr && m == 0) ? trp + 8 : nullptr,
+                               MR == 1);
             if (blockIdx.x == 0 && tid == 0) { p.lin_ascale[m] = sc; p.lin_rowsum[m] = rsum; }
         }
         group_bar<1, LS_CT>();     // activations complete
         if (tr) trp[3] = gtimer();
 
-        int acc[4][4];
+        constexpr int NACC = MR == 0 ? 16 : 8;
+        int acc[NACC];
 #pragma unroll
-        for (int g = 0; g < 4; ++g)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) acc[g][j] = 0;
+        for (int j = 0; j < NACC; ++j) acc[j] = 0;
         int cur_rb = -1;
-        const int arow = min(lane & 7, M - 1);
-        const unsigned char* abase = acts + arow * p.act_stride + p.k_off + (lane >> 3) * 16;
 
         auto flush = [&](int rb) {
             if (rb < 0) return;
-            const int g = lane >> 2, t = lane & 3;
-            int v[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                v[j] = (acc[0][j] >> 6) + (acc[1][j] >> 4) + (acc[2][j] >> 2) + acc[3][j];
-#pragma unroll
-                for (int gg = 0; gg < 4; ++gg) acc[gg][j] = 0;
-            }
             int* dst = sacc + (rb - rb_first) * 128;
-            const int m = 2 * t;
-            if (m < M) {
-                if (v[0]) atomicAdd(dst + m * 16 + g, v[0]);
-                if (v[2]) atomicAdd(dst + m * 16 + g + 8, v[2]);
-            }
-            if (m + 1 < M) {
-                if (v[1]) atomicAdd(dst + (m + 1) * 16 + g, v[1]);
-                if (v[3]) atomicAdd(dst + (m + 1) * 16 + g + 8, v[3]);
+            if (MR == 0) {
+                const int g = lane >> 2, t = lane & 3;
+                int v[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    v[j] = (acc[0 + j] >> 6) + (acc[4 + j] >> 4) + (acc[8 + j] >> 2) + acc[12 + j];
+#pragma unroll
+                    for (int gg = 0; gg < 4; ++gg) acc[gg * 4 + j] = 0;
+                }
+                const int m = 2 * t;
+                if (m < M) {
+                    if (v[0]) atomicAdd(dst + m * 16 + g, v[0]);
+                    if (v[2]) atomicAdd(dst + m * 16 + g + 8, v[2]);
+                }
+                if (m + 1 < M) {
+                    if (v[1]) atomicAdd(dst + (m + 1) * 16 + g, v[1]);
+                    if (v[3]) atomicAdd(dst + (m + 1) * 16 + g + 8, v[3]);
+                }
+            } else {
+                // acc[r*4 + g]: row (lane/4) + 8r, k-group g; the four lanes of a row hold disjoint k
+#pragma unroll
+                for (int r = 0; r < 2; ++r) {
+                    int v = (acc[r * 4 + 0] >> 6) + (acc[r * 4 + 1] >> 4) + (acc[r * 4 + 2] >> 2) + acc[r * 4 + 3];
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) acc[r * 4 + g] = 0;
+                    v += __shfl_xor_sync(0xffffffffu, v, 1);
+                    v += __shfl_xor_sync(0xffffffffu, v, 2);
+                    if ((lane & 3) == 0 && v) atomicAdd(dst + (lane >> 2) + 8 * r, v);
+                }
             }
         };
 
-        // Tile -> warp mapping: tile i of the slab belongs to warp i % LS_CW; (row-block, k-block) of the warp's next tile
-        // are tracked incrementally (no division on the per-tile path).
-        int i_next = warp;
-        int kb = (int)(t0 - (long long)rb_first * p.KB) + warp, rb = rb_first;
-        while (kb >= p.KB) { kb -= p.KB; ++rb; }
-        for (int it = 0; it < nstages; ++it) {
-            const int s = it % LS_STAGES;
-            mbar_wait(&full_bar[s], (it / LS_STAGES) & 1);
-            const int lim = min(ntiles, (it + 1) * LS_STAGE_TILES);
-            while (i_next < lim) {
-                const int tl = i_next - it * LS_STAGE_TILES;
-                if (rb != cur_rb) { flush(cur_rb); cur_rb = rb; }
-                const uint4 Wv = *reinterpret_cast<const uint4*>(ring + s * LS_STAGE_BYTES + tl * WF_TILE_BYTES + lane * 16);
+        const int KB = p.KB;
+        const int arow = min(lane & 7, M - 1);
+        const unsigned char* abase = MR == 0 ? acts + arow * p.act_stride + p.k_off + (lane >> 3) * 16 : acts + p.k_off + (lane & 3) * 32;
+        auto tile_math = [&](const uint4& Wv, int kb) {
+            if (MR == 0) {
                 uint32_t b[8];
                 const unsigned char* ap = abase + kb * 128;
                 ldmatrix_x4(b[0], b[1], b[2], b[3], ap);
@@ -157,14 +170,54 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
                     const uint32_t mask = 0x03030303u << (6 - 2 * g);   // k-group g sits in bits (7-2g .. 6-2g)
-                    mma_u8s8_16832(acc[g], Wv.x & mask, Wv.y & mask, Wv.z & mask, Wv.w & mask, b[2 * g], b[2 * g + 1]);
+                    int(&d)[4] = *reinterpret_cast<int(*)[4]>(&acc[g * 4]);
+                    mma_u8s8_16832(d, Wv.x & mask, Wv.y & mask, Wv.z & mask, Wv.w & mask, b[2 * g], b[2 * g + 1]);
                 }
-                i_next += LS_CW;
-                kb += LS_CW;
-                while (kb >= p.KB) { kb -= p.KB; ++rb; }
+            } else {
+                const unsigned char* ap = abase + kb * 128;
+                const uint4 a0 = *reinterpret_cast<const uint4*>(ap);        // (g0,h0) (g0,h1) (g1,h0) (g1,h1)
+                const uint4 a1 = *reinterpret_cast<const uint4*>(ap + 16);   // (g2,h0) (g2,h1) (g3,h0) (g3,h1)
+                const uint32_t A[4][2] = {{a0.x, a0.y}, {a0.z, a0.w}, {a1.x, a1.y}, {a1.z, a1.w}};
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const uint32_t mask = 0x03030303u << (6 - 2 * g);
+                    acc[g] = ls_dp4a_us(Wv.x & mask, A[g][0], acc[g]);
+                    acc[4 + g] = ls_dp4a_us(Wv.y & mask, A[g][0], acc[4 + g]);
+                    acc[g] = ls_dp4a_us(Wv.z & mask, A[g][1], acc[g]);
+                    acc[4 + g] = ls_dp4a_us(Wv.w & mask, A[g][1], acc[4 + g]);
+                }
             }
+        };
+
+        // Tile -> warp mapping: a stage holds LS_TPW*LS_CW tiles, warp w owns the LS_TPW adjacent tiles starting at LS_TPW*w;
+        // (row-block, k-block) are tracked incrementally (no division on the per-tile path).
+        int kb0 = (int)(t0 - (long long)rb_first * KB) + LS_TPW * warp, rb0 = rb_first;
+        while (kb0 >= KB) { kb0 -= KB; ++rb0; }
+        const unsigned char* wbase = ring + warp * (LS_TPW * WF_TILE_BYTES) + lane * 16;
+        int s = 0, ph = 0;
+        for (int it = 0; it < nstages; ++it) {
+            mbar_wait(&full_bar[s], ph);
+            const int i0 = it * LS_STAGE_TILES + LS_TPW * warp;
+            if (i0 < ntiles) {
+                const unsigned char* wp = wbase + s * LS_STAGE_BYTES;
+                const bool two = i0 + 1 < ntiles;
+                const uint4 W0 = *reinterpret_cast<const uint4*>(wp);
+                uint4 W1 = make_uint4(0, 0, 0, 0);
+                if (two) W1 = *reinterpret_cast<const uint4*>(wp + WF_TILE_BYTES);
+                int kb1 = kb0 + 1, rb1 = rb0;
+                if (kb1 >= KB) { kb1 = 0; ++rb1; }
+                if (rb0 != cur_rb) { flush(cur_rb); cur_rb = rb0; }
+                tile_math(W0, kb0);
+                if (two) {
+                    if (rb1 != cur_rb) { flush(cur_rb); cur_rb = rb1; }
+                    tile_math(W1, kb1);
+                }
+            }
+            kb0 += LS_STAGE_TILES;
+            while (kb0 >= KB) { kb0 -= KB; ++rb0; }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[s]);
+            if (++s == LS_STAGES) { s = 0; ph ^= 1; }
         }
         flush(cur_rb);
         group_bar<1, LS_CT>();
@@ -253,7 +306,8 @@ int launch_linear_small(const SmallLinArgs& a, cudaStream_t s, bool pdl) {
     cfg.stream = s;
     cudaLaunchAttribute at[1];
     set_pdl(cfg, at, pdl);
-    return launch_check(cudaLaunchKernelEx(&cfg, linear_small_kernel, p), "linear_small");
+    if (a.g.M == 1) return launch_check(cudaLaunchKernelEx(&cfg, linear_small_kernel<1>, p), "linear_small");
+    return launch_check(cudaLaunchKernelEx(&cfg, linear_small_kernel<0>, p), "linear_small");
 }
 
 int launch_glue_rows(const GlueParams& g, cudaStream_t s, bool pdl) {
@@ -311,7 +365,8 @@ int launch_h_exchange(const HExchangeArgs& a, cudaStream_t s, bool pdl) {
 }
 
 void linear_small_init_attrs() {
-    cudaFuncSetAttribute(linear_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(linear_small_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(linear_small_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
     cudaFuncSetAttribute(glue_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
 }
 
