@@ -433,6 +433,24 @@ def run_gpu(args):
         except Exception as ex:  # noqa: BLE001
             aux = {"error": str(ex)}
 
+    # ---------------- kernel-level GEMV bandwidth (the third part of BASELINE's metric): M = 1, > L2 worth of weight copies
+    if world == 1 and not args.no_aux:
+        try:
+            import ctypes as C
+            rows = []
+            for name, (N_, K_) in (("2b_gate|up", (13824, 2560)), ("2b_down", (2560, 6912)), ("8b_gate|up", (28672, 4096)), ("70b_gate|up", (57344, 8192)),
+                                   ("70b_down", (8192, 28672))):
+                ms = C.c_float()
+                check(lib().wf_bench_gemv(N_, K_, 1, 200, 1, C.byref(ms)))
+                byt = N_ * K_ // 4 + K_ + 4 * N_
+                gbs = byt / (ms.value * 1e-3) / 1e9
+                rows.append({"shape": name, "N": N_, "K": K_, "us_per_launch": round(ms.value * 1e3, 2), "algorithmic_bytes": byt, "GBs": round(gbs, 1),
+                             "frac_of_hbm_peak": round(gbs / peak, 4)})
+            aux["gemv_kernel_M1"] = {"method": "wf_bench_gemv: 200 graph-captured launches of ternary_gemv_stream_kernel rotating over > 320 MB of weight copies, "
+                                               "PDL between launches, bytes = N*K/4 + K + 4*N (scripts/benchmark_kernels.py:61-66)", "rows": rows}
+        except Exception as ex:  # noqa: BLE001
+            aux["gemv_kernel_M1"] = {"error": str(ex)}
+
     # ---------------- CPU baseline beside it (rank 0, N = 1 only; bounded sample)
     cpu_baseline = None
     if world == 1 and not args.no_cpu:

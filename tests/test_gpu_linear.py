@@ -44,6 +44,45 @@ def test_accumulators_bit_exact_small_batch(nk, m):
     assert np.array_equal(got, O.gemm_i32_fast(packed, q, 1))
 
 
+@pytest.mark.parametrize("nk,m", [((28672, 4096), 1), ((28672, 4096), 5), ((8192, 8192), 1), ((8192, 8192), 2), ((10240, 8192), 1),
+                                  ((4096, 14336), 2), ((8208, 4096), 1), ((2576, 8192), 4)])
+def test_gemv_large_shapes_every_slab_mode(nk, m):
+    """8B / 70B-sized matrices: two CTAs per SM, whole-row-block slabs (28672x4096), one-group-per-CTA (4096x14336) and the
+    even split with the split-K round (8192x8192, odd row-block counts); dp4a (m = 1) and mma (m > 1) consumers."""
+    from wf_bitnet import ops
+    n, k = nk
+    rng = np.random.default_rng(n + 3 * k + m)
+    w = rng.integers(-1, 2, size=(n, k)).astype(np.float32)
+    packed = O.pack_ternary(w)[0]
+    q = rng.integers(-128, 128, size=(m, k)).astype(np.int8)
+    want = O.gemm_i32_fast(packed, q, 0)
+    tile = ops.i2s_to_tile(cu(packed))
+    for _ in range(2):   # twice: the self-cleaning workspace must be left zero
+        got = ops.ternary_linear(tile, n, k, cu(q), mode="i32_plus1", algo=1).cpu().numpy()
+        assert np.array_equal(got, want)
+
+
+def test_gemv_large_relu2_epilogue():
+    """fused gate|up with relu^2*up at the 8B ffn width through the GEMV (two-row-block finalisation groups, two CTAs per SM)."""
+    from wf_bitnet import ops
+    rng = np.random.default_rng(11)
+    k, ffn, m = 4096, 14336, 3
+    q = rng.integers(-100, 101, size=(m, k)).astype(np.int8)
+    rs = q.astype(np.int64).sum(axis=1).astype(np.int32)
+    s = np.array([0.011, 0.02, 0.007], np.float32)
+    wg = rng.integers(-1, 2, size=(ffn, k)).astype(np.float32)
+    wu = rng.integers(-1, 2, size=(ffn, k)).astype(np.float32)
+    pg, pu = O.pack_ternary(wg)[0], O.pack_ternary(wu)[0]
+    tile_gu = ops.i2s_to_tile(ops.interleave_rows16(cu(pg), cu(pu)))
+    sg, su = np.float32(0.9), np.float32(1.6)
+    g = torch.from_numpy((O.gemm_i32_fast(pg, q, 1).astype(np.float32) * sg) * s[:, None]).to(torch.bfloat16)
+    u = torch.from_numpy((O.gemm_i32_fast(pu, q, 1).astype(np.float32) * su) * s[:, None]).to(torch.bfloat16)
+    want_h = torch.relu(g).square() * u
+    got = ops.ternary_linear(tile_gu, 2 * ffn, k, cu(q), mode="linear", rowsum=cu(rs), act_scale=cu(s),
+                             w_scale=torch.tensor([float(sg), float(su)]).cuda(), relu2_mul=True, out_dtype=torch.bfloat16, algo=1).cpu()
+    assert torch.equal(got, want_h)
+
+
 @pytest.mark.parametrize("nk", [(2560, 2560), (13824, 2560), (2560, 6912), (200, 640)])
 @pytest.mark.parametrize("m", [9, 16, 17, 32, 40, 64, 100])
 def test_accumulators_bit_exact_batched(nk, m):

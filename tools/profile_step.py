@@ -28,6 +28,8 @@ def main():
     ap.add_argument("--shape", default="2b", choices=["2b", "8b", "70b"])
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (0 = the shape's own)")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--tp-shard", type=int, default=0, help="single-GPU stand-in for ONE rank of a TP=n engine: heads, kv heads and ffn divided by n "
+                                                          "(the compute of a rank without the exchanges)")
     args = ap.parse_args()
 
     from wf_bitnet import _lib
@@ -37,9 +39,14 @@ def main():
     torch.cuda.set_device(0)
     mk = {"2b": EngineConfig.bitnet_2b, "8b": EngineConfig.llama3_8b, "70b": EngineConfig.llama3_70b}[args.shape]
     kw = dict(max_seq=args.ctx + 64, page_size=16, max_batch=args.batch)
+    cfg = mk(**kw)
     if args.layers:
-        kw["layers"] = args.layers
-    eng = Engine(mk(**kw))
+        cfg.layers = args.layers
+    if args.tp_shard > 1:
+        cfg.heads //= args.tp_shard
+        cfg.kv_heads //= args.tp_shard
+        cfg.ffn //= args.tp_shard
+    eng = Engine(cfg)
     eng.init_synthetic(1234)
     for slot in range(args.batch):
         eng.set_context(slot, args.ctx, fill_random=False)   # zero KV: same bytes moved, no 16K fill launches

@@ -207,7 +207,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
     const int MB = c.max_batch;
     const int T = e->tp.size;
     const bool tp = T > 1;
-    const bool hx = tp || (e->hx && B <= 8);   // relu^2*up as its own small kernel: always under TP; at B <= 8 it keeps the relu^2 out of every down-proj CTA prologue; glue_rows (B > 8) is per-row and folds it in for free
+    const bool hx = tp || e->hx;   // relu^2*up as its own small kernel (always under TP; measured faster than folding it into the down-proj glue at every batch size)
     float* asc[4] = {e->lin_asc, e->lin_asc + MB, e->lin_asc + 2 * MB, e->lin_asc + 3 * MB};
     int32_t* rs[4] = {e->lin_rs, e->lin_rs + MB, e->lin_rs + 2 * MB, e->lin_rs + 3 * MB};
     __nv_bfloat16 *hA = e->hid, *hB = e->hid2;

@@ -51,9 +51,10 @@ __device__ __forceinline__ int ld_relaxed_gpu(const int* p) {
 // last publishes flag `id` = step + 1 on all ranks.  `nblocks` = total CTAs of the grid.
 __device__ __forceinline__ void tp_signal_grid_done(const TpComm& c, int id, int nblocks) {
     if (c.size <= 1) return;
-    __threadfence_system();          // this thread's peer writes are visible system-wide ...
-    __syncthreads();                 // ... for all threads of the CTA, before the CTA's arrival
+    __syncthreads();                 // every thread's peer stores / REDs happen-before thread 0's fence (CTA barrier) ...
     if (threadIdx.x == 0) {
+        __threadfence_system();      // ... which makes them visible system-wide before the CTA's arrival (ONE membar.sys per CTA:
+                                     // a fence per thread serialises tens of thousands of system-scope fences behind NVLink)
         const int prev = atomicAdd(c.done_cnt + id, 1);
         if (prev == nblocks - 1) {
             c.done_cnt[id] = 0;      // self-cleaning for the next step
@@ -74,8 +75,7 @@ __device__ __forceinline__ void tp_wait_flags_warp(const TpComm& c, int id) {
         const int* f = tp_flag_ptr(c, c.rank, id, lane);
         while (ld_acquire_sys(f) < want) { __nanosleep(20); }
     }
-    __syncwarp();
-    __threadfence_system();
+    __syncwarp();                    // ld.acquire.sys + the caller's CTA barrier order everything that follows after the peers' writes
 }
 
 }  // namespace wf
