@@ -142,7 +142,7 @@ def _run_tokens(cfg, w, fused, steps, monkeypatch, ctx=None, synthetic=None):
     return outs
 
 
-@pytest.mark.parametrize("B", [1, 3, 8, 12, 33])
+@pytest.mark.parametrize("B", [1, 3, 8, 12, 33, 40, 64])
 def test_phase_kernels_equal_per_op_kernels(B, monkeypatch):
     """The fused phase path (glue prologues, raw fp32 accumulators, fused attention) and the one-kernel-per-op path share
     every rounding point of the reference step, so their logits must be IDENTICAL, not merely close."""
@@ -159,7 +159,7 @@ def test_phase_kernels_equal_per_op_kernels(B, monkeypatch):
         assert (na == nb).all()
 
 
-@pytest.mark.parametrize("B,ctx", [(1, 500), (4, 700), (16, 1200)])
+@pytest.mark.parametrize("B,ctx", [(1, 500), (4, 700), (16, 1200), (40, 100), (64, 300)])
 def test_phase_kernels_equal_per_op_kernels_2b_shape(B, ctx, monkeypatch):
     """same identity at the BitNet-2B layer shapes (split attention chunks, 54 k-blocks) on a 4-layer slice"""
     from wf_bitnet.engine import EngineConfig
@@ -170,5 +170,22 @@ def test_phase_kernels_equal_per_op_kernels_2b_shape(B, ctx, monkeypatch):
     b = _run_tokens(cfg, None, False, steps, monkeypatch, ctx=ctx, synthetic=5)
     for i, ((la, na, _), (lb, nb, _)) in enumerate(zip(a, b)):
         assert torch.isfinite(la).all()
+        assert torch.equal(la, lb), (i, (la - lb).abs().max().item())
+        assert (na == nb).all()
+
+
+@pytest.mark.parametrize("B,ctx", [(40, 100), (64, 300)])
+def test_tcgen05_decode_linears_equal_per_op_kernels(B, ctx, monkeypatch):
+    """WF_DECODE_TC=1: the batched decode linears on tcgen05 kind::i8 with split-K fp32 REDs (gemm_tc.cu, decode form) give the
+    same logits, bit for bit, as the one-kernel-per-op path at the 2B layer shapes."""
+    from wf_bitnet.engine import EngineConfig
+    cfg = EngineConfig.bitnet_2b(max_seq=2048, max_batch=B, layers=3, vocab=4096)
+    rng = np.random.default_rng(17 + B)
+    steps = [list(map(int, rng.integers(0, cfg.vocab, B))) for _ in range(3)]
+    monkeypatch.setenv("WF_DECODE_TC", "1")
+    a = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=ctx, synthetic=5)
+    monkeypatch.setenv("WF_DECODE_TC", "0")
+    b = _run_tokens(cfg, None, False, steps, monkeypatch, ctx=ctx, synthetic=5)
+    for i, ((la, na, _), (lb, nb, _)) in enumerate(zip(a, b)):
         assert torch.equal(la, lb), (i, (la - lb).abs().max().item())
         assert (na == nb).all()

@@ -72,6 +72,7 @@ struct wf_engine {
     bool pdl = false;
     int linear_algo = 0;
     int hx = 1;              // relu^2(gate)*up in its own small kernel instead of every down-proj CTA's prologue (WF_HX=0 to fold it back)
+    int decode_tc = 0;       // WF_DECODE_TC=1: batched decode linears (B > 32) on tcgen05 split-K REDs instead of the mma.sync one-shot GEMM (parity-identical; measured equal in step time, both latency-bound — see DESIGN.md)
     int fused = 1;           // 1: phase kernels (linear_small / glue_rows + gemm_oneshot / fused attention); 0: one kernel per op
     // fused path state: raw fp32 accumulators of the four linears, their per-token activation scale / Sigma a,
     // a second hidden buffer (residual ping-pong) and the attention merge counters
@@ -213,12 +214,21 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
     __nv_bfloat16 *hA = e->hid, *hB = e->hid2;
     int rc;
     int trace_slot = 0;
+    // Row-parallel linears (o, down) under TP.  B <= 8: every CTA's prologue needs the whole reduced vector locally -> all-reduce
+    // (RED into every rank).  B > 8: reduce-scatter (RED into the owner of the column only, 1/T of the NVLink packets) and the
+    // per-row glue of the consumer pulls each column from its owner.
+    const bool scatter = tp && B > 8 && (e->hidden % (8 * T)) == 0;
+    const int own_cols = scatter ? e->hidden / T : 0;
     auto local_dest = [&](float* acc) { TpDest d = {}; d.n = 1; d.acc[0] = acc; d.signal_flag = -1; return d; };
     auto all_dest = [&](size_t off, int flag) {
         TpDest d = {};
-        d.n = T; d.signal_flag = tp ? flag : -1;
+        d.n = T; d.signal_flag = tp ? flag : -1; d.own_cols = own_cols;
         for (int r = 0; r < T; ++r) d.acc[r] = reinterpret_cast<float*>(e->tp.peer[r] + off);
         return d;
+    };
+    auto pull_from = [&](GlueParams& g, size_t off) {
+        g.acc_own_cols = own_cols;
+        if (scatter) for (int r = 0; r < T; ++r) g.acc_peer[r] = reinterpret_cast<const float*>(e->tp.peer[r] + off);
     };
     // one linear phase: prologue over the full activation vector of length Kfull, GEMV/GEMM over this rank's K columns
     auto phase = [&](GlueParams g, const uint8_t* w, int N, int Kfull, int K, int k_off, const TpDest& dest, int slot, bool first) -> int {
@@ -232,6 +242,8 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
         g.q_out = e->q8; g.scale_out = asc[slot]; g.rowsum_out = rs[slot];
         int r = launch_glue_rows(g, s, pdl && !first);
         if (r) return r;
+        // a real dense contraction (33..64 tokens): tcgen05 int8 with split-K REDs; single-GPU engines only for now
+        if (e->decode_tc && !tp && B > 32 && N % 8 == 0) return launch_gemm_tc_red(w, N, K, e->q8, B, Kfull, k_off, dest.acc[0], N, s, pdl);
         OneshotArgs o;
         o.w = w; o.N = N; o.K = K; o.q = e->q8; o.M = B; o.ldq = Kfull; o.k_off = k_off; o.dest = dest; o.acc_ld = N; o.tp = e->tp;
         return launch_gemm_oneshot(o, s, pdl);
@@ -248,6 +260,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
             else {
                 g.mode = GL_RESID; g.hid_in = hA; g.acc = e->acc_down; g.acc_ld = e->hidden;
                 g.acc_rowsum = rs[3]; g.acc_ascale = asc[3]; g.acc_wscale = e->layers[l - 1].scales + 6;
+                pull_from(g, e->off_acc_down);
                 if (tp) g.wait_flag = fE - 4;
             }
             g.hid_out = hB; g.gamma = L.g_in;
@@ -264,7 +277,10 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
             for (int r = 0; r < T; ++r) a.out_peer[r] = e->tp.peer[r] + e->off_attn;
             a.qkv_acc = e->acc_qkv; a.qkv_ld = e->qkv_rows; a.qkv_rowsum = rs[0]; a.qkv_ascale = asc[0]; a.qkv_wscale = L.scales;
             a.cos_tab = e->cos_tab; a.sin_tab = e->sin_tab; a.max_pos = c.max_seq;
-            a.merge_cnt = e->merge_cnt; a.zero0 = e->acc_down; a.zero0_n = B * e->hidden;
+            a.merge_cnt = e->merge_cnt;
+            // acc_down of the previous layer is cleared here — except under TP, where a peer may still be pulling / a slower
+            // rank still reading it: there phase C clears it (it sits behind the attention all-gather flags of ALL ranks)
+            a.zero0 = tp ? nullptr : e->acc_down; a.zero0_n = tp ? 0 : B * e->hidden;
             a.max_seq_hint = e->attn_seq_hint; a.ws = e->ws_attn; a.ws_bytes = e->ws_attn_bytes;
             if (e->trace) a.trace = e->trace + (size_t)32 * (4 * c.layers + 4 + l);
             if ((rc = attn_decode_fused(a, s, pdl))) return rc;
@@ -274,6 +290,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
             GlueParams g = {};
             g.mode = GL_PLAIN; g.src = e->attn; g.gamma = L.g_attn; g.wait_flag = tp ? fB : -1;
             g.zero0 = e->acc_qkv; g.zero0_n = B * e->qkv_rows;
+            if (tp) { g.zero1 = e->acc_down; g.zero1_n = B * e->hidden; }
             if ((rc = phase(g, L.o, e->hidden, e->attn_full, e->attn_dim, e->tp.rank * e->attn_dim, all_dest(e->off_acc_o, fC), 1, false))) return rc;
         }
         // ---- D: hidden + o-proj -> post_attention_layernorm -> gate|up (this rank's ffn rows)
@@ -281,6 +298,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
             GlueParams g = {};
             g.mode = GL_RESID; g.hid_in = hB; g.hid_out = hA; g.acc = e->acc_o; g.acc_ld = e->hidden;
             g.acc_rowsum = rs[1]; g.acc_ascale = asc[1]; g.acc_wscale = L.scales + 3; g.gamma = L.g_post; g.wait_flag = tp ? fC : -1;
+            pull_from(g, e->off_acc_o);
             if ((rc = phase(g, L.gu, 2 * e->ffn, e->hidden, e->hidden, 0, local_dest(e->acc_gu), 2, false))) return rc;
         }
         // ---- D' (TP only): relu^2(gate)*up of the local slice -> h_full of every rank
@@ -312,6 +330,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
         g.mode = GL_RESID; g.M = B; g.K = e->hidden; g.eps = c.eps; g.tp = e->tp; g.wait_flag = tp ? fLM - 1 : -1;
         g.hid_in = hA; g.hid_out = hB; g.acc = e->acc_down; g.acc_ld = e->hidden;
         g.acc_rowsum = rs[3]; g.acc_ascale = asc[3]; g.acc_wscale = e->layers[c.layers - 1].scales + 6;
+        pull_from(g, e->off_acc_down);
         g.gamma = e->final_norm; g.y_out = e->normed; g.q_out = e->q8;
         if ((rc = launch_glue_rows(g, s, pdl))) return rc;
     }
@@ -432,6 +451,7 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     e->fused = env_fused ? atoi(env_fused) != 0 : 1;
     if (T > 1) e->fused = 1;                   // the exchanges live in the phase kernels
     { const char* x = getenv("WF_HX"); if (x) e->hx = atoi(x) != 0; }
+    { const char* x = getenv("WF_DECODE_TC"); if (x) e->decode_tc = atoi(x) != 0; }
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
     int rc = WF_OK;
     auto fail = [&](int r) { wf_engine_destroy(e); return r; };

@@ -32,6 +32,10 @@ struct GlueParams {
     const __nv_bfloat16* src;       // GL_PLAIN: [M][K]
     const float* acc;               // GL_RESID: [M][acc_ld]; GL_RELU2: gate|up interleaved in 16-row blocks
     int acc_ld;
+    // tensor parallel, batched path: the accumulator is reduce-SCATTERED — column k lives on rank k / acc_own_cols and is
+    // pulled from that rank's buffer over NVLink (0 = the local buffer holds every column)
+    const float* acc_peer[TP_MAX];
+    int acc_own_cols;
     const int32_t* acc_rowsum;      // [M] Sigma a of the linear that produced acc
     const float* acc_ascale;        // [M] its per-token activation scale
     const float* acc_wscale;        // device: [1] (RESID) or [2] gate, up (RELU2)
@@ -59,6 +63,7 @@ __device__ __forceinline__ unsigned long long gtimer() {
 // on every rank — the all-reduce is the RED itself
 struct TpDest {
     int n;                          // destinations (1 = local only)
+    int own_cols;                   // > 0: reduce-scatter — column n is added on rank n / own_cols only (acc[] indexed by rank)
     float* acc[TP_MAX];
     int signal_flag;                // flag id published when the whole grid has finished its REDs, -1 = none
 };
@@ -214,7 +219,10 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
 #pragma unroll
             for (int u = 0; u < GU; ++u) {
                 const int k = k0 + u * NT * 8;
-                if (k < K) { t[u] = ldcg_u4(hrow + k); a0[u] = ldcg_f4(arow + k); a1[u] = ldcg_f4(arow + k + 4); }
+                if (k < K) {
+                    const float* ak = (p.acc_own_cols > 0 ? p.acc_peer[k / p.acc_own_cols] + (size_t)m * p.acc_ld : arow) + k;
+                    t[u] = ldcg_u4(hrow + k); a0[u] = ldcg_f4(ak); a1[u] = ldcg_f4(ak + 4);
+                }
             }
 #pragma unroll
             for (int u = 0; u < GU; ++u) {

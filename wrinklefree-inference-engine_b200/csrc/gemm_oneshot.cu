@@ -77,14 +77,17 @@ __global__ void __launch_bounds__(GO_T) gemm_oneshot_kernel(const OneshotParams 
     __syncthreads();
 
     const bool warp_active = (wb * 32) < p.M;
+    const int nt_cnt = min(4, (p.M - wb * 32 + 7) >> 3);   // 8-token column tiles this warp really has (M = 16: two, not four)
     if (warp_active) {
         for (int kbl = 0; kbl < kc; ++kbl) {
             uint32_t b[4][8];
 #pragma unroll
             for (int nt = 0; nt < 4; ++nt) {
-                const unsigned char* ap = as + (size_t)((wb * 4 + nt) * 8 + (lane & 7)) * a_stride + kbl * 128 + (lane >> 3) * 16;
-                ldmatrix_x4(b[nt][0], b[nt][1], b[nt][2], b[nt][3], ap);
-                ldmatrix_x4(b[nt][4], b[nt][5], b[nt][6], b[nt][7], ap + 64);
+                if (nt < nt_cnt) {
+                    const unsigned char* ap = as + (size_t)((wb * 4 + nt) * 8 + (lane & 7)) * a_stride + kbl * 128 + (lane >> 3) * 16;
+                    ldmatrix_x4(b[nt][0], b[nt][1], b[nt][2], b[nt][3], ap);
+                    ldmatrix_x4(b[nt][4], b[nt][5], b[nt][6], b[nt][7], ap + 64);
+                }
             }
 #pragma unroll
             for (int i = 0; i < RBW; ++i) {
@@ -95,7 +98,8 @@ __global__ void __launch_bounds__(GO_T) gemm_oneshot_kernel(const OneshotParams 
                     const uint32_t a0 = (Wv.x >> sh) & 0x03030303u, a1 = (Wv.y >> sh) & 0x03030303u;
                     const uint32_t a2 = (Wv.z >> sh) & 0x03030303u, a3 = (Wv.w >> sh) & 0x03030303u;
 #pragma unroll
-                    for (int nt = 0; nt < 4; ++nt) mma_u8s8_16832(acc[i][nt], a0, a1, a2, a3, b[nt][2 * g], b[nt][2 * g + 1]);
+                    for (int nt = 0; nt < 4; ++nt)
+                        if (nt < nt_cnt) mma_u8s8_16832(acc[i][nt], a0, a1, a2, a3, b[nt][2 * g], b[nt][2 * g + 1]);
                 }
             }
         }
@@ -129,7 +133,11 @@ __global__ void __launch_bounds__(GO_T) gemm_oneshot_kernel(const OneshotParams 
         const float4 v = *reinterpret_cast<const float4*>(St + ml * SS + 4 * c);
         if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) {
             // row-parallel linears under TP: the RED into every rank's accumulator IS the all-reduce
-            for (int d = 0; d < p.dest.n; ++d) red_add_v4_f32(p.dest.acc[d] + (size_t)ml * p.acc_ld + n, v.x, v.y, v.z, v.w);
+            // all-reduce = the RED into every rank's accumulator; reduce-scatter (own_cols > 0) = the RED into the owner's only:
+            // 1/T of the NVLink packets, the consumer pulls the columns from their owners
+            if (p.dest.own_cols > 0) red_add_v4_f32(p.dest.acc[n / p.dest.own_cols] + (size_t)ml * p.acc_ld + n, v.x, v.y, v.z, v.w);
+            else
+                for (int d = 0; d < p.dest.n; ++d) red_add_v4_f32(p.dest.acc[d] + (size_t)ml * p.acc_ld + n, v.x, v.y, v.z, v.w);
         }
     }
     if (p.dest.signal_flag >= 0) tp_signal_grid_done(p.tp, p.dest.signal_flag, gridDim.x * gridDim.y);

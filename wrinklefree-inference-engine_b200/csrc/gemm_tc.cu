@@ -24,8 +24,10 @@
 // 128 B/clk at the floor, so the epilogue's transpose traffic serialises) — the cta_group::2 form (each SM holds
 // half of the activation tile) is the next step.
 #include "linear_common.cuh"
+#include "fused_common.cuh"
 #include <cuda.h>
 #include <stdlib.h>
+#include <string.h>
 
 namespace wf {
 
@@ -48,6 +50,12 @@ struct TcParams {
     int M, N, K, KB;
     int tiles_n, tiles_m;
     int dbg;   // timing experiments only (WF_TC_DBG): 1 = epilogue skips math/stores, 2 = also skips the TMEM loads
+    // batched-decode form (launch_gemm_tc_red): the K dimension is cut into `splitk` equal runs of KBs k-blocks, one CTA
+    // tile each, and the epilogue adds the raw accumulators into a global fp32 buffer (exact: integers < 2^24) instead
+    // of storing a finished output — the consumer phase of the decode step applies scales / residual / norm.
+    int splitk, KBs;
+    float* red_acc;
+    int red_ld;
     EpiParams ep;
 };
 
@@ -122,14 +130,18 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
     const int crank = (CL > 1) ? (int)(blockIdx.x % CL) : 0;          // 1-D cluster: rank == blockIdx.x % CL
     const int cluster_id = blockIdx.x / CL, n_clusters = gridDim.x / CL;
     const int ngroups = (p.tiles_n + CL - 1) / CL;                    // groups of CL weight-row tiles
-    const int total_tiles = ngroups * p.tiles_m;                      // cluster tiles
+    const int total_tiles = ngroups * p.tiles_m * p.splitk;           // cluster tiles (x K-splits in the decode form)
     const int my_tiles = (total_tiles - cluster_id + n_clusters - 1) / n_clusters;
-    const int n_items = my_tiles * p.KB;
-    auto tile_coords = [&](int tl, int& m_blk, int& n_blk) {
-        const int ct = cluster_id + tl * n_clusters;
+    const int KBs = p.KBs;                                            // k-blocks per tile (== KB unless split)
+    const int n_items = my_tiles * KBs;
+    auto tile_coords = [&](int tl, int& m_blk, int& n_blk, int& ks) {
+        const int ct0 = cluster_id + tl * n_clusters;
+        ks = ct0 % p.splitk;                                          // splits of one tile run side by side
+        const int ct = ct0 / p.splitk;
         m_blk = ct / ngroups;
         n_blk = (ct - m_blk * ngroups) * CL + crank;                  // may be >= tiles_n (padding tile: epilogue masks it)
     };
+    pdl_launch_dependents();   // no-op unless launched with programmatic stream serialisation (decode step)
 
     if (tid == 0) {
         for (int s = 0; s < TC_STAGES; ++s) { mbar_init(&full_bar[s], 5); mbar_init(&empty_bar[s], CL); }
@@ -154,22 +166,24 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
         // ------------------------------------------------------------ TMA producer: int8 activations
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_q) : "memory");
+            pdl_wait_prior();   // the activations are the previous kernel's output (the weights are not: unpack warps run ahead)
             int it = 0;
             constexpr int SLICE = TC_BN / CL;   // tokens this CTA fetches for the whole cluster
             for (int tl = 0; tl < my_tiles; ++tl) {
-                int m_blk, n_blk;
-                tile_coords(tl, m_blk, n_blk);
-                for (int kb = 0; kb < p.KB; ++kb, ++it) {
+                int m_blk, n_blk, ks;
+                tile_coords(tl, m_blk, n_blk, ks);
+                for (int kb = 0; kb < KBs; ++kb, ++it) {
+                    const int kg = ks * KBs + kb;
                     const int s = it % TC_STAGES;
                     mbar_wait(&empty_bar[s], (uint32_t)(((it / TC_STAGES) & 1) ^ 1));   // all CL CTAs retired this slot
                     mbar_expect_tx(&full_bar[s], TC_STAGE_BYTES);                        // own barrier: all CL slices land here
                     const uint32_t dst = ring + s * TC_STAGE_BYTES + crank * SLICE * TC_BK;
                     if (CL == 1)
                         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                                     ::"r"(dst), "l"(&tmap_q), "r"(kb * TC_BK), "r"(m_blk * TC_BN), "r"(smem_u32(&full_bar[s])) : "memory");
+                                     ::"r"(dst), "l"(&tmap_q), "r"(kg * TC_BK), "r"(m_blk * TC_BN), "r"(smem_u32(&full_bar[s])) : "memory");
                     else
                         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%2, %3}], [%4], %5;"
-                                     ::"r"(dst), "l"(&tmap_q), "r"(kb * TC_BK), "r"(m_blk * TC_BN + crank * SLICE), "r"(smem_u32(&full_bar[s])),
+                                     ::"r"(dst), "l"(&tmap_q), "r"(kg * TC_BK), "r"(m_blk * TC_BN + crank * SLICE), "r"(smem_u32(&full_bar[s])),
                                        "h"((uint16_t)((1u << CL) - 1)) : "memory");
                 }
             }
@@ -189,7 +203,7 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
             mbar_wait(&tempty_bar[buf], (uint32_t)(((tl >> 1) & 1) ^ 1));
             tc_fence_after();
             const uint32_t d_tmem = tmem + buf * TC_BN;
-            for (int kb = 0; kb < p.KB; ++kb) {
+            for (int kb = 0; kb < KBs; ++kb) {
                 {   // wait for the TMA bytes and the four unpack warps of this stage
                     uint32_t ok;
                     do {
@@ -231,15 +245,16 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
         const uint32_t kb_stride = i2s ? 32u : (uint32_t)WF_TILE_BYTES;
         const uint8_t* rowbase = p.w;
         auto set_tile = [&](int tl) {
-            int m_blk, n_blk;
-            tile_coords(tl, m_blk, n_blk);
+            int m_blk, n_blk, ks;
+            tile_coords(tl, m_blk, n_blk, ks);
             int row = n_blk * TC_BM + q * 32 + lane;
             if (row >= p.N) row = p.N - 1;   // padded rows compute garbage that the epilogue masks
             // b200_tile_v1: word (16*(r&7) + 4*(j&3) + 2*(j>>2) + (r>>3)) of tile (row/16, kb) holds packed bytes [4j,4j+4) of row r
             rowbase = i2s ? p.w + (size_t)row * K4
                           : p.w + (size_t)(row >> 4) * p.KB * WF_TILE_BYTES + (size_t)(16 * (row & 7) + ((row >> 3) & 1)) * 4;
+            rowbase += (size_t)ks * KBs * kb_stride;   // this tile's K run
         };
-        while (ld_kb >= p.KB) { ld_kb -= p.KB; ++ld_tl; }
+        while (ld_kb >= KBs) { ld_kb -= KBs; ++ld_tl; }
         set_tile(ld_tl);
         auto load_item = [&](uint32_t (&r)[8]) {
             if (ld_item >= n_items) return;
@@ -253,8 +268,8 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
             }
             ld_item += NU;
             ld_kb += NU;
-            if (ld_kb >= p.KB) {
-                do { ld_kb -= p.KB; ++ld_tl; } while (ld_kb >= p.KB);
+            if (ld_kb >= KBs) {
+                do { ld_kb -= KBs; ++ld_tl; } while (ld_kb >= KBs);
                 set_tile(ld_tl);
             }
         };
@@ -310,9 +325,11 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
         const int ncols = relu2 ? p.N / 2 : p.N;
         const bool vec_ok = (((size_t)p.ep.ldo * esize) % 16 == 0) && (((uintptr_t)p.ep.out & 15) == 0) &&
                             (!resid || (((uintptr_t)p.ep.residual & 15) == 0));
+        const bool red = p.red_acc != nullptr;
+        if (red) pdl_wait_prior();   // the accumulator buffer was cleared by an earlier phase of the step
         for (int tl = 0; tl < my_tiles; ++tl) {
-            int m_blk, n_blk;
-            tile_coords(tl, m_blk, n_blk);
+            int m_blk, n_blk, ks;
+            tile_coords(tl, m_blk, n_blk, ks);
             const int buf = tl & 1;
             mbar_wait(&tfull_bar[buf], (uint32_t)((tl >> 1) & 1));
             tc_fence_after();
@@ -355,6 +372,19 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
                         const int4 sa4 = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + oct * 32);
                         const int4 sb4 = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + oct * 32 + 16);
                         const int S[8] = {sa4.x, sa4.y, sa4.z, sa4.w, sb4.x, sb4.y, sb4.z, sb4.w};
+                        if (red) {
+                            // decode form: exact fp32 RED of the raw accumulators (split-K partial sums meet in L2)
+                            float* op = p.red_acc + (size_t)m * p.red_ld + c0;
+                            if (nvalid == 8) {
+                                red_add_v4_f32(op, (float)S[0], (float)S[1], (float)S[2], (float)S[3]);
+                                red_add_v4_f32(op + 4, (float)S[4], (float)S[5], (float)S[6], (float)S[7]);
+                            } else {
+#pragma unroll
+                                for (int e = 0; e < 8; ++e)
+                                    if (e < nvalid) red_add_f32(op + e, (float)S[e]);
+                            }
+                            continue;
+                        }
                         const int rs = p.ep.rowsum ? p.ep.rowsum[m] : 0;
                         const size_t o = (size_t)m * p.ep.ldo + c0;
                         if (mode == WF_OUT_LINEAR) {
@@ -494,6 +524,7 @@ static int launch_tc_cl(const wf_linear_args* a, const EpiParams& ep, cudaStream
     p.tiles_n = (a->N + TC_BM - 1) / TC_BM;
     p.tiles_m = (a->M + TC_BN - 1) / TC_BN;
     p.ep = ep;
+    p.splitk = 1; p.KBs = p.KB; p.red_acc = nullptr; p.red_ld = 0;
     { const char* d = getenv("WF_TC_DBG"); p.dbg = d ? atoi(d) : 0; }
     const int total = ((p.tiles_n + CL - 1) / CL) * p.tiles_m;
     cudaLaunchConfig_t cfg = {};
@@ -518,6 +549,52 @@ static int launch_tc_cl(const wf_linear_args* a, const EpiParams& ep, cudaStream
     const int clusters = total < max_clusters ? total : max_clusters;
     cfg.gridDim = dim3(clusters * CL);
     return launch_check(cudaLaunchKernelEx(&cfg, ternary_gemm_tc_kernel<CL, NU>, tmap, p), "ternary_gemm_tc");
+}
+
+// Batched-decode form (the engine's phase kernels, 32 < M <= 128): S[m][n] += sum over this launch's K columns, added into the
+// global fp32 accumulator `acc` ([M][acc_ld], zero on entry of the step phase) exactly like gemm_oneshot does — but on the
+// tcgen05 int8 pipe (mma.sync int8 is a slow legacy path on sm_100: the M = 64 linears were IMMA-bound).  The (rows x K)
+// plane is cut into 128-row x KBs-k-block tiles so that ~one tile lands on every SM; split-K partial sums meet in L2.
+int launch_gemm_tc_red(const uint8_t* w_tile, int N, int K, const int8_t* q, int M, int ldq, int k_off, float* acc, int acc_ld,
+                       cudaStream_t s, bool pdl) {
+    gemm_tc_init_attrs();
+    if (!g_tc_attr || !g_encode) { set_error("gemm_tc: tcgen05 path unavailable (driver entry point / smem attribute)"); return WF_ERR_CUDA; }
+    if (M < 1 || M > TC_BN || K % WF_QK || k_off % WF_QK || ldq % 16 || acc_ld % 4 || N % 8) { set_error("gemm_tc_red: unsupported shape"); return WF_ERR_UNSUPPORTED; }
+    constexpr int NU = 3;
+    CUtensorMap tmap;
+    const cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)M};
+    const cuuint64_t gstride[1] = {(cuuint64_t)ldq};
+    const cuuint32_t box[2] = {TC_BK, TC_BN};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult cr = g_encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void*)(q + k_off), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                 CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) { set_error("gemm_tc_red: cuTensorMapEncodeTiled failed (%d)", (int)cr); return WF_ERR_CUDA; }
+    TcParams p;
+    memset(&p, 0, sizeof p);
+    p.w = w_tile; p.w_layout = WF_W_TILE;
+    p.M = M; p.N = N; p.K = K; p.KB = K / WF_QK;
+    p.tiles_n = (N + TC_BM - 1) / TC_BM;
+    p.tiles_m = 1;
+    p.ep.M = M; p.ep.N = N; p.ep.out_mode = WF_OUT_I32_PLUS1; p.ep.nseg = 1; p.ep.ldo = acc_ld; p.ep.out = acc;
+    p.red_acc = acc; p.red_ld = acc_ld;
+    // largest divisor of KB that still gives every SM at most one tile
+    const int sms = sm_count();
+    int split = 1;
+    for (int d = 1; d <= p.KB; ++d)
+        if (p.KB % d == 0 && p.tiles_n * d <= sms) split = d;
+    p.splitk = split; p.KBs = p.KB / split;
+    const int total = p.tiles_n * split;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(total < sms ? total : sms);
+    cfg.blockDim = dim3((4 + 4 * NU + 2) * 32);
+    cfg.dynamicSmemBytes = TC_SMEM;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return launch_check(cudaLaunchKernelEx(&cfg, ternary_gemm_tc_kernel<1, NU>, tmap, p), "ternary_gemm_tc(decode)");
 }
 
 int launch_gemm_tc(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s) {

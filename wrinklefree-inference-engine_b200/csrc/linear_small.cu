@@ -226,13 +226,25 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
         if (ntiles > 0) {
             const int rb_last = (int)((t1 - 1) / p.KB);
             const int n_rbs = rb_last - rb_first + 1;
-            for (int i = tid; i < n_rbs * 128; i += LS_CT) {
-                const int rbl = i >> 7, m = (i >> 4) & 7, r = i & 15;
-                const int n = (rb_first + rbl) * 16 + r;
-                const int v = sacc[i];
-                if (m < M && n < p.N && v) {
-                    // row-parallel linears under TP: the RED into every rank's accumulator IS the all-reduce
-                    for (int d = 0; d < p.dest.n; ++d) red_add_f32(p.dest.acc[d] + (size_t)m * p.acc_ld + n, (float)v);
+            if ((p.N & 3) == 0 && (p.acc_ld & 3) == 0) {
+                // four consecutive rows of one token per RED.v4: a quarter of the NVLink packets under tensor parallelism
+                for (int i = tid; i < n_rbs * 32; i += LS_CT) {
+                    const int rbl = i >> 5, m = (i >> 2) & 7, r = (i & 3) * 4;
+                    const int n = (rb_first + rbl) * 16 + r;
+                    const int4 v = *reinterpret_cast<const int4*>(sacc + rbl * 128 + m * 16 + r);
+                    if (m < M && n < p.N && (v.x | v.y | v.z | v.w)) {
+                        // row-parallel linears under TP: the RED into every rank's accumulator IS the all-reduce
+                        for (int d = 0; d < p.dest.n; ++d)
+                            red_add_v4_f32(p.dest.acc[d] + (size_t)m * p.acc_ld + n, (float)v.x, (float)v.y, (float)v.z, (float)v.w);
+                    }
+                }
+            } else {
+                for (int i = tid; i < n_rbs * 128; i += LS_CT) {
+                    const int rbl = i >> 7, m = (i >> 4) & 7, r = i & 15;
+                    const int n = (rb_first + rbl) * 16 + r;
+                    const int v = sacc[i];
+                    if (m < M && n < p.N && v)
+                        for (int d = 0; d < p.dest.n; ++d) red_add_f32(p.dest.acc[d] + (size_t)m * p.acc_ld + n, (float)v);
                 }
             }
         }
@@ -244,7 +256,7 @@ __global__ void __launch_bounds__(LS_THREADS, 2) linear_small_kernel(const Small
 
 // ---------------------------------------------------------------------------------------------------------------
 // Standalone glue for large batch: grid = M rows, 256 threads; int8 codes / scale / rowsum go to global.
-constexpr int GR_T = 256;
+constexpr int GR_T = 512;   // one pass iteration for K <= 4096, two for the 2B ffn width
 __global__ void __launch_bounds__(GR_T) glue_rows_kernel(const GlueParams p) {
     extern __shared__ __align__(16) unsigned char gsm[];
     __nv_bfloat16* ys = reinterpret_cast<__nv_bfloat16*>(gsm);

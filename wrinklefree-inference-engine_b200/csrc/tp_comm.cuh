@@ -51,16 +51,22 @@ __device__ __forceinline__ int ld_relaxed_gpu(const int* p) {
 // last publishes flag `id` = step + 1 on all ranks.  `nblocks` = total CTAs of the grid.
 __device__ __forceinline__ void tp_signal_grid_done(const TpComm& c, int id, int nblocks) {
     if (c.size <= 1) return;
-    __syncthreads();                 // every thread's peer stores / REDs happen-before thread 0's fence (CTA barrier) ...
-    if (threadIdx.x == 0) {
-        __threadfence_system();      // ... which makes them visible system-wide before the CTA's arrival (ONE membar.sys per CTA:
+    __syncthreads();                 // every thread's peer stores / REDs happen-before warp 0's fences (CTA barrier) ...
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        int last = 0;
+        if (lane == 0) {
+            __threadfence_system();  // ... which make them visible system-wide before the CTA's arrival (ONE membar.sys per CTA:
                                      // a fence per thread serialises tens of thousands of system-scope fences behind NVLink)
-        const int prev = atomicAdd(c.done_cnt + id, 1);
-        if (prev == nblocks - 1) {
-            c.done_cnt[id] = 0;      // self-cleaning for the next step
-            __threadfence_system();
+            const int prev = atomicAdd(c.done_cnt + id, 1);
+            last = (prev == nblocks - 1);
+            if (last) { c.done_cnt[id] = 0; __threadfence(); }   // self-cleaning; acquire the other CTAs' arrivals (their fence + atomic)
+        }
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (last && lane < c.size) {
+            // one lane per peer: the T release stores (each a fence + an NVLink round trip) go out side by side, not in sequence
             const int val = ld_relaxed_gpu(c.step) + 1;
-            for (int r = 0; r < c.size; ++r) st_release_sys(tp_flag_ptr(c, r, id, c.rank), val);
+            st_release_sys(tp_flag_ptr(c, lane, id, c.rank), val);
         }
     }
 }
