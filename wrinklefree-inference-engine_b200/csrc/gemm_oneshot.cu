@@ -11,6 +11,7 @@
 // red.global.add.v4.f32 (integers < 2^24: exact, order-independent).  The consumer of the accumulator
 // (glue_rows_kernel / attention prologue) applies scales, residual, norm and re-quantisation.
 #include "fused_common.cuh"
+#include <type_traits>
 
 namespace wf {
 
@@ -78,12 +79,15 @@ __global__ void __launch_bounds__(GO_T) gemm_oneshot_kernel(const OneshotParams 
 
     const bool warp_active = (wb * 32) < p.M;
     const int nt_cnt = min(4, (p.M - wb * 32 + 7) >> 3);   // 8-token column tiles this warp really has (M = 16: two, not four)
-    if (warp_active) {
+    // FULL = all four 8-token column tiles of this warp are live (compile-time trip counts: the predicated form costs
+    // ~7 us per launch at M = 64); otherwise only nt_cnt of them (M = 16: two — half the IMMA work)
+    auto main_loop = [&](auto full_tag) {
+        constexpr bool FULL = decltype(full_tag)::value;
         for (int kbl = 0; kbl < kc; ++kbl) {
             uint32_t b[4][8];
 #pragma unroll
             for (int nt = 0; nt < 4; ++nt) {
-                if (nt < nt_cnt) {
+                if (FULL || nt < nt_cnt) {
                     const unsigned char* ap = as + (size_t)((wb * 4 + nt) * 8 + (lane & 7)) * a_stride + kbl * 128 + (lane >> 3) * 16;
                     ldmatrix_x4(b[nt][0], b[nt][1], b[nt][2], b[nt][3], ap);
                     ldmatrix_x4(b[nt][4], b[nt][5], b[nt][6], b[nt][7], ap + 64);
@@ -99,10 +103,14 @@ __global__ void __launch_bounds__(GO_T) gemm_oneshot_kernel(const OneshotParams 
                     const uint32_t a2 = (Wv.z >> sh) & 0x03030303u, a3 = (Wv.w >> sh) & 0x03030303u;
 #pragma unroll
                     for (int nt = 0; nt < 4; ++nt)
-                        if (nt < nt_cnt) mma_u8s8_16832(acc[i][nt], a0, a1, a2, a3, b[nt][2 * g], b[nt][2 * g + 1]);
+                        if (FULL || nt < nt_cnt) mma_u8s8_16832(acc[i][nt], a0, a1, a2, a3, b[nt][2 * g], b[nt][2 * g + 1]);
                 }
             }
         }
+    };
+    if (warp_active) {
+        if (nt_cnt == 4) main_loop(std::true_type{});
+        else main_loop(std::false_type{});
     }
     __syncthreads();   // everyone is done with the load buffers
 
