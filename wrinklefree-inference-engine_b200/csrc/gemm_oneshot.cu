@@ -28,7 +28,7 @@ struct OneshotParams {
     TpComm tp;
 };
 
-template <int RBW>
+template <int RBW, bool FULLM>   // FULLM: M is a multiple of 32, every active warp owns four live 8-token tiles
 __global__ void __launch_bounds__(GO_T) gemm_oneshot_kernel(const OneshotParams p) {
     constexpr int RBS = 4 * RBW;        // row-blocks per CTA
     constexpr int RT = 16 * RBS;        // rows per CTA
@@ -108,10 +108,7 @@ __global__ void __launch_bounds__(GO_T) gemm_oneshot_kernel(const OneshotParams 
             }
         }
     };
-    if (warp_active) {
-        if (nt_cnt == 4) main_loop(std::true_type{});
-        else main_loop(std::false_type{});
-    }
+    if (warp_active) main_loop(std::integral_constant<bool, FULLM>{});
     __syncthreads();   // everyone is done with the load buffers
 
     // ---- accumulators -> St[m][RT] (fp32, stride RT+4) -> vectorised exact RED
@@ -151,7 +148,7 @@ __global__ void __launch_bounds__(GO_T) gemm_oneshot_kernel(const OneshotParams 
     if (p.dest.signal_flag >= 0) tp_signal_grid_done(p.tp, p.dest.signal_flag, gridDim.x * gridDim.y);
 }
 
-template <int RBW>
+template <int RBW, bool FULLM>
 static int launch_rbw(const OneshotParams& p, cudaStream_t s, bool pdl) {
     constexpr int RBS = 4 * RBW;
     const size_t smem_load = (size_t)RBS * p.KC * WF_TILE_BYTES + (size_t)GO_MT * (p.KC * 128 + 16);
@@ -167,7 +164,7 @@ static int launch_rbw(const OneshotParams& p, cudaStream_t s, bool pdl) {
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl ? 1 : 0;
-    return launch_check(cudaLaunchKernelEx(&cfg, gemm_oneshot_kernel<RBW>, p), "gemm_oneshot");
+    return launch_check(cudaLaunchKernelEx(&cfg, gemm_oneshot_kernel<RBW, FULLM>, p), "gemm_oneshot");
 }
 
 static int g_kc_max = 0;
@@ -192,14 +189,17 @@ int launch_gemm_oneshot(const OneshotArgs& a, cudaStream_t s, bool pdl) {
     const int kcmax = wide ? (g_kc_max > 5 ? g_kc_max - 1 : g_kc_max) : g_kc_max;
     const int splits = (p.KB + kcmax - 1) / kcmax;
     p.KC = (p.KB + splits - 1) / splits;
-    return wide ? launch_rbw<2>(p, s, pdl) : launch_rbw<1>(p, s, pdl);
+    if (p.M % 32 == 0) return wide ? launch_rbw<2, true>(p, s, pdl) : launch_rbw<1, true>(p, s, pdl);
+    return wide ? launch_rbw<2, false>(p, s, pdl) : launch_rbw<1, false>(p, s, pdl);
 }
 
 void linear_small_init_attrs();
 void fused_init_attrs() {
     linear_small_init_attrs();
-    cudaFuncSetAttribute(gemm_oneshot_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-    cudaFuncSetAttribute(gemm_oneshot_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(gemm_oneshot_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(gemm_oneshot_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(gemm_oneshot_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(gemm_oneshot_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
 }
 
 }  // namespace wf
