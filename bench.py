@@ -32,6 +32,9 @@ for p in (str(ROOT), str(PKG)):
     if p not in sys.path:
         sys.path.insert(0, p)
 
+if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":   # keeps "NCCL version ..." off stdout: rank 0 prints ONE JSON line
+    os.environ["NCCL_DEBUG"] = "WARN"
+
 import numpy as np
 import torch
 

@@ -119,3 +119,14 @@ def test_act_scale_needs_no_fp64():
     lim = np.float32(1e-6)
     assert float(lim) < 1e-6 < float(np.nextafter(lim, np.float32(1)))
     assert np.array_equal(a.astype(np.float64) < 1e-6, a <= lim)
+
+
+def test_cache_key_matches_reference_and_separates_pack_formats():
+    """cache/cache_key.py:9-45 — golden keys produced by the reference's own function (imported from /root/reference when this
+    test was written); the B200 tile format gets a key of its own."""
+    from wrinklefree_inference.cache import compute_cache_key
+    assert compute_cache_key("microsoft/bitnet-b1.58-2B-4T") == "microsoft_bitnet_b1_58_2B_4T_7573223ca919"
+    assert compute_cache_key("microsoft/bitnet-b1.58-2B-4T", "abc123") == "microsoft_bitnet_b1_58_2B_4T_e3cc8c56ba2c"
+    assert compute_cache_key("HF1BitLLM/Llama3-8B-1.58-100B-tokens") == "HF1BitLLM_Llama3_8B_1_58_100B_tokens_61cd867e670d"
+    k = compute_cache_key("microsoft/bitnet-b1.58-2B-4T", pack_format="b200_tile_v1")
+    assert k.startswith("microsoft_bitnet_b1_58_2B_4T_") and k != "microsoft_bitnet_b1_58_2B_4T_7573223ca919"
