@@ -130,3 +130,12 @@ def test_cache_key_matches_reference_and_separates_pack_formats():
     assert compute_cache_key("HF1BitLLM/Llama3-8B-1.58-100B-tokens") == "HF1BitLLM_Llama3_8B_1_58_100B_tokens_61cd867e670d"
     k = compute_cache_key("microsoft/bitnet-b1.58-2B-4T", pack_format="b200_tile_v1")
     assert k.startswith("microsoft_bitnet_b1_58_2B_4T_") and k != "microsoft_bitnet_b1_58_2B_4T_7573223ca919"
+
+
+def test_sglang_model_mirror_imports_without_gpu():
+    """tests/test_vllm_cpu_stub.py:346-354: the model module must import on a CUDA-less host; detection helpers are host logic."""
+    import torch
+    from sglang.srt.models.bitnet import BitNetForCausalLM, BitNetLinear, EntryClass, _is_packed_weight, _is_ternary_float
+    assert EntryClass is BitNetForCausalLM and BitNetLinear is not None
+    assert _is_packed_weight(torch.zeros(8, 4, dtype=torch.uint8)) and not _is_packed_weight(torch.zeros(8, 16))
+    assert _is_ternary_float(torch.tensor([[-1.0, 0.0, 1.0]])) and not _is_ternary_float(torch.tensor([[0.5]]))
