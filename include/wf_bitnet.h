@@ -34,6 +34,7 @@ extern "C" {
 #define WF_F32 0
 #define WF_BF16 1
 #define WF_F16 2
+#define WF_I8 3 /* KV pools only: int8 codes + one fp32 scale per (token, kv head) */
 
 /* ---- library ------------------------------------------------------------------------ */
 
@@ -144,7 +145,9 @@ int wf_bitnet_gemm(const uint8_t* packed_i2s, const int8_t* x, float scale, int 
 typedef struct wf_kv_layout {
     void* pool;
     int max_pages, layers, kv_heads, page_size, head_dim;
-    int dtype; /* WF_BF16 | WF_F32 (f32 only for the KVCacheManager scatter/gather API) */
+    int dtype; /* WF_BF16 | WF_I8 | WF_F32 (f32 only for the KVCacheManager scatter/gather API). WF_I8: the reference's
+                  KVCacheDtype.INT8 (kv_cache/kv_cache.py:198-228) at (token, head) granularity; k / v rows handed to
+                  scatter / gather are bf16; pool = int8 region followed by the fp32 scale region (wf_kv_pool_bytes) */
 } wf_kv_layout;
 
 size_t wf_kv_pool_bytes(int max_pages, int layers, int kv_heads, int page_size, int head_dim, int dtype);
@@ -200,6 +203,7 @@ typedef struct wf_model_config {
     int max_batch;
     int max_pages;  /* KV pool pages */
     int tp_rank, tp_size; /* tensor parallel (1 = off); see INTEGRATION.md */
+    int kv_dtype;         /* 0 or WF_BF16: bf16 KV pool; WF_I8: int8 KV pool (half the attention bytes) */
 } wf_model_config;
 
 typedef struct wf_engine wf_engine;

@@ -75,6 +75,24 @@ def bitnet_linear(x: torch.Tensor, packed: np.ndarray, scale: float, use_ref: bo
     return out.to(torch.bfloat16)
 
 
+def kv_int8_quant(x: torch.Tensor):
+    """KVCache._quantize_to_int8 (kv_cache/kv_cache.py:198-218) applied per (token, head) row instead of once per update call:
+    scale = 127 / absmax (absmax < 1e-6 -> 1), codes = clamp(round(x * scale), -127, 127), stored scale = absmax / 127.
+    x: [..., D] (bf16 or fp32).  Returns (int8 codes, fp32 dequant scales [..., 1]).  fp32 arithmetic, round-half-even."""
+    xf = x.float()
+    amax = xf.abs().amax(dim=-1, keepdim=True)
+    amax = torch.where(amax < 1e-6, torch.ones_like(amax), amax)
+    inv = torch.tensor(127.0, dtype=torch.float32) / amax
+    codes = (xf * inv).round().clamp(-127, 127).to(torch.int8)
+    return codes, amax / torch.tensor(127.0, dtype=torch.float32)
+
+
+def kv_int8_roundtrip(x: torch.Tensor) -> torch.Tensor:
+    """What KVCache.get returns for an INT8 cache: (codes.float() * scale).to(bf16)  (kv_cache.py:220-228)."""
+    codes, sc = kv_int8_quant(x)
+    return (codes.float() * sc).to(torch.bfloat16)
+
+
 class OracleModel:
     """DirectBitNetInference (direct_inference_full.py:73-302) on caller-supplied weights.
 
@@ -83,10 +101,12 @@ class OracleModel:
         "<p>_proj": u8 I2_S [N,K/4], "<p>_scale": float  for p in q,k,v,o,gate,up,down } ]}
     """
 
-    def __init__(self, cfg: ModelConfig, weights: Dict, use_ref: bool = True):
+    def __init__(self, cfg: ModelConfig, weights: Dict, use_ref: bool = True, kv_int8: bool = False):
         self.cfg = cfg
         self.w = weights
         self.use_ref = use_ref
+        self.kv_int8 = kv_int8   # KVCacheDtype.INT8: what the cache returns is dequant(quant(x)), see kv_int8_roundtrip
+        self.taps: Dict = {}     # ("q"|"k"|"v"|"attn", layer) of the last forward: q, k (after RoPE) / v before the cache, attention output
         self.rope = RotaryEmbedding(cfg.head_dim, cfg.max_seq, cfg.rope_theta)
         self.k_cache = torch.zeros(cfg.layers, cfg.max_seq, cfg.kv_heads, cfg.head_dim, dtype=torch.bfloat16)
         self.v_cache = torch.zeros_like(self.k_cache)
@@ -101,6 +121,9 @@ class OracleModel:
         v = self._lin(hidden, layer, "v").view(c.kv_heads, c.head_dim)
         q = self.rope.rotate(q, pos)
         k = self.rope.rotate(k, pos)
+        self.taps[("q", li)], self.taps[("k", li)], self.taps[("v", li)] = q, k, v
+        if self.kv_int8:
+            k, v = kv_int8_roundtrip(k), kv_int8_roundtrip(v)
         self.k_cache[li, pos] = k
         self.v_cache[li, pos] = v
         k_seq = self.k_cache[li, : pos + 1]
@@ -110,6 +133,7 @@ class OracleModel:
         v_attn = v_seq.transpose(0, 1).unsqueeze(0)
         attn_out = F.scaled_dot_product_attention(q_attn, k_attn, v_attn, enable_gqa=True)
         attn_out = attn_out.squeeze(0).squeeze(1).flatten()
+        self.taps[("attn", li)] = attn_out
         attn_out = rms_norm(attn_out, layer["attn_sub_norm"], c.eps)
         return self._lin(attn_out, layer, "o")
 

@@ -15,6 +15,8 @@
 //   the streaming loop and ~100 KB of loads stay in flight per SM.  The G = H/Hkv query heads of a KV
 //   head form the (padded) M=16 rows of mma.m16n8k16 bf16: S = Q K^T (fp32), online softmax in fp32 with
 //   exp2, O += P V.  Warps are merged through shared memory; chunks are merged by a second tiny kernel.
+#include <cuda_fp16.h>
+
 #include "fused_common.cuh"
 
 namespace wf {
@@ -26,6 +28,51 @@ constexpr int AT_D = 128;                               // head_dim (all BASELIN
 constexpr int AT_ROW = AT_D * 2;                        // bytes per token row
 constexpr int AT_STAGE_BYTES = 2 * AT_BLK * AT_ROW;     // K + V
 constexpr int AT_SMEM = AT_WARPS * AT_STAGES * AT_STAGE_BYTES;   // 96 KB
+
+// ---- int8 KV option (the reference's KVCacheDtype.INT8, kv_cache/kv_cache.py:198-228): K and V are int8
+// with one fp32 scale per (token, kv head).  Pool = int8 region [page][layer][K|V][head][slot][D] followed by the scale
+// region [page][layer][K|V][head][slot].  The streaming loop moves half the bytes: int8 rows go through the same cp.async
+// ring (6 stages of 4 KB + 128 B of scales), ldmatrix reads them as b16 pairs and ONE PRMT per f16x2 operand register turns
+// two codes into f16: codes are stored offset-binary (u = code + 128) and 0x6400 | u is the f16 value 1024 + u = code + 1152,
+// exactly.  The constant 1152 is not subtracted per element: S = sum q (code + 1152) - 1152 sum q and
+// O = sum p (code + 1152) - 1152 sum p, i.e. one correction per score / per output row (fp32 accumulators: the offset costs
+// ~3 of 24 bits).  The MMAs are f16 instead of bf16.  The K scale multiplies the score column, the V scale the probability
+// (times 2^8 to stay clear of f16 subnormals; undone exactly at the end).
+// The d index inside a 16-wide granule is permuted identically for Q and K (k = 4t.. instead of 2t.., 2t+8..).
+constexpr int AT8_ROW = AT_D;
+constexpr int AT8_STAGES = 6;
+constexpr int AT8_SCALE_OFF = 2 * AT_BLK * AT8_ROW;                 // 16 K scales | 16 V scales
+constexpr int AT8_STAGE_BYTES = AT8_SCALE_OFF + 2 * AT_BLK * 4;     // 4224
+constexpr int AT8_SMEM = AT_WARPS * AT8_STAGES * AT8_STAGE_BYTES;   // 101,376
+constexpr float AT8_PV_UP = 256.f, AT8_PV_DOWN = 1.f / 256.f;
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
+// two offset-binary bytes of y (selected by `sel`) -> f16x2 of (code + 1152)
+__device__ __forceinline__ uint32_t u8pair_to_f16x2(uint32_t y, uint32_t sel) { return prmt(y, 0x64646464u, sel); }
+constexpr float AT8_BIAS = 1152.f;
+__device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
+    __half2 t = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ void mma_f16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// per-(token, head) symmetric int8 quantisation, the reference's arithmetic (kv_cache.py:198-218) at token granularity:
+// scale = 127 / absmax (absmax < 1e-6 -> 1), code = clamp(round(x * scale), -127, 127), stored dequant scale = absmax / 127
+__device__ __forceinline__ float kv8_inv(float& amax) {
+    if (amax < 1e-6f) amax = 1.0f;
+    return __fdiv_rn(127.0f, amax);
+}
+__device__ __forceinline__ int kv8_code(float x, float inv) { return (int)fminf(fmaxf(rintf(__fmul_rn(x, inv)), -127.f), 127.f); }
+__device__ __forceinline__ uint8_t kv8_store(float x, float inv) { return (uint8_t)(kv8_code(x, inv) + 128); }   // offset binary
+__device__ __forceinline__ float kv8_scale(float amax) { return __fdiv_rn(amax, 127.0f); }
 
 struct AttnParams {
     const __nv_bfloat16* q;      // [B][H][D]
@@ -60,6 +107,7 @@ struct AttnParams {
     int n_out, out_ld, out_col0, signal_flag;
     TpComm tp;
     unsigned long long* trace;
+    float* kv_scales;            // int8 KV: scale region of the pool (null = bf16 pool)
 };
 
 // final output element (b, local head h, d): local buffer, or the attn_full buffer of every rank (the all-gather)
@@ -79,8 +127,15 @@ __device__ __forceinline__ size_t kv_block_offset(int page, int layers, int laye
     return ((((size_t)page * layers + layer) * 2 + kv) * Hkv + head) * (size_t)page_size * AT_D;
 }
 
-template <bool FUSED>
+__device__ __forceinline__ size_t kv_scale_offset(int page, int layers, int layer, int kv, int Hkv, int head, int page_size) {
+    return ((((size_t)page * layers + layer) * 2 + kv) * Hkv + head) * (size_t)page_size;
+}
+
+template <bool FUSED, bool I8>
 __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(const AttnParams p) {
+    constexpr int ST = I8 ? AT8_STAGES : AT_STAGES;
+    constexpr int SB = I8 ? AT8_STAGE_BYTES : AT_STAGE_BYTES;
+    constexpr int ROW = I8 ? AT8_ROW : AT_ROW;
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int chunk = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
@@ -99,7 +154,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
     const bool active = !(blk0 >= nblocks && chunk != 0);
     const int blk1 = min(nblocks, blk0 + p.chunk_blocks);
     const int my_n = active ? (blk1 - blk0 - warp + AT_WARPS - 1) / AT_WARPS : 0;   // blocks blk0 + warp + 4*i
-    unsigned char* wsm = smem + warp * (AT_STAGES * AT_STAGE_BYTES);
+    unsigned char* wsm = smem + warp * (ST * SB);
     const int32_t* bt = p.block_table + (size_t)b * p.max_blocks;
 
     auto issue = [&](int i) {   // i-th block of this warp -> stage i % AT_STAGES
@@ -108,25 +163,48 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
             const int tok0 = blk * AT_BLK;
             const int page = bt[tok0 / p.page_size];
             const int slot0 = tok0 % p.page_size;
-            const __nv_bfloat16* kb = p.pool + kv_block_offset(page, p.layers, p.layer, 0, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
-            const __nv_bfloat16* vb = p.pool + kv_block_offset(page, p.layers, p.layer, 1, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
-            unsigned char* ks = wsm + (i % AT_STAGES) * AT_STAGE_BYTES;
-            unsigned char* vs = ks + AT_BLK * AT_ROW;
+            const size_t ko = kv_block_offset(page, p.layers, p.layer, 0, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
+            const size_t vo = kv_block_offset(page, p.layers, p.layer, 1, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
+            unsigned char* ks = wsm + (i % ST) * SB;
+            unsigned char* vs = ks + AT_BLK * ROW;
             const int valid = seq_len - tok0;   // tokens >= valid are zero-filled (pool slots may be uninitialised)
+            if (!I8) {
+                const unsigned char* kb = reinterpret_cast<const unsigned char*>(p.pool + ko);
+                const unsigned char* vb = reinterpret_cast<const unsigned char*>(p.pool + vo);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int gi = lane + 32 * j;
-                const int r = gi >> 4, c = gi & 15;
-                const int dst = r * AT_ROW + ((c ^ (r & 7)) << 4);
-                const int nb = (r < valid) ? 16 : 0;
-                cp_async16_zfill(ks + dst, reinterpret_cast<const unsigned char*>(kb) + gi * 16, nb);
-                cp_async16_zfill(vs + dst, reinterpret_cast<const unsigned char*>(vb) + gi * 16, nb);
+                for (int j = 0; j < 8; ++j) {
+                    const int gi = lane + 32 * j;
+                    const int r = gi >> 4, c = gi & 15;
+                    const int dst = r * ROW + ((c ^ (r & 7)) << 4);
+                    const int nb = (r < valid) ? 16 : 0;
+                    cp_async16_zfill(ks + dst, kb + gi * 16, nb);
+                    cp_async16_zfill(vs + dst, vb + gi * 16, nb);
+                }
+            } else {
+                const unsigned char* kb = reinterpret_cast<const unsigned char*>(p.pool) + ko;
+                const unsigned char* vb = reinterpret_cast<const unsigned char*>(p.pool) + vo;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int gi = lane + 32 * j;
+                    const int r = gi >> 3, c = gi & 7;
+                    const int dst = r * ROW + ((c ^ (r & 7)) << 4);
+                    const int nb = (r < valid) ? 16 : 0;
+                    cp_async16_zfill(ks + dst, kb + gi * 16, nb);
+                    cp_async16_zfill(vs + dst, vb + gi * 16, nb);
+                }
+                // 16 K scales | 16 V scales, 16-byte granules through L2 (.cg): a scale appended by another CTA in this
+                // launch must never be served from a stale L1 line
+                if (lane < 8) {
+                    const int kv = lane >> 2, q4 = (lane & 3) * 4;
+                    const float* sc = p.kv_scales + kv_scale_offset(page, p.layers, p.layer, kv, p.Hkv, kvh, p.page_size) + slot0 + q4;
+                    cp_async16_zfill(ks + AT8_SCALE_OFF + lane * 16, sc, 4 * max(0, min(4, valid - q4)));
+                }
             }
         }
         cp_async_commit();
     };
     int pre = 0;   // stages issued before the dependency wait
-    while (pre < AT_STAGES - 1 && (pre >= my_n || blk0 + warp + AT_WARPS * pre < blk_pos)) { issue(pre); ++pre; }
+    while (pre < ST - 1 && (pre >= my_n || blk0 + warp + AT_WARPS * pre < blk_pos)) { issue(pre); ++pre; }
 
     pdl_wait_prior();
     if (tr) p.trace[1] = gtimer();
@@ -147,8 +225,15 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
         const __nv_bfloat16* qrow = p.q + ((size_t)b * p.H + (size_t)kvh * p.G + g) * AT_D;
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
-            qa[ks][0] = (g < p.G) ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 2 * t) : 0u;
-            qa[ks][1] = (g < p.G) ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8 + 2 * t) : 0u;
+            if (!I8) {
+                qa[ks][0] = (g < p.G) ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 2 * t) : 0u;
+                qa[ks][1] = (g < p.G) ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8 + 2 * t) : 0u;
+            } else {   // d = 16 ks + 4t .. 4t+3 (the order the int8 K bytes come out of ldmatrix), bf16 -> f16 is exact here
+                uint2 w = make_uint2(0u, 0u);
+                if (g < p.G) w = *reinterpret_cast<const uint2*>(qrow + ks * 16 + 4 * t);
+                qa[ks][0] = pack_f16x2(bf16lo(w.x), bf16hi(w.x));
+                qa[ks][1] = pack_f16x2(bf16lo(w.y), bf16hi(w.y));
+            }
         }
     } else {
         // dequantise the qkv accumulator (direct_inference_full.py:204-206), round to bf16 as the linear's output
@@ -167,7 +252,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
             float2 xa[8], xb[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const int d = (i >> 1) * 16 + (i & 1) * 8 + 2 * t;   // < 64; partner at d + 64
+                const int d = I8 ? (i >> 1) * 16 + 4 * t + 2 * (i & 1) : (i >> 1) * 16 + (i & 1) * 8 + 2 * t;   // < 64; partner at d + 64
                 xa[i] = make_float2(0.f, 0.f);
                 xb[i] = make_float2(0.f, 0.f);
                 if (g < p.G) {
@@ -178,7 +263,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int ks = i >> 1, half = i & 1;
-                const int d = ks * 16 + half * 8 + 2 * t;
+                const int d = I8 ? ks * 16 + 4 * t + 2 * half : ks * 16 + half * 8 + 2 * t;
                 const float a[2] = {xa[i].x, xa[i].y}, bq[2] = {xb[i].x, xb[i].y};
                 float o1[2], o2[2];
 #pragma unroll
@@ -192,8 +277,8 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
                     o1[e] = bf16_round(x1 * c) - bf16_round(x2 * sn);
                     o2[e] = bf16_round(x1 * sn) + bf16_round(x2 * c);
                 }
-                qa[ks][half] = pack_bf16x2(o1[0], o1[1]);
-                qa[ks + 4][half] = pack_bf16x2(o2[0], o2[1]);
+                qa[ks][half] = I8 ? pack_f16x2(bf16_round(o1[0]), bf16_round(o1[1])) : pack_bf16x2(o1[0], o1[1]);
+                qa[ks + 4][half] = I8 ? pack_f16x2(bf16_round(o2[0]), bf16_round(o2[1])) : pack_bf16x2(o2[0], o2[1]);
             }
         }
         // the CTA whose chunk holds the new token appends k (RoPE'd) and v before it streams that block
@@ -202,21 +287,40 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
             const int page = bt[pos / p.page_size];
             const int slot = pos % p.page_size;
             const int d = tid & 63;
-            if (tid < 64) {
+            const int kv = tid >> 6;   // warps 0,1: k   warps 2,3: v
+            float y1, y2;              // the bf16 values the bf16 cache would hold at d and d + 64
+            if (kv == 0) {
                 const float wk = p.qkv_wscale[1];
                 const float* hk = arow + ((size_t)p.H + kvh) * AT_D;
                 const float x1 = bf16_round(lin_value(ldcg_f(hk + d), rs, wk, sa));
                 const float x2 = bf16_round(lin_value(ldcg_f(hk + d + 64), rs, wk, sa));
                 const float c = __bfloat162float(ct[d]), s = __bfloat162float(st[d]);
-                __nv_bfloat16* dst = p.pool_w + kv_block_offset(page, p.layers, p.layer, 0, p.Hkv, kvh, p.page_size) + (size_t)slot * AT_D;
-                dst[d] = __float2bfloat16_rn(bf16_round(x1 * c) - bf16_round(x2 * s));
-                dst[d + 64] = __float2bfloat16_rn(bf16_round(x1 * s) + bf16_round(x2 * c));
+                y1 = bf16_round(bf16_round(x1 * c) - bf16_round(x2 * s));
+                y2 = bf16_round(bf16_round(x1 * s) + bf16_round(x2 * c));
             } else {
                 const float wv = p.qkv_wscale[2];
                 const float* hv = arow + ((size_t)p.H + p.Hkv + kvh) * AT_D;
-                __nv_bfloat16* dst = p.pool_w + kv_block_offset(page, p.layers, p.layer, 1, p.Hkv, kvh, p.page_size) + (size_t)slot * AT_D;
-                dst[d] = __float2bfloat16_rn(lin_value(ldcg_f(hv + d), rs, wv, sa));
-                dst[d + 64] = __float2bfloat16_rn(lin_value(ldcg_f(hv + d + 64), rs, wv, sa));
+                y1 = bf16_round(lin_value(ldcg_f(hv + d), rs, wv, sa));
+                y2 = bf16_round(lin_value(ldcg_f(hv + d + 64), rs, wv, sa));
+            }
+            const size_t off = kv_block_offset(page, p.layers, p.layer, kv, p.Hkv, kvh, p.page_size) + (size_t)slot * AT_D;
+            if (!I8) {
+                __nv_bfloat16* dst = p.pool_w + off;
+                dst[d] = __float2bfloat16_rn(y1);
+                dst[d + 64] = __float2bfloat16_rn(y2);
+            } else {
+                __shared__ float s_amax[AT_WARPS];
+                float am = fmaxf(fabsf(y1), fabsf(y2));
+#pragma unroll
+                for (int o = 16; o; o >>= 1) am = fmaxf(am, __shfl_xor_sync(0xffffffffu, am, o));
+                if (lane == 0) s_amax[warp] = am;
+                __syncthreads();
+                float amax = fmaxf(s_amax[2 * kv], s_amax[2 * kv + 1]);
+                const float inv = kv8_inv(amax);
+                uint8_t* dst = reinterpret_cast<uint8_t*>(p.pool_w) + off;
+                dst[d] = kv8_store(y1, inv);
+                dst[d + 64] = kv8_store(y2, inv);
+                if (d == 0) p.kv_scales[kv_scale_offset(page, p.layers, p.layer, kv, p.Hkv, kvh, p.page_size) + slot] = kv8_scale(amax);
             }
             __threadfence();
             __syncthreads();
@@ -228,31 +332,68 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
 #pragma unroll
     for (int j = 0; j < 16; ++j) { o[j][0] = 0.f; o[j][1] = 0.f; o[j][2] = 0.f; o[j][3] = 0.f; }
     float m_run = -INFINITY, l_run = 0.f;   // row g (replicated over the 4 lanes of a group)
+    float c_run = 0.f, q_bias = 0.f;        // int8 KV: running sum of the f16 P operands (per lane); 1152 * sum_d q[g][d]
+    if (I8) {
+        float qs = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+            const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&qa[ks][0]));
+            const float2 c = __half22float2(*reinterpret_cast<const __half2*>(&qa[ks][1]));
+            qs += (a.x + a.y) + (c.x + c.y);
+        }
+        qs += __shfl_xor_sync(0xffffffffu, qs, 1);
+        qs += __shfl_xor_sync(0xffffffffu, qs, 2);
+        q_bias = AT8_BIAS * qs;
+    }
 
-    for (int s = pre; s < AT_STAGES - 1; ++s) issue(s);
+    for (int s = pre; s < ST - 1; ++s) issue(s);
 
     for (int i = 0; i < my_n; ++i) {
-        issue(i + AT_STAGES - 1);
-        cp_async_wait<AT_STAGES - 1>();
+        issue(i + ST - 1);
+        cp_async_wait<ST - 1>();
         __syncwarp();
-        const unsigned char* ks = wsm + (i % AT_STAGES) * AT_STAGE_BYTES;
-        const unsigned char* vs = ks + AT_BLK * AT_ROW;
+        const unsigned char* ks = wsm + (i % ST) * SB;
+        const unsigned char* vs = ks + AT_BLK * ROW;
         const int tok0 = (blk0 + warp + AT_WARPS * i) * AT_BLK;
 
         // ---- S = Q K^T : 16 (heads) x 16 (tokens)
         float s[2][4];
 #pragma unroll
         for (int nt = 0; nt < 2; ++nt) { s[nt][0] = 0.f; s[nt][1] = 0.f; s[nt][2] = 0.f; s[nt][3] = 0.f; }
-        {
+        if (!I8) {
             const int r = (lane & 7) + ((lane >> 4) << 3);   // token row supplied by this lane
             const int gsel = (lane >> 3) & 1;                // granule parity supplied by this lane
 #pragma unroll
             for (int ks_i = 0; ks_i < 8; ++ks_i) {
                 const int c = 2 * ks_i + gsel;
                 uint32_t b0, b1, b2, b3;
-                ldmatrix_x4(b0, b1, b2, b3, ks + r * AT_ROW + ((c ^ (r & 7)) << 4));
+                ldmatrix_x4(b0, b1, b2, b3, ks + r * ROW + ((c ^ (r & 7)) << 4));
                 mma_bf16_16816(s[0], qa[ks_i][0], 0u, qa[ks_i][1], 0u, b0, b1);
                 mma_bf16_16816(s[1], qa[ks_i][0], 0u, qa[ks_i][1], 0u, b2, b3);
+            }
+        } else {
+            // matrices: (tokens 0-7, granule 2i) (tokens 8-15, 2i) (tokens 0-7, 2i+1) (tokens 8-15, 2i+1); a register is the
+            // int8 d = 16c + 4t .. 4t+3 of token g: bytes (0,1) are the k slots 2t,2t+1 and bytes (2,3) the slots 2t+8,2t+9
+            const int r = (lane & 7) + (((lane >> 3) & 1) << 3);
+            const int gsel = lane >> 4;
+#pragma unroll
+            for (int i2 = 0; i2 < 4; ++i2) {
+                const int c = 2 * i2 + gsel;
+                uint32_t r0, r1, r2, r3;
+                ldmatrix_x4(r0, r1, r2, r3, ks + r * ROW + ((c ^ (r & 7)) << 4));
+                mma_f16_16816(s[0], qa[2 * i2][0], 0u, qa[2 * i2][1], 0u, u8pair_to_f16x2(r0, 0x4140u), u8pair_to_f16x2(r0, 0x4342u));
+                mma_f16_16816(s[1], qa[2 * i2][0], 0u, qa[2 * i2][1], 0u, u8pair_to_f16x2(r1, 0x4140u), u8pair_to_f16x2(r1, 0x4342u));
+                mma_f16_16816(s[0], qa[2 * i2 + 1][0], 0u, qa[2 * i2 + 1][1], 0u, u8pair_to_f16x2(r2, 0x4140u), u8pair_to_f16x2(r2, 0x4342u));
+                mma_f16_16816(s[1], qa[2 * i2 + 1][0], 0u, qa[2 * i2 + 1][1], 0u, u8pair_to_f16x2(r3, 0x4140u), u8pair_to_f16x2(r3, 0x4342u));
+            }
+        }
+        float2 ksc[2], vsc[2];   // int8 KV: scales of tokens 8nt + 2t, +1
+        if (I8) {
+            const float* scs = reinterpret_cast<const float*>(ks + AT8_SCALE_OFF);
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) {
+                ksc[nt] = *reinterpret_cast<const float2*>(scs + nt * 8 + 2 * t);
+                vsc[nt] = *reinterpret_cast<const float2*>(scs + AT_BLK + nt * 8 + 2 * t);
             }
         }
         // ---- online softmax for row g over this block's 16 tokens (columns 8nt+2t, 8nt+2t+1)
@@ -262,7 +403,9 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 const int tok = tok0 + nt * 8 + 2 * t + e;
-                const float v = (tok < seq_len) ? s[nt][e] * p.scale_log2e : -INFINITY;
+                float sv = s[nt][e];
+                if (I8) sv = (sv - q_bias) * (e ? ksc[nt].y : ksc[nt].x);
+                const float v = (tok < seq_len) ? sv * p.scale_log2e : -INFINITY;
                 s[nt][e] = v;
                 mx = fmaxf(mx, v);
             }
@@ -276,9 +419,18 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
             const float p00 = exp2f(s[0][0] - m_new), p01 = exp2f(s[0][1] - m_new);
             const float p10 = exp2f(s[1][0] - m_new), p11 = exp2f(s[1][1] - m_new);
             psum = (p00 + p01) + (p10 + p11);
-            pa[0] = pack_bf16x2(p00, p01);   // A frag: row g, k = 2t,2t+1
-            pa[1] = 0u;                      // rows 8..15 unused
-            pa[2] = pack_bf16x2(p10, p11);   // row g, k = 8+2t,..
+            if (!I8) {
+                pa[0] = pack_bf16x2(p00, p01);   // A frag: row g, k = 2t,2t+1
+                pa[2] = pack_bf16x2(p10, p11);   // row g, k = 8+2t,..
+            } else {                             // probability * V scale of the token (* 2^8, undone at the end)
+                pa[0] = pack_f16x2(p00 * vsc[0].x * AT8_PV_UP, p01 * vsc[0].y * AT8_PV_UP);
+                pa[2] = pack_f16x2(p10 * vsc[1].x * AT8_PV_UP, p11 * vsc[1].y * AT8_PV_UP);
+                // sum of the ROUNDED operands (this lane's 4 tokens; the 4 lanes of a row are added up once, at the end)
+                const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&pa[0]));
+                const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&pa[2]));
+                c_run = c_run * corr + ((f0.x + f0.y) + (f1.x + f1.y));
+            }
+            pa[1] = 0u;                          // rows 8..15 unused
             pa[3] = 0u;
         }
         psum += __shfl_xor_sync(0xffffffffu, psum, 1);
@@ -290,16 +442,32 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
             for (int j = 0; j < 16; ++j) { o[j][0] *= corr; o[j][1] *= corr; }
         }
         // ---- O += P V : V^T fragments via ldmatrix.trans
-        {
+        if (!I8) {
             const int r = (lane & 7) + (((lane >> 3) & 1) << 3);   // token row
             const int gsel = lane >> 4;                            // d-granule parity
 #pragma unroll
             for (int jj = 0; jj < 8; ++jj) {
                 const int c = 2 * jj + gsel;
                 uint32_t b0, b1, b2, b3;
-                ldmatrix_x4_trans(b0, b1, b2, b3, vs + r * AT_ROW + ((c ^ (r & 7)) << 4));
+                ldmatrix_x4_trans(b0, b1, b2, b3, vs + r * ROW + ((c ^ (r & 7)) << 4));
                 mma_bf16_16816(o[2 * jj], pa[0], pa[1], pa[2], pa[3], b0, b1);
                 mma_bf16_16816(o[2 * jj + 1], pa[0], pa[1], pa[2], pa[3], b2, b3);
+            }
+        } else {
+            // transposed b16 units: a register holds V[tok 2t][d0], V[2t][d0+1], V[2t+1][d0], V[2t+1][d0+1] with d0 = 16c + 2g;
+            // bytes (0,2) are the B fragment of column d0, bytes (1,3) of column d0 + 1: accumulator o[2c + par] element e
+            // is d = 16c + 4t + 2e + par
+            const int r = (lane & 7) + (((lane >> 3) & 1) << 3);
+            const int gsel = lane >> 4;
+#pragma unroll
+            for (int i2 = 0; i2 < 4; ++i2) {
+                const int c = 2 * i2 + gsel;
+                uint32_t r0, r1, r2, r3;
+                ldmatrix_x4_trans(r0, r1, r2, r3, vs + r * ROW + ((c ^ (r & 7)) << 4));
+                mma_f16_16816(o[4 * i2 + 0], pa[0], pa[1], pa[2], pa[3], u8pair_to_f16x2(r0, 0x4240u), u8pair_to_f16x2(r1, 0x4240u));
+                mma_f16_16816(o[4 * i2 + 1], pa[0], pa[1], pa[2], pa[3], u8pair_to_f16x2(r0, 0x4341u), u8pair_to_f16x2(r1, 0x4341u));
+                mma_f16_16816(o[4 * i2 + 2], pa[0], pa[1], pa[2], pa[3], u8pair_to_f16x2(r2, 0x4240u), u8pair_to_f16x2(r3, 0x4240u));
+                mma_f16_16816(o[4 * i2 + 3], pa[0], pa[1], pa[2], pa[3], u8pair_to_f16x2(r2, 0x4341u), u8pair_to_f16x2(r3, 0x4341u));
             }
         }
         __syncwarp();
@@ -312,9 +480,22 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
     float* mo = reinterpret_cast<float*>(smem);                       // AT_WARPS * 8 * 128 floats = 16 KB
     float* mml = mo + AT_WARPS * 8 * AT_D;                            // AT_WARPS * 8 * 2
     if (g < p.G) {
+        if (!I8) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            *reinterpret_cast<float2*>(mo + ((warp * 8 + g) * AT_D) + j * 8 + 2 * t) = make_float2(o[j][0], o[j][1]);
+            for (int j = 0; j < 16; ++j) {
+                *reinterpret_cast<float2*>(mo + ((warp * 8 + g) * AT_D) + j * 8 + 2 * t) = make_float2(o[j][0], o[j][1]);
+            }
+        } else {
+            float cs = c_run;
+            cs += __shfl_xor_sync(0xfu << (lane & 28), cs, 1);
+            cs += __shfl_xor_sync(0xfu << (lane & 28), cs, 2);
+            const float ob = AT8_BIAS * cs;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                *reinterpret_cast<float4*>(mo + ((warp * 8 + g) * AT_D) + c * 16 + 4 * t) =
+                    make_float4((o[2 * c][0] - ob) * AT8_PV_DOWN, (o[2 * c + 1][0] - ob) * AT8_PV_DOWN,
+                                (o[2 * c][1] - ob) * AT8_PV_DOWN, (o[2 * c + 1][1] - ob) * AT8_PV_DOWN);
+            }
         }
         if (t == 0) {
             mml[(warp * 8 + g) * 2 + 0] = m_run;
@@ -457,6 +638,7 @@ struct RopeParams {
     const __nv_bfloat16* sin_tab;
     int max_pos;
     __nv_bfloat16* q_out;       // [B][H][D]
+    float* kv_scales;           // int8 pool: scale region (null = bf16 pool); D == 128
 };
 
 __global__ void rope_kv_append_kernel(const RopeParams p) {
@@ -467,29 +649,79 @@ __global__ void rope_kv_append_kernel(const RopeParams p) {
     const __nv_bfloat16* src = p.qkv + (size_t)b * (p.H + 2 * p.Hkv) * p.D + (size_t)head * p.D;
     const float x1 = __bfloat162float(src[i]), x2 = __bfloat162float(src[i + half]);
     __nv_bfloat16* dst;
+    size_t blk = 0;      // (page, layer, K|V, head) block index of a K/V head
+    int slot = 0, kv = -1;
     if (head < p.H) {
         dst = p.q_out + ((size_t)b * p.H + head) * p.D;
     } else {
-        const int kv = (head < p.H + p.Hkv) ? 0 : 1;
+        kv = (head < p.H + p.Hkv) ? 0 : 1;
         const int kh = head - p.H - kv * p.Hkv;
         const int page = p.block_table[(size_t)b * p.max_blocks + pos / p.page_size];
-        const int slot = pos % p.page_size;
-        dst = p.pool + ((((size_t)page * p.layers + p.layer) * 2 + kv) * p.Hkv + kh) * (size_t)p.page_size * p.D + (size_t)slot * p.D;
-        if (kv == 1) {   // V: plain copy
-            dst[i] = src[i];
-            dst[i + half] = src[i + half];
-            pdl_launch_dependents();
-            return;
+        slot = pos % p.page_size;
+        blk = (((size_t)page * p.layers + p.layer) * 2 + kv) * p.Hkv + kh;
+        dst = p.pool + blk * (size_t)p.page_size * p.D + (size_t)slot * p.D;
+    }
+    float o1 = x1, o2 = x2;   // V: plain copy
+    if (kv != 1) {
+        const int pc = min(pos, p.max_pos - 1);
+        const float c = __bfloat162float(p.cos_tab[(size_t)pc * half + i]);
+        const float s = __bfloat162float(p.sin_tab[(size_t)pc * half + i]);
+        o1 = bf16_round(bf16_round(x1 * c) - bf16_round(x2 * s));
+        o2 = bf16_round(bf16_round(x1 * s) + bf16_round(x2 * c));
+    }
+    if (kv >= 0 && p.kv_scales) {   // int8 pool: per-(token, head) absmax over the 2 warps of this block (D == 128)
+        __shared__ float s_amax[2];
+        float am = fmaxf(fabsf(o1), fabsf(o2));
+#pragma unroll
+        for (int o = 16; o; o >>= 1) am = fmaxf(am, __shfl_xor_sync(0xffffffffu, am, o));
+        if ((i & 31) == 0) s_amax[i >> 5] = am;
+        __syncthreads();
+        float amax = fmaxf(s_amax[0], s_amax[1]);
+        const float inv = kv8_inv(amax);
+        uint8_t* d8 = reinterpret_cast<uint8_t*>(p.pool) + blk * (size_t)p.page_size * p.D + (size_t)slot * p.D;
+        d8[i] = kv8_store(o1, inv);
+        d8[i + half] = kv8_store(o2, inv);
+        if (i == 0) p.kv_scales[blk * p.page_size + slot] = kv8_scale(amax);
+    } else {
+        dst[i] = __float2bfloat16_rn(o1);
+        dst[i + half] = __float2bfloat16_rn(o2);
+    }
+    pdl_launch_dependents();
+}
+
+// int8 pool <-> bf16 rows: one CTA per token, one warp per (K|V, head), 4 values per lane (D == 128)
+template <bool SCATTER>
+__global__ void kv_scatter_gather_i8_kernel(uint8_t* pool, float* scales, __nv_bfloat16* k, __nv_bfloat16* v, const int32_t* pages,
+                                            const int32_t* slots, int layers, int layer, int Hkv, int page_size, int max_pages) {
+    const int tkn = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int page = pages[tkn], slot = slots[tkn];
+    if (page < 0 || page >= max_pages || slot < 0 || slot >= page_size) return;
+    for (int idx = warp; idx < 2 * Hkv; idx += nw) {
+        const int kv = idx / Hkv, hh = idx % Hkv;
+        const size_t blk = (((size_t)page * layers + layer) * 2 + kv) * Hkv + hh;
+        __nv_bfloat16* row = (kv ? v : k) + ((size_t)tkn * Hkv + hh) * AT_D + 4 * lane;
+        uint8_t* q = pool + blk * (size_t)page_size * AT_D + (size_t)slot * AT_D + 4 * lane;
+        if (SCATTER) {
+            const uint2 w = *reinterpret_cast<const uint2*>(row);
+            const float x[4] = {bf16lo(w.x), bf16hi(w.x), bf16lo(w.y), bf16hi(w.y)};
+            float am = fmaxf(fmaxf(fabsf(x[0]), fabsf(x[1])), fmaxf(fabsf(x[2]), fabsf(x[3])));
+#pragma unroll
+            for (int o = 16; o; o >>= 1) am = fmaxf(am, __shfl_xor_sync(0xffffffffu, am, o));
+            const float inv = kv8_inv(am);
+            uchar4 c;
+            c.x = kv8_store(x[0], inv); c.y = kv8_store(x[1], inv);
+            c.z = kv8_store(x[2], inv); c.w = kv8_store(x[3], inv);
+            *reinterpret_cast<uchar4*>(q) = c;
+            if (lane == 0) scales[blk * page_size + slot] = kv8_scale(am);
+        } else {   // dequantise like the reference's get(): bf16(float(code) * scale)  (kv_cache.py:220-228)
+            const uchar4 c = *reinterpret_cast<const uchar4*>(q);
+            const float sc = scales[blk * page_size + slot];
+            uint2 w;
+            w.x = pack_bf16x2((float)((int)c.x - 128) * sc, (float)((int)c.y - 128) * sc);
+            w.y = pack_bf16x2((float)((int)c.z - 128) * sc, (float)((int)c.w - 128) * sc);
+            *reinterpret_cast<uint2*>(row) = w;
         }
     }
-    const int pc = min(pos, p.max_pos - 1);
-    const float c = __bfloat162float(p.cos_tab[(size_t)pc * half + i]);
-    const float s = __bfloat162float(p.sin_tab[(size_t)pc * half + i]);
-    const float o1 = bf16_round(x1 * c) - bf16_round(x2 * s);
-    const float o2 = bf16_round(x1 * s) + bf16_round(x2 * c);
-    dst[i] = __float2bfloat16_rn(o1);
-    dst[i + half] = __float2bfloat16_rn(o2);
-    pdl_launch_dependents();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -510,7 +742,7 @@ __global__ void kv_scatter_gather_kernel(T* pool, T* k, T* v, const int32_t* pag
     }
 }
 
-static int elt_size(int dtype) { return dtype == WF_F32 ? 4 : 2; }
+static int elt_size(int dtype) { return dtype == WF_F32 ? 4 : dtype == WF_I8 ? 1 : 2; }
 
 int launch_rope_kv_append(const RopeParams& p, cudaStream_t s, bool pdl) {
     cudaLaunchConfig_t cfg = {};
@@ -529,14 +761,17 @@ int launch_rope_kv_append(const RopeParams& p, cudaStream_t s, bool pdl) {
 int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, size_t workspace_bytes, cudaStream_t s, bool pdl) {
     static bool attr = false;
     if (!attr) {
-        if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM), "attn smem")) return WF_ERR_CUDA;
-        if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM), "attn smem")) return WF_ERR_CUDA;
+        if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM), "attn smem")) return WF_ERR_CUDA;
+        if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM), "attn smem")) return WF_ERR_CUDA;
+        if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT8_SMEM), "attn smem")) return WF_ERR_CUDA;
+        if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT8_SMEM), "attn smem")) return WF_ERR_CUDA;
         attr = true;
     }
     const int max_blocks16 = (max_seq_hint + AT_BLK - 1) / AT_BLK;
     // chunk size: aim for >= 4 CTAs per SM-slot (2 per SM) over the whole grid, but never below 4 blocks (64 tokens)
     const long long pairs = (long long)p.B * p.Hkv;
-    const long long want = 8LL * 2 * sm_count();
+    static const int want_mult = getenv("WF_ATTN_WANT") ? atoi(getenv("WF_ATTN_WANT")) : 4;
+    const long long want = (long long)want_mult * 2 * sm_count();
     int chunks = (int)((want + pairs - 1) / pairs);
     if (chunks < 1) chunks = 1;
     int chunk_blocks = (max_blocks16 + chunks - 1) / chunks;
@@ -560,12 +795,16 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(nchunks < 1 ? 1 : nchunks, p.Hkv, p.B);
         cfg.blockDim = dim3(AT_WARPS * 32);
-        cfg.dynamicSmemBytes = AT_SMEM;
+        const bool i8 = p.kv_scales != nullptr;
+        cfg.dynamicSmemBytes = i8 ? AT8_SMEM : AT_SMEM;
         cfg.stream = s;
         cfg.attrs = at;
         cfg.numAttrs = pdl ? 1 : 0;
         const bool fused = p.qkv_acc != nullptr;
-        if (launch_check(fused ? cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel<true>, p) : cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel<false>, p), "paged_decode_attn")) return WF_ERR_CUDA;
+        cudaError_t le;
+        if (i8) le = fused ? cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel<true, true>, p) : cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel<false, true>, p);
+        else le = fused ? cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel<true, false>, p) : cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel<false, false>, p);
+        if (launch_check(le, "paged_decode_attn")) return WF_ERR_CUDA;
         if (fused) return WF_OK;
     }
     if (!p.direct) {
@@ -587,8 +826,9 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
 
 int rope_append(const void* qkv, int B, int H, int Hkv, int D, void* pool, int layers, int layer, int page_size,
                 const int32_t* positions, const int32_t* block_table, int max_blocks, const void* cos_tab, const void* sin_tab,
-                int max_pos, void* q_out, cudaStream_t s, bool pdl) {
+                int max_pos, void* q_out, cudaStream_t s, bool pdl, float* kv_scales) {
     RopeParams p;
+    p.kv_scales = kv_scales;
     p.qkv = (const __nv_bfloat16*)qkv; p.B = B; p.H = H; p.Hkv = Hkv; p.D = D;
     p.pool = (__nv_bfloat16*)pool; p.layers = layers; p.layer = layer; p.page_size = page_size; p.max_blocks = max_blocks;
     p.positions = positions; p.block_table = block_table;
@@ -599,8 +839,9 @@ int rope_append(const void* qkv, int B, int H, int Hkv, int D, void* pool, int l
 
 int attn_decode(const void* q, const void* pool, int layers, int layer, int Hkv, int page_size, const int32_t* block_table,
                 int max_blocks, const int32_t* seq_lens, int B, int H, float scale, void* out, int out_dtype, int max_seq_hint,
-                void* ws, size_t ws_bytes, cudaStream_t s, bool pdl) {
+                void* ws, size_t ws_bytes, cudaStream_t s, bool pdl, float* kv_scales) {
     AttnParams p = {};
+    p.kv_scales = kv_scales;
     p.q = (const __nv_bfloat16*)q; p.pool = (const __nv_bfloat16*)pool;
     p.block_table = block_table; p.seq_lens = seq_lens;
     p.B = B; p.H = H; p.Hkv = Hkv; p.G = H / Hkv;
@@ -627,6 +868,7 @@ int attn_decode_fused(const FusedAttnArgs& a, cudaStream_t s, bool pdl) {
     p.n_out = a.n_out < 1 ? 1 : a.n_out; p.out_ld = a.out_ld > 0 ? a.out_ld : a.H * AT_D; p.out_col0 = a.out_col0;
     for (int r = 0; r < TP_MAX; ++r) p.out_peer[r] = a.out_peer[r];
     p.signal_flag = a.n_out > 1 ? a.signal_flag : -1; p.tp = a.tp; p.trace = a.trace;
+    p.kv_scales = a.kv_scales;
     return launch_paged_decode_attn(p, a.max_seq_hint, a.ws, a.ws_bytes, s, pdl);
 }
 
@@ -635,7 +877,16 @@ int attn_decode_fused(const FusedAttnArgs& a, cudaStream_t s, bool pdl) {
 using namespace wf;
 
 extern "C" size_t wf_kv_pool_bytes(int max_pages, int layers, int kv_heads, int page_size, int head_dim, int dtype) {
-    return (size_t)max_pages * layers * 2 * kv_heads * page_size * head_dim * elt_size(dtype);
+    const size_t elems = (size_t)max_pages * layers * 2 * kv_heads * page_size * head_dim;
+    if (dtype == WF_I8) return elems + elems / head_dim * sizeof(float);   // int8 region + one fp32 scale per (token, head)
+    return elems * elt_size(dtype);
+}
+
+// scale region of an int8 pool
+static float* kv_scales_of(const wf_kv_layout* kv) {
+    if (kv->dtype != WF_I8) return nullptr;
+    return reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(kv->pool) +
+                                    (size_t)kv->max_pages * kv->layers * 2 * kv->kv_heads * kv->page_size * kv->head_dim);
 }
 
 static int check_kv(const wf_kv_layout* kv, const char* who) {
@@ -656,7 +907,10 @@ static int scatter_gather(const wf_kv_layout* kv, void* k, void* v, const int32_
         kv_scatter_gather_kernel<float, SC><<<T, 256, 0, s>>>((float*)kv->pool, (float*)k, (float*)v, pages, slots, kv->layers, layer, kv->kv_heads, kv->page_size, kv->head_dim, kv->max_pages);
     else if (kv->dtype == WF_BF16)
         kv_scatter_gather_kernel<__nv_bfloat16, SC><<<T, 256, 0, s>>>((__nv_bfloat16*)kv->pool, (__nv_bfloat16*)k, (__nv_bfloat16*)v, pages, slots, kv->layers, layer, kv->kv_heads, kv->page_size, kv->head_dim, kv->max_pages);
-    else { set_error("kv scatter/gather: dtype must be f32 or bf16"); return WF_ERR_INVALID; }
+    else if (kv->dtype == WF_I8) {   // k / v rows are bf16; quantised per (token, head) on the way in, dequantised on the way out
+        if (kv->head_dim != AT_D) { set_error("kv scatter/gather: int8 pools need head_dim 128"); return WF_ERR_UNSUPPORTED; }
+        kv_scatter_gather_i8_kernel<SC><<<T, 128, 0, s>>>((uint8_t*)kv->pool, kv_scales_of(kv), (__nv_bfloat16*)k, (__nv_bfloat16*)v, pages, slots, kv->layers, layer, kv->kv_heads, kv->page_size, kv->max_pages);
+    } else { set_error("kv scatter/gather: dtype must be f32, bf16 or int8"); return WF_ERR_INVALID; }
     return launch_check(cudaGetLastError(), "kv scatter/gather");
 }
 
@@ -673,11 +927,12 @@ extern "C" int wf_rope_kv_append(const void* qkv, int B, int H, const wf_kv_layo
     int rc = check_kv(kv, "wf_rope_kv_append");
     if (rc) return rc;
     if (!qkv || !positions || !block_table || !cos_tab || !sin_tab || !q_out) { set_error("wf_rope_kv_append: null pointer"); return WF_ERR_INVALID; }
-    if (kv->dtype != WF_BF16) { set_error("wf_rope_kv_append: pool must be bf16"); return WF_ERR_UNSUPPORTED; }
+    if (kv->dtype != WF_BF16 && kv->dtype != WF_I8) { set_error("wf_rope_kv_append: pool must be bf16 or int8"); return WF_ERR_UNSUPPORTED; }
     if (kv->head_dim % 2 || kv->head_dim > 2048) { set_error("wf_rope_kv_append: bad head_dim"); return WF_ERR_UNSUPPORTED; }
+    if (kv->dtype == WF_I8 && kv->head_dim != AT_D) { set_error("wf_rope_kv_append: int8 pools need head_dim 128"); return WF_ERR_UNSUPPORTED; }
     if (B <= 0) return WF_OK;
     return rope_append(qkv, B, H, kv->kv_heads, kv->head_dim, kv->pool, kv->layers, layer, kv->page_size, positions, block_table,
-                       max_blocks, cos_tab, sin_tab, max_pos, q_out, (cudaStream_t)stream, false);
+                       max_blocks, cos_tab, sin_tab, max_pos, q_out, (cudaStream_t)stream, false, kv_scales_of(kv));
 }
 
 extern "C" size_t wf_attn_workspace_bytes(int B, int H, int head_dim, int max_seq) {
@@ -691,7 +946,7 @@ extern "C" int wf_paged_decode_attn(const void* q, const wf_kv_layout* kv, int l
     int rc = check_kv(kv, "wf_paged_decode_attn");
     if (rc) return rc;
     if (!q || !block_table || !seq_lens || !out) { set_error("wf_paged_decode_attn: null pointer"); return WF_ERR_INVALID; }
-    if (kv->dtype != WF_BF16) { set_error("wf_paged_decode_attn: pool must be bf16"); return WF_ERR_UNSUPPORTED; }
+    if (kv->dtype != WF_BF16 && kv->dtype != WF_I8) { set_error("wf_paged_decode_attn: pool must be bf16 or int8"); return WF_ERR_UNSUPPORTED; }
     if (kv->head_dim != AT_D) { set_error("wf_paged_decode_attn: head_dim must be 128 (got %d)", kv->head_dim); return WF_ERR_UNSUPPORTED; }
     if (kv->page_size % AT_BLK) { set_error("wf_paged_decode_attn: page_size must be a multiple of 16 (got %d)", kv->page_size); return WF_ERR_UNSUPPORTED; }
     if (H % kv->kv_heads || H / kv->kv_heads > 8) { set_error("wf_paged_decode_attn: H/Hkv must be an integer <= 8"); return WF_ERR_UNSUPPORTED; }
@@ -699,12 +954,14 @@ extern "C" int wf_paged_decode_attn(const void* q, const wf_kv_layout* kv, int l
     if (out_dtype != WF_BF16 && out_dtype != WF_F32) { set_error("wf_paged_decode_attn: out dtype"); return WF_ERR_INVALID; }
     if (B <= 0) return WF_OK;
     return attn_decode(q, kv->pool, kv->layers, layer, kv->kv_heads, kv->page_size, block_table, max_blocks, seq_lens, B, H, scale, out,
-                       out_dtype, max_blocks * kv->page_size, workspace, workspace_bytes, (cudaStream_t)stream, false);
+                       out_dtype, max_blocks * kv->page_size, workspace, workspace_bytes, (cudaStream_t)stream, false, kv_scales_of(kv));
 }
 
 namespace wf {
 void attn_init_attrs() {
-    cudaFuncSetAttribute(paged_decode_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
-    cudaFuncSetAttribute(paged_decode_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    cudaFuncSetAttribute(paged_decode_attn_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    cudaFuncSetAttribute(paged_decode_attn_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    cudaFuncSetAttribute(paged_decode_attn_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT8_SMEM);
+    cudaFuncSetAttribute(paged_decode_attn_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT8_SMEM);
 }
 }

@@ -50,7 +50,8 @@ struct wf_engine {
     int v_lo = 0, v_n = 0;                   // this rank's vocab slice of the tied LM head
     unsigned long long* trace = nullptr;     // WF_TRACE=1: 16 globaltimer stamps per linear_small launch
     // kv
-    __nv_bfloat16* pool = nullptr;
+    __nv_bfloat16* pool = nullptr;   // bf16 pool, or the int8 region of an int8 pool (kv_scales != null)
+    float* kv_scales = nullptr;      // int8 KV: scale region [page][layer][K|V][head][slot]
     int max_blocks = 0;
     int32_t* d_block_table = nullptr;
     std::vector<int32_t> h_block_table;
@@ -162,9 +163,9 @@ int run_step(wf_engine* e, int B, int feed_back) {
             if ((rc = linear(e, L.qkv, e->qkv_rows, e->hidden, B, L.scales + 0, 3, seg, 0, e->qkv, e->qkv_rows, nullptr))) return rc;
         }
         if ((rc = rope_append(e->qkv, B, e->H, e->Hkv, e->D, e->pool, c.layers, l, c.page_size, e->d_pos, e->d_block_table, e->max_blocks,
-                              e->cos_tab, e->sin_tab, c.max_seq, e->qrot, s, e->pdl))) return rc;
+                              e->cos_tab, e->sin_tab, c.max_seq, e->qrot, s, e->pdl, e->kv_scales))) return rc;
             if ((rc = attn_decode(e->qrot, e->pool, c.layers, l, e->Hkv, c.page_size, e->d_block_table, e->max_blocks, e->d_len, B, e->H,
-                              attn_scale, e->attn, WF_BF16, e->attn_seq_hint, e->ws_attn, e->ws_attn_bytes, s, e->pdl))) return rc;
+                              attn_scale, e->attn, WF_BF16, e->attn_seq_hint, e->ws_attn, e->ws_attn_bytes, s, e->pdl, e->kv_scales))) return rc;
             if ((rc = launch_rmsnorm_quant(e->attn, L.g_attn, c.eps, B, e->attn_dim, nullptr, e->q8, e->a_scale, e->rowsum, s, e->pdl))) return rc;
             {
             const int seg[1] = {e->hidden};
@@ -270,7 +271,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
         // ---- B: dequant + RoPE + KV append + paged attention + chunk merge (+ all-gather of the heads)
         {
             FusedAttnArgs a = {};
-            a.pool = e->pool; a.layers = c.layers; a.layer = l; a.Hkv = e->Hkv; a.page_size = c.page_size;
+            a.pool = e->pool; a.kv_scales = e->kv_scales; a.layers = c.layers; a.layer = l; a.Hkv = e->Hkv; a.page_size = c.page_size;
             a.block_table = e->d_block_table; a.max_blocks = e->max_blocks; a.seq_lens = e->d_len; a.positions = e->d_pos;
             a.B = B; a.H = e->H; a.scale = attn_scale; a.out = e->attn;
             a.n_out = T; a.out_ld = e->attn_full; a.out_col0 = e->tp.rank * e->attn_dim; a.signal_flag = fB; a.tp = e->tp;
@@ -496,8 +497,19 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     }
     // KV pool
     const size_t pool_elems = (size_t)c.max_pages * c.layers * 2 * e->Hkv * c.page_size * c.head_dim;
-    if ((rc = dalloc(e, &e->pool, pool_elems))) return fail(rc);
-    if (cuda_check(cudaMemset(e->pool, 0, pool_elems * 2), "pool memset")) return fail(WF_ERR_CUDA);
+    if (c.kv_dtype == WF_I8) {   // int8 codes + one fp32 scale per (token, kv head), one allocation (the wf_kv_layout convention)
+        if (c.head_dim != 128) { set_error("int8 KV needs head_dim 128"); return fail(WF_ERR_UNSUPPORTED); }
+        unsigned char* raw = nullptr;
+        const size_t bytes = pool_elems + pool_elems / c.head_dim * sizeof(float);
+        if ((rc = dalloc(e, &raw, bytes))) return fail(rc);
+        if (cuda_check(cudaMemset(raw, 0, bytes), "pool memset")) return fail(WF_ERR_CUDA);
+        e->pool = reinterpret_cast<__nv_bfloat16*>(raw);
+        e->kv_scales = reinterpret_cast<float*>(raw + pool_elems);
+    } else {
+        if (c.kv_dtype != 0 && c.kv_dtype != WF_BF16) { set_error("kv_dtype must be WF_BF16 or WF_I8"); return fail(WF_ERR_INVALID); }
+        if ((rc = dalloc(e, &e->pool, pool_elems))) return fail(rc);
+        if (cuda_check(cudaMemset(e->pool, 0, pool_elems * 2), "pool memset")) return fail(WF_ERR_CUDA);
+    }
     e->max_blocks = c.max_seq / c.page_size;
     if ((rc = dalloc(e, &e->d_block_table, (size_t)B * e->max_blocks))) return fail(rc);
     if ((rc = dalloc(e, &e->d_pos, B)) || (rc = dalloc(e, &e->d_len, B)) || (rc = dalloc(e, &e->d_tok, B)) || (rc = dalloc(e, &e->d_next, B))) return fail(rc);
@@ -742,7 +754,13 @@ extern "C" int wf_engine_set_context(wf_engine* e, int slot, int len, int fill_r
         const size_t page_elems = (size_t)e->cfg.layers * 2 * e->Hkv * ps * e->D;
         for (int blk = 0; blk * ps < len; ++blk) {
             const int32_t page = e->h_block_table[(size_t)slot * e->max_blocks + blk];
-            int rc = launch_fill_bf16(e->pool + (size_t)page * page_elems, page_elems, 0xC0FFEEull + (uint64_t)page, 0.0f, 1.0f, e->stream);
+            int rc;
+            if (e->kv_scales) {   // random int8 codes (the bytes of random bf16 values) and scales of N(1, 0.1)/42 so that values are O(1)
+                rc = launch_fill_bf16(reinterpret_cast<unsigned char*>(e->pool) + (size_t)page * page_elems, page_elems / 2, 0xC0FFEEull + (uint64_t)page, 0.0f, 1.0f, e->stream);
+                if (!rc) rc = launch_fill_f32(e->kv_scales + (size_t)page * (page_elems / e->D), page_elems / e->D, 1.0f / 42.0f, e->stream);
+            } else {
+                rc = launch_fill_bf16(e->pool + (size_t)page * page_elems, page_elems, 0xC0FFEEull + (uint64_t)page, 0.0f, 1.0f, e->stream);
+            }
             if (rc) return rc;
         }
         return cuda_check(cudaStreamSynchronize(e->stream), "fill pool");
@@ -845,7 +863,7 @@ extern "C" int wf_engine_time_kernel(wf_engine* e, const char* which, int B, int
         LayerW& L = e->layers[l];
         if (w == "attn")
             return attn_decode(e->qrot, e->pool, c.layers, l, e->Hkv, c.page_size, e->d_block_table, e->max_blocks, e->d_len, B, e->H,
-                               1.0f / sqrtf((float)e->D), e->attn, WF_BF16, e->attn_seq_hint, e->ws_attn, e->ws_attn_bytes, e->stream, false);
+                               1.0f / sqrtf((float)e->D), e->attn, WF_BF16, e->attn_seq_hint, e->ws_attn, e->ws_attn_bytes, e->stream, false, e->kv_scales);
         if (w == "qkv") { const int seg[3] = {e->H * e->D, (e->H + e->Hkv) * e->D, e->qkv_rows}; return linear(e, L.qkv, e->qkv_rows, e->hidden, B, L.scales, 3, seg, 0, e->qkv, e->qkv_rows, nullptr); }
         if (w == "o") { const int seg[1] = {e->hidden}; return linear(e, L.o, e->hidden, e->attn_dim, B, L.scales + 3, 1, seg, 0, e->normed, e->hidden, nullptr); }
         if (w == "gateup") { const int seg[2] = {e->ffn, 2 * e->ffn}; return linear(e, L.gu, 2 * e->ffn, e->hidden, B, L.scales + 4, 2, seg, WF_EPI_RELU2_MUL, e->gu, e->ffn, nullptr); }

@@ -400,6 +400,7 @@ struct FusedAttnArgs {
     int max_seq_hint;
     void* ws;
     size_t ws_bytes;
+    float* kv_scales;          // int8 pool: scale region (null = bf16 pool)
 };
 int attn_decode_fused(const FusedAttnArgs& a, cudaStream_t s, bool pdl);
 

@@ -277,6 +277,13 @@ int launch_fill_ternary(void* out, size_t bytes, uint64_t seed, cudaStream_t s) 
     fill_ternary_kernel<<<sm_count() * 8, 256, 0, s>>>((uint32_t*)out, bytes / 4, seed);
     return launch_check(cudaGetLastError(), "fill_ternary");
 }
+__global__ void fill_f32_kernel(float* out, size_t n, float v) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) out[i] = v;
+}
+int launch_fill_f32(float* out, size_t n, float value, cudaStream_t s) {
+    fill_f32_kernel<<<sm_count() * 4, 256, 0, s>>>(out, n, value);
+    return launch_check(cudaGetLastError(), "fill_f32");
+}
 int launch_fill_bf16(void* out, size_t n, uint64_t seed, float mean, float std, cudaStream_t s) {
     fill_bf16_kernel<<<sm_count() * 8, 256, 0, s>>>((__nv_bfloat16*)out, n, seed, mean, std);
     return launch_check(cudaGetLastError(), "fill_bf16");

@@ -13,7 +13,7 @@ _PKG_ROOT = Path(__file__).resolve().parent.parent
 LIB_PATH = Path(os.environ.get("WF_BITNET_LIB", _PKG_ROOT / "libwf_bitnet.so"))
 
 WF_OK, WF_ERR_INVALID, WF_ERR_UNSUPPORTED, WF_ERR_CUDA = 0, -1, -2, -3
-WF_F32, WF_BF16, WF_F16 = 0, 1, 2
+WF_F32, WF_BF16, WF_F16, WF_I8 = 0, 1, 2, 3
 WF_W_I2S, WF_W_TILE = 0, 1
 WF_OUT_I32_PLUS1, WF_OUT_I32, WF_OUT_COMPAT_F32, WF_OUT_LINEAR = 0, 1, 2, 3
 WF_EPI_RESIDUAL, WF_EPI_RELU2_MUL = 1, 2
@@ -48,7 +48,7 @@ class ModelConfig(C.Structure):
         ("hidden", C.c_int), ("layers", C.c_int), ("heads", C.c_int), ("kv_heads", C.c_int), ("head_dim", C.c_int),
         ("ffn", C.c_int), ("vocab", C.c_int), ("rope_theta", C.c_float), ("eps", C.c_float),
         ("max_seq", C.c_int), ("page_size", C.c_int), ("max_batch", C.c_int), ("max_pages", C.c_int),
-        ("tp_rank", C.c_int), ("tp_size", C.c_int),
+        ("tp_rank", C.c_int), ("tp_size", C.c_int), ("kv_dtype", C.c_int),
     ]
 
 

@@ -31,6 +31,7 @@ class EngineConfig:
     page_size: int = 16
     max_batch: int = 1
     max_pages: int = 0   # 0 -> max_batch * max_seq / page_size
+    kv_dtype: str = "bf16"   # "bf16" | "int8" (the reference's KVCacheDtype.INT8 at (token, head) granularity)
 
     @staticmethod
     def bitnet_2b(**kw) -> "EngineConfig":
@@ -58,7 +59,8 @@ class Engine:
         self.tp_rank, self.tp_size = tp_rank, tp_size
         max_pages = cfg.max_pages or cfg.max_batch * (cfg.max_seq // cfg.page_size)
         c = _CConfig(cfg.hidden, cfg.layers, cfg.heads, cfg.kv_heads, cfg.head_dim, cfg.ffn, cfg.vocab, cfg.rope_theta, cfg.eps,
-                     cfg.max_seq, cfg.page_size, cfg.max_batch, max_pages, tp_rank, tp_size)
+                     cfg.max_seq, cfg.page_size, cfg.max_batch, max_pages, tp_rank, tp_size,
+                     {"bf16": _lib.WF_BF16, "int8": _lib.WF_I8}[cfg.kv_dtype])
         h = C.c_void_p()
         check(lib().wf_engine_create(C.byref(c), C.byref(h)))
         self._h = h

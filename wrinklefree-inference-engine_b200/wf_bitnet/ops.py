@@ -12,7 +12,7 @@ from typing import Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import (WF_BF16, WF_EPI_RELU2_MUL, WF_EPI_RESIDUAL, WF_F16, WF_F32, WF_OUT_COMPAT_F32, WF_OUT_I32,
+from ._lib import (WF_BF16, WF_EPI_RELU2_MUL, WF_EPI_RESIDUAL, WF_F16, WF_F32, WF_I8, WF_OUT_COMPAT_F32, WF_OUT_I32,
                    WF_OUT_I32_PLUS1, WF_OUT_LINEAR, WF_W_I2S, WF_W_TILE, KvLayout, LinearArgs, check, lib)
 
 _DT = {torch.float32: WF_F32, torch.bfloat16: WF_BF16, torch.float16: WF_F16}
@@ -241,11 +241,28 @@ class PagedKV:
         _lib.require_gpu()
         self.max_pages, self.layers, self.kv_heads, self.page_size, self.head_dim = max_pages, layers, kv_heads, page_size, head_dim
         self.dtype = dtype
+        if dtype == torch.int8:
+            # codes [page][layer][K|V][head][slot][D], stored offset-binary (uint8 = code + 128), followed by the fp32 scales
+            # [page][layer][K|V][head][slot] in ONE allocation
+            elems = max_pages * layers * 2 * kv_heads * page_size * head_dim
+            nbytes = int(lib().wf_kv_pool_bytes(max_pages, layers, kv_heads, page_size, head_dim, WF_I8))
+            self.raw = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+            self.pool = self.raw[:elems].view(max_pages, layers, 2, kv_heads, page_size, head_dim)
+            self.scales = self.raw[elems:].view(torch.float32).view(max_pages, layers, 2, kv_heads, page_size)
+            self.c = KvLayout(self.raw.data_ptr(), max_pages, layers, kv_heads, page_size, head_dim, WF_I8)
+            return
         self.pool = torch.zeros(max_pages, layers, 2, kv_heads, page_size, head_dim, dtype=dtype, device=device)
         self.c = KvLayout(self.pool.data_ptr(), max_pages, layers, kv_heads, page_size, head_dim, _DT[dtype])
 
     def ref(self):
         return C.byref(self.c)
+
+    def codes(self) -> torch.Tensor:
+        """int8 pools: the signed codes (pool bytes are offset-binary)."""
+        return (self.pool.to(torch.int16) - 128).to(torch.int8)
+
+    def set_codes(self, codes: torch.Tensor) -> None:
+        self.pool.copy_((codes.to(torch.int16) + 128).to(torch.uint8))
 
 
 def kv_scatter(kv: PagedKV, k: torch.Tensor, v: torch.Tensor, pages: torch.Tensor, slots: torch.Tensor, layer: int) -> None:
