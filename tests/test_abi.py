@@ -39,7 +39,7 @@ def test_every_declared_symbol_is_exported_and_bound():
 def test_struct_sizes_match_header_layout():
     # sizes follow the field lists of the header (LP64): catches drift between header and ctypes mirror
     assert C.sizeof(_lib.KvLayout) == 8 + 6 * 4
-    assert C.sizeof(_lib.ModelConfig) == 15 * 4
+    assert C.sizeof(_lib.ModelConfig) == 16 * 4   # + kv_dtype
     assert C.sizeof(_lib.LinearArgs) % 8 == 0 and C.sizeof(_lib.LinearArgs) >= 120
 
 

@@ -227,3 +227,38 @@ def test_int8_pool_is_half_the_bytes():
     b16 = lib().wf_kv_pool_bytes(100, 30, 5, 16, 128, WF_BF16)
     i8 = lib().wf_kv_pool_bytes(100, 30, 5, 16, 128, WF_I8)
     assert i8 == b16 // 2 + b16 // 2 // 128 * 4
+
+
+def test_kvcache_mirror_int8_update_get_attention(golden):
+    """wrinklefree_inference.kv_cache with KVCacheDtype.INT8 (the reference's default dtype, kv_cache.py:56): update / get
+    reproduce the reference's row arithmetic (golden rows from its own KVCache), attention_with_kv_cache equals the oracle
+    attention over what get() returns."""
+    from wrinklefree_inference.kv_cache import KVCache, KVCacheConfig, KVCacheDtype, attention_with_kv_cache, compute_kv_cache_memory
+    g = golden["kv_int8"]
+    x = torch.from_numpy(g["x"])                                     # [96, 128] rows
+    H, D, S, R0 = 4, 128, 8, 32                                    # rows 32..63: magnitudes 0.1 .. 10
+    cfg = KVCacheConfig(max_seq_len=32, num_layers=2, num_heads=H, head_dim=D, dtype=KVCacheDtype.INT8)
+    assert cfg.bytes_per_token_per_layer == 2 * H * D
+    cache = KVCache(cfg)
+    rows = x[R0: R0 + S * H].view(S, H, D)
+    for pos in range(S):
+        cache.update(1, rows[pos].view(1, 1, H, D), rows[pos].flip(0).contiguous().view(1, 1, H, D), pos)
+    k, v = cache.get(1)
+    want = torch.from_numpy(g["deq"])[R0: R0 + S * H].view(S, H, D)
+    assert torch.equal(k.float().cpu(), want)
+    assert torch.equal(v.float().cpu(), want.flip(1))
+    assert cache.k_scales[1].item() == np.float32(g["scales"][R0 + S * H - 1])
+    # attention at the next position over the int8 cache
+    gen = torch.Generator().manual_seed(5)
+    q = torch.randn(1, H, 1, D, generator=gen)
+    nk, nv = torch.randn(1, 1, H, D, generator=gen), torch.randn(1, 1, H, D, generator=gen)
+    out = attention_with_kv_cache(q, cache, 1, nk, nv, S)
+    k2, v2 = cache.get(1)
+    ref = OM.attention_gqa_fp32(q.view(H, D).to(torch.bfloat16), k2.cpu(), v2.cpu())
+    assert out.shape == (1, H, 1, D)
+    assert torch.allclose(out.view(H, D).cpu(), ref, atol=2e-2 * ref.abs().max().item(), rtol=2e-2)
+    m8 = compute_kv_cache_memory({"num_layers": 30, "num_heads": 5, "head_dim": 128}, 4096, KVCacheDtype.INT8)
+    m16 = compute_kv_cache_memory({"num_layers": 30, "num_heads": 5, "head_dim": 128}, 4096, KVCacheDtype.BF16)
+    assert m8["total_mb"] * 2 == m16["total_mb"]
+    cache.clear()
+    assert cache.current_seq_len == 0

@@ -227,3 +227,18 @@ def test_paged_reference_semantics():
     assert torch.equal(ko, k) and torch.equal(vo, v)
     c.free_pages(p)
     assert c.num_free_pages() == 10
+
+
+def test_kv_int8_quantiser_matches_reference_kvcache(golden):
+    """tests/golden/kv_int8.npz: the reference's KVCache(INT8).update / .get fed one (token, head) row per call
+    (kv_cache.py:198-228).  The oracle restatement the GPU tests check against must give the same codes, the same stored
+    fp32 scale and the same dequantised bf16 row."""
+    import torch
+    from oracle import model as OM
+    g = golden["kv_int8"]
+    x = torch.from_numpy(g["x"])
+    codes, sc = OM.kv_int8_quant(x)
+    assert np.array_equal(codes.numpy(), g["codes"])
+    assert np.array_equal(sc[:, 0].numpy(), g["scales"].astype(np.float32))
+    assert np.array_equal(OM.kv_int8_roundtrip(x).float().numpy(), g["deq"])
+    assert g["scales"][0] == np.float32(1.0 / 127.0) and np.all(g["codes"][0] == 0)      # all-zero row: absmax -> 1

@@ -6,9 +6,14 @@ Storage is the paged pool of the CUDA library ([page][layer][K|V][head][slot][D]
 config — the reference declares `page_size=16` but never uses it); a sequence owns pages 0..n in order.
 `attention_with_kv_cache` = append + split-KV flash-decode kernel (wf_paged_decode_attn).
 
-Supported cache dtypes: BF16 (attention + update/get), FP32 (update/get only).  The reference's
-INT8/"FP8" modes re-derive ONE scale per layer from the most recent update and apply it to the whole
-cache (kv_cache.py:198-228) — not reproduced yet; they raise NotImplementedError.
+Supported cache dtypes: BF16 and INT8 (attention + update/get), FP32 (update/get only).
+INT8 uses the reference's arithmetic (kv_cache.py:198-228: scale = 127/absmax, round, clamp +-127, dequantise to bf16)
+with one scale per (token, head) row.  The reference keeps ONE scale per layer, re-derived from the most recent update()
+call and applied by get() to everything already cached - with token-by-token decode that rescales old entries by the
+newest token's absmax; a row-wise scale is what that code does when it is handed one row, without the defect
+(tests/golden/kv_int8.npz pins the row arithmetic to the reference's own KVCache).  `k_scales` / `v_scales` are kept for
+API compatibility and hold the scale of the most recent row.  The "FP8" modes (int8 storage with a per-update scale,
+kv_cache.py:150-196) raise NotImplementedError.
 """
 from __future__ import annotations
 
@@ -74,6 +79,8 @@ class KVCache:
             self.storage_dtype = torch.bfloat16
         elif config.dtype == KVCacheDtype.FP32:
             self.storage_dtype = torch.float32
+        elif config.dtype == KVCacheDtype.INT8:
+            self.storage_dtype = torch.bfloat16     # dtype of the rows handed to / returned by the int8 pool
         else:
             raise NotImplementedError(f"KV cache dtype {config.dtype.value} is not implemented on the GPU path yet")
         ps = config.page_size
@@ -81,10 +88,11 @@ class KVCache:
             raise ValueError("page_size must be a multiple of 16")
         self.num_pages = (config.max_seq_len + ps - 1) // ps
         self.kv = ops.PagedKV(self.num_pages, config.num_layers, config.num_heads, ps, config.head_dim,
-                              dtype=self.storage_dtype, device=device)
+                              dtype=torch.int8 if config.dtype == KVCacheDtype.INT8 else self.storage_dtype, device=device)
         self.block_table = torch.arange(self.num_pages, dtype=torch.int32, device=device).reshape(1, -1)
-        self.k_scales = torch.ones(config.num_layers, dtype=torch.float32)
-        self.v_scales = torch.ones(config.num_layers, dtype=torch.float32)
+        sdev = device if config.dtype == KVCacheDtype.INT8 else "cpu"
+        self.k_scales = torch.ones(config.num_layers, dtype=torch.float32, device=sdev)
+        self.v_scales = torch.ones(config.num_layers, dtype=torch.float32, device=sdev)
 
     def _pages_slots(self, start: int, n: int):
         pos = torch.arange(start, start + n, dtype=torch.int32, device=self.kv.pool.device)
@@ -105,6 +113,10 @@ class KVCache:
         v = value.to(dev, self.storage_dtype).reshape(new_tokens, -1)
         pages, slots = self._pages_slots(seq_pos, new_tokens)
         ops.kv_scatter(self.kv, k, v, pages, slots, layer_idx)
+        if self.config.dtype == KVCacheDtype.INT8:
+            pg, sl, hh = (end_pos - 1) // self.config.page_size, (end_pos - 1) % self.config.page_size, self.config.num_heads - 1
+            self.k_scales[layer_idx] = self.kv.scales[pg, layer_idx, 0, hh, sl]      # device-side copies, no sync
+            self.v_scales[layer_idx] = self.kv.scales[pg, layer_idx, 1, hh, sl]
         self.current_seq_len = max(self.current_seq_len, end_pos)
 
     def get(self, layer_idx: int, end_pos: Optional[int] = None) -> Tuple[torch.Tensor, torch.Tensor]:
@@ -121,13 +133,14 @@ class KVCache:
         return k.view(end_pos, c.num_heads, c.head_dim), v.view(end_pos, c.num_heads, c.head_dim)
 
     def clear(self) -> None:
-        self.kv.pool.zero_()
+        (self.kv.raw if self.config.dtype == KVCacheDtype.INT8 else self.kv.pool).zero_()
         self.k_scales.fill_(1.0)
         self.v_scales.fill_(1.0)
         self.current_seq_len = 0
 
     def memory_usage_mb(self) -> float:
-        return self.kv.pool.numel() * self.kv.pool.element_size() / (1024 * 1024)
+        t = self.kv.raw if self.config.dtype == KVCacheDtype.INT8 else self.kv.pool
+        return t.numel() * t.element_size() / (1024 * 1024)
 
 
 def attention_with_kv_cache(query: torch.Tensor, kv_cache: KVCache, layer_idx: int, new_key: torch.Tensor,
