@@ -436,6 +436,37 @@ def run_gpu(args):
         except Exception as ex:  # noqa: BLE001
             aux = {"error": str(ex)}
 
+    # ---------------- the same step with the int8 KV option (the reference's KVCacheDtype.INT8): NOT the headline (other cache
+    # precision), reported beside it because it halves the attention bytes of this configuration
+    if args.workload == "bs64" and world == 1 and not args.no_aux:
+        try:
+            c8 = EngineConfig(**SHAPE, max_seq=ctx + 64, page_size=page, max_batch=batch, kv_dtype="int8")
+            e8 = Engine(c8)
+            e8.init_synthetic(1234)
+            for slot in range(batch):
+                e8.set_context(slot, ctx, fill_random=True)
+            for _ in range(5):
+                e8.decode_device(batch)
+            e8.sync()
+            ext8 = torch.cuda.ExternalStream(e8.stream)
+            b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            n8 = 30
+            b0.record(ext8)
+            for _ in range(n8):
+                e8.decode_device(batch)
+            b1.record(ext8)
+            b1.synchronize()
+            ms8 = b0.elapsed_time(b1) / n8
+            attn8 = e8.time_kernel("attn", batch, 60)
+            bytes8 = batch * (ctx + 36) * 2 * 5 * (128 + 4)
+            aux["int8_kv"] = {"note": "same workload with kv_dtype=int8 (int8 codes + one fp32 scale per token and kv head); not the headline precision",
+                              "ms_per_step": ms8, "tok_s": batch / ms8 * 1e3, "attn_ms_per_layer": attn8, "attn_algorithmic_bytes": bytes8,
+                              "attn_GBs": bytes8 / (attn8 * 1e-3) / 1e9, "attn_frac_of_hbm_peak": bytes8 / (attn8 * 1e-3) / 1e9 / peak,
+                              "kv_pool_bytes_ratio_vs_bf16": (128 + 4) / 256}
+            e8.close()
+        except Exception as ex:  # noqa: BLE001
+            aux["int8_kv"] = {"error": str(ex)}
+
     # ---------------- kernel-level GEMV bandwidth (the third part of BASELINE's metric): M = 1, > L2 worth of weight copies
     if world == 1 and not args.no_aux:
         try:
