@@ -74,6 +74,13 @@ __device__ __forceinline__ int kv8_code(float x, float inv) { return (int)fminf(
 __device__ __forceinline__ uint8_t kv8_store(float x, float inv) { return (uint8_t)(kv8_code(x, inv) + 128); }   // offset binary
 __device__ __forceinline__ float kv8_scale(float amax) { return __fdiv_rn(amax, 127.0f); }
 
+// ex2.approx: one MUFU instead of exp2f()'s range-scaling sequence; exp2(-inf) = 0, 2 ulp — far inside the 16-bit rounding of P
+__device__ __forceinline__ float fast_exp2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 struct AttnParams {
     const __nv_bfloat16* q;      // [B][H][D]
     const __nv_bfloat16* pool;
@@ -81,6 +88,7 @@ struct AttnParams {
     const int32_t* seq_lens;     // [B]
     int B, H, Hkv, G;
     int layers, layer, page_size, max_blocks;
+    int page_shift;              // log2(page_size) when it is a power of two, else -1
     int chunk_blocks;            // 16-token blocks per CTA
     int max_chunks;              // partial slots per (b, h)
     float scale_log2e;           // softmax scale * log2(e)
@@ -157,12 +165,23 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
     unsigned char* wsm = smem + warp * (ST * SB);
     const int32_t* bt = p.block_table + (size_t)b * p.max_blocks;
 
+    int pg_next;
+    {
+        const int tokf = (blk0 + warp) * AT_BLK;
+        const int pi = p.page_shift >= 0 ? (tokf >> p.page_shift) : tokf / p.page_size;
+        pg_next = bt[min(pi, p.max_blocks - 1)];
+    }
     auto issue = [&](int i) {   // i-th block of this warp -> stage i % AT_STAGES
         if (i < my_n) {
             const int blk = blk0 + warp + AT_WARPS * i;
             const int tok0 = blk * AT_BLK;
-            const int page = bt[tok0 / p.page_size];
-            const int slot0 = tok0 % p.page_size;
+            const int page = pg_next;           // looked up one issue ahead: the L2 round trip is off the critical path
+            const int slot0 = p.page_shift >= 0 ? (tok0 & (p.page_size - 1)) : tok0 % p.page_size;
+            {
+                const int tokn = tok0 + AT_WARPS * AT_BLK;
+                const int pi = p.page_shift >= 0 ? (tokn >> p.page_shift) : tokn / p.page_size;
+                pg_next = bt[min(pi, p.max_blocks - 1)];
+            }
             const size_t ko = kv_block_offset(page, p.layers, p.layer, 0, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
             const size_t vo = kv_block_offset(page, p.layers, p.layer, 1, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
             unsigned char* ks = wsm + (i % ST) * SB;
@@ -412,12 +431,12 @@ __global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(con
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
         const float m_new = fmaxf(m_run, mx);
-        const float corr = exp2f(m_run - m_new);   // 0 on the first block (m_run = -inf)
+        const float corr = fast_exp2(m_run - m_new);   // 0 on the first block (m_run = -inf)
         float psum = 0.f;
         uint32_t pa[4];
         {
-            const float p00 = exp2f(s[0][0] - m_new), p01 = exp2f(s[0][1] - m_new);
-            const float p10 = exp2f(s[1][0] - m_new), p11 = exp2f(s[1][1] - m_new);
+            const float p00 = fast_exp2(s[0][0] - m_new), p01 = fast_exp2(s[0][1] - m_new);
+            const float p10 = fast_exp2(s[1][0] - m_new), p11 = fast_exp2(s[1][1] - m_new);
             psum = (p00 + p01) + (p10 + p11);
             if (!I8) {
                 pa[0] = pack_bf16x2(p00, p01);   // A frag: row g, k = 2t,2t+1
@@ -781,6 +800,8 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     const int nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
     p.chunk_blocks = chunk_blocks;
     p.max_chunks = nchunks;
+    p.page_shift = -1;
+    if ((p.page_size & (p.page_size - 1)) == 0) { p.page_shift = 0; while ((1 << p.page_shift) < p.page_size) ++p.page_shift; }
     p.direct = (nchunks <= 1);
     if (!p.direct) {
         const size_t need = (size_t)p.B * p.H * nchunks * (AT_D + 2) * sizeof(float);

@@ -181,8 +181,8 @@ int launch_gemm_oneshot(const OneshotArgs& a, cudaStream_t s, bool pdl) {
     if (a.ldq % 16 || a.k_off % WF_QK) { set_error("gemm_oneshot: ldq %% 16 and k_off %% 128 must be 0"); return WF_ERR_INVALID; }
     if (!g_kc_max) {
         const char* e = getenv("WF_ONESHOT_KC");
-        g_kc_max = e ? atoi(e) : 6;
-        if (g_kc_max < 1 || g_kc_max > 12) g_kc_max = 6;
+        g_kc_max = e ? atoi(e) : 4;
+        if (g_kc_max < 1 || g_kc_max > 12) g_kc_max = 4;
     }
     // wide matrices take 128-row units (halves the L2->SM activation traffic), the rest 64-row units
     const bool wide = p.RB >= 8 * 64;
