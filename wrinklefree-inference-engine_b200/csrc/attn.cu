@@ -40,7 +40,7 @@ constexpr int AT_SMEM = AT_WARPS * AT_STAGES * AT_STAGE_BYTES;   // 96 KB
 // (times 2^8 to stay clear of f16 subnormals; undone exactly at the end).
 // The d index inside a 16-wide granule is permuted identically for Q and K (k = 4t.. instead of 2t.., 2t+8..).
 constexpr int AT8_ROW = AT_D;
-constexpr int AT8_STAGES = 6;
+constexpr int AT8_STAGES = 4;                                    // 67.6 KB per CTA: three CTAs (12 warps) per SM
 constexpr int AT8_SCALE_OFF = 2 * AT_BLK * AT8_ROW;                 // 16 K scales | 16 V scales
 constexpr int AT8_STAGE_BYTES = AT8_SCALE_OFF + 2 * AT_BLK * 4;     // 4224
 constexpr int AT8_SMEM = AT_WARPS * AT8_STAGES * AT8_STAGE_BYTES;   // 101,376
@@ -140,7 +140,7 @@ __device__ __forceinline__ size_t kv_scale_offset(int page, int layers, int laye
 }
 
 template <bool FUSED, bool I8>
-__global__ void __launch_bounds__(AT_WARPS * 32, 2) paged_decode_attn_kernel(const AttnParams p) {
+__global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_kernel(const AttnParams p) {
     constexpr int ST = I8 ? AT8_STAGES : AT_STAGES;
     constexpr int SB = I8 ? AT8_STAGE_BYTES : AT_STAGE_BYTES;
     constexpr int ROW = I8 ? AT8_ROW : AT_ROW;
