@@ -25,7 +25,7 @@ __global__ void embed_kernel(const uint4* __restrict__ table, const int32_t* __r
 // 64-wide k stages through a 4-stage cp.async ring, XOR-swizzled smem, ldmatrix + mma.m16n8k16 bf16.
 constexpr int LM_ROWS = 128;
 constexpr int LM_KC = 64;                       // k per stage (128 B per row)
-constexpr int LM_STAGES = 4;
+constexpr int LM_STAGES = 3;                    // 72 KB per CTA at M = 64: three CTAs (24 warps) per SM
 
 template <int NT>
 __global__ void __launch_bounds__(256) lm_head_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* __restrict__ E,
