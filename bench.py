@@ -35,6 +35,18 @@ for p in (str(ROOT), str(PKG)):
 if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":   # keeps "NCCL version ..." off stdout: rank 0 prints ONE JSON line
     os.environ["NCCL_DEBUG"] = "WARN"
 
+# stdout carries exactly ONE JSON line: anything a library writes to fd 1 (NCCL prints its version banner there when torch
+# initialises the communicator) is sent to stderr, and the JSON line goes to a private duplicate of the original stdout.
+sys.stdout.flush()
+_JSON_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(obj) -> None:
+    _JSON_OUT.write(json.dumps(obj) + "\n")
+    _JSON_OUT.flush()
+
+
 import numpy as np
 import torch
 
@@ -146,7 +158,7 @@ def run_gpu_tp(args):
                          "algorithmic_bytes_per_launch": per_gpu, "avg_launch_ms": ms_step},
             "cpu_baseline": None,
         }
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -294,7 +306,7 @@ def run_reference(args):
         "cpu_baseline": {"value": val, "unit": "tok/s", "cores": cores, "kind": kind, "sample": desc},
         "e2e": {"value": val, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -515,7 +527,7 @@ def run_gpu(args):
             "breakdown_ms": breakdown,
             "aux": aux,
         }
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -533,7 +545,7 @@ def main():
     args = ap.parse_args()
     if args.workload in TP_WORKLOADS:
         if args.impl == "reference":
-            print(json.dumps({"impl": "reference", "unavailable": "the reference arm is defined for the 2B workloads (bs64 / bs1) only"}))
+            emit({"impl": "reference", "unavailable": "the reference arm is defined for the 2B workloads (bs64 / bs1) only"})
             return 0
         return run_gpu_tp(args)
     if args.impl == "reference":
