@@ -33,12 +33,20 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     _lib.require_gpu()
     ok = True
-    for batch, steps, ctx, kvd in ((1, 6, 0, "bf16"), (3, 4, 37, "bf16"), (12, 4, 21, "bf16"), (3, 6, 0, "int8"), (12, 20, 0, "int8")):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    # last case: the TP engine is filled by the checkpoint loader from a FULL HF-packed state dict (every rank shards on the fly)
+    for batch, steps, ctx, kvd, via_loader in ((1, 6, 0, "bf16", False), (3, 4, 37, "bf16", False), (12, 4, 21, "bf16", False),
+                                               (3, 6, 0, "int8", False), (12, 20, 0, "int8", False), (3, 4, 0, "bf16", True)):
         cfg = EngineConfig(hidden=512, layers=3, heads=4 * world, kv_heads=world, head_dim=128, ffn=256 * world, vocab=1000, max_seq=128,
                            page_size=16, max_batch=batch, kv_dtype=kvd)
-        weights = make_weights(cfg, seed=5 + batch)
+        weights = make_weights(cfg, seed=5 + batch, keep_ternary=via_loader)
         eng = Engine(cfg, tp_rank=rank, tp_size=world)
-        eng.load_weights(tp.shard_weights(weights, rank, world))
+        if via_loader:
+            from test_gpu_loader import _state_dict
+            from wf_bitnet import loader
+            loader.load_state_dict(eng, _state_dict(cfg, weights, "hf"))
+        else:
+            eng.load_weights(tp.shard_weights(weights, rank, world))
         tp.attach(eng)
         ref = None
         if rank == 0:
@@ -75,7 +83,7 @@ def main():
             if not torch.equal(n_tp, n_ref):
                 ok = False
                 print(f"[tp_check] MISMATCH after graph replay batch={batch}: {n_tp} vs {n_ref}", flush=True)
-            print(f"[tp_check] batch={batch} kv={kvd}: tp{world} == tp1 over {steps}+3 steps: {ok}; launches/step tp={eng.launches_per_step()} ref={ref.launches_per_step()}", flush=True)
+            print(f"[tp_check] batch={batch} kv={kvd} loader={via_loader}: tp{world} == tp1 over {steps}+3 steps: {ok}; launches/step tp={eng.launches_per_step()} ref={ref.launches_per_step()}", flush=True)
         flag = torch.tensor([1 if ok else 0], device="cuda")
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         ok = bool(flag.item())

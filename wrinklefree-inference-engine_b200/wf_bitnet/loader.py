@@ -65,11 +65,28 @@ def _i2s_and_scale(sd: Dict[str, torch.Tensor], base: str, N: int, K: int):
     return packed, float(scale_t.reshape(-1)[0].item())
 
 
+def _shard(packed: torch.Tensor, name: str, rank: int, size: int) -> torch.Tensor:
+    """This rank's piece of a full I2_S matrix (wf_bitnet/tp.py: q/k/v/gate/up by output rows, o/down by input columns in
+    whole 128-blocks = 32 packed bytes)."""
+    if size == 1:
+        return packed
+    if name in ("o", "down"):
+        k4 = packed.shape[1]
+        if k4 % (32 * size):
+            raise ValueError(f"{name}_proj: in_features ({k4 * 4}) must be divisible by 128 * tp_size ({128 * size})")
+        s = k4 // size
+        return packed[:, rank * s:(rank + 1) * s].contiguous()
+    n = packed.shape[0]
+    if n % size:
+        raise ValueError(f"{name}_proj: rows ({n}) not divisible by tp_size {size}")
+    s = n // size
+    return packed[rank * s:(rank + 1) * s].contiguous()
+
+
 def load_state_dict(engine, sd: Dict[str, torch.Tensor]) -> None:
-    """Fill a single-GPU engine from an HF-named state dict (any of the three forms above, mixed freely)."""
+    """Fill an engine from an HF-named state dict (any of the three forms above, mixed freely).  A tensor-parallel engine
+    (tp_size > 1) takes the FULL state dict on every rank and keeps its own shard; call wf_bitnet.tp.attach afterwards."""
     cfg = engine.cfg
-    if engine.tp_size != 1:
-        raise NotImplementedError("load_state_dict: shard with wf_bitnet.tp.shard_weights for tensor-parallel engines")
     shapes = {
         "q": (cfg.heads * cfg.head_dim, cfg.hidden), "k": (cfg.kv_heads * cfg.head_dim, cfg.hidden),
         "v": (cfg.kv_heads * cfg.head_dim, cfg.hidden), "o": (cfg.hidden, cfg.heads * cfg.head_dim),
@@ -78,6 +95,7 @@ def load_state_dict(engine, sd: Dict[str, torch.Tensor]) -> None:
     for li in range(cfg.layers):
         for name, (N, K) in shapes.items():
             packed, scale = _i2s_and_scale(sd, _proj_key(li, name), N, K)
+            packed = _shard(packed, name, engine.tp_rank, engine.tp_size)
             check(lib().wf_engine_set_linear(engine._h, li, name.encode(), packed.data_ptr(), scale, 0))
             torch.cuda.synchronize()   # `packed` may be freed by the next iteration; the engine staged its own copy
         for ours, theirs in _NORMS.items():
