@@ -41,23 +41,39 @@ __global__ void __launch_bounds__(256) lm_head_kernel(const __nv_bfloat16* __res
     const int m0 = blockIdx.y * MT;
     const int nchunks = K / LM_KC;
 
+    // per-thread source rows / swizzled destinations of the E tile are loop-invariant: only the k offset moves per stage
+    constexpr int EJ = LM_ROWS * 8 / 256;
+    const __nv_bfloat16* e_src[EJ];
+    int e_dst[EJ], e_nb[EJ];
+#pragma unroll
+    for (int j = 0; j < EJ; ++j) {
+        const int g = tid + 256 * j;
+        const int r = g >> 3, c = g & 7;
+        const int v = v0 + r;
+        e_nb[j] = (v < V) ? 16 : 0;
+        e_src[j] = E + (size_t)(v < V ? v : 0) * K + c * 8;
+        e_dst[j] = r * 128 + ((c ^ (r & 7)) << 4);
+    }
+    constexpr int HJ = (MT * 8 + 255) / 256;
+    const __nv_bfloat16* h_src[HJ];
+    int h_dst[HJ], h_nb[HJ];
+#pragma unroll
+    for (int j = 0; j < HJ; ++j) {
+        const int g = tid + 256 * j;
+        const int r = (g >> 3) % MT, c = g & 7;
+        const int m = m0 + r;
+        h_nb[j] = (m < B) ? 16 : 0;
+        h_src[j] = h + (size_t)(m < B ? m : 0) * K + c * 8;
+        h_dst[j] = r * 128 + ((c ^ (r & 7)) << 4);
+    }
     auto load_stage = [&](int chunk, int stage) {
         unsigned char* es = smem + stage * STAGE;
         unsigned char* hs = es + E_STAGE;
-        for (int g = tid; g < LM_ROWS * 8; g += 256) {
-            const int r = g >> 3, c = g & 7;
-            const int v = v0 + r;
-            const int ok = v < V;
-            cp_async16_zfill(es + r * 128 + ((c ^ (r & 7)) << 4),
-                             ok ? (const void*)(E + (size_t)v * K + chunk * LM_KC + c * 8) : (const void*)E, ok ? 16 : 0);
-        }
-        for (int g = tid; g < MT * 8; g += 256) {
-            const int r = g >> 3, c = g & 7;
-            const int m = m0 + r;
-            const int ok = m < B;
-            cp_async16_zfill(hs + r * 128 + ((c ^ (r & 7)) << 4),
-                             ok ? (const void*)(h + (size_t)m * K + chunk * LM_KC + c * 8) : (const void*)h, ok ? 16 : 0);
-        }
+#pragma unroll
+        for (int j = 0; j < EJ; ++j) cp_async16_zfill(es + e_dst[j], e_src[j] + chunk * LM_KC, e_nb[j]);
+#pragma unroll
+        for (int j = 0; j < HJ; ++j)
+            if (HJ * 256 == MT * 8 || tid + 256 * j < MT * 8) cp_async16_zfill(hs + h_dst[j], h_src[j] + chunk * LM_KC, h_nb[j]);
     };
 
     float acc[NT][4];
