@@ -267,23 +267,28 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
         {
             const float wq = p.qkv_wscale[0];
             const float* hq = arow + ((size_t)kvh * p.G + g) * AT_D;
-            // all 16 loads are issued before the first use: one L2 round trip instead of sixteen
-            float2 xa[8], xb[8];
+            // The fragments depend on the lane only, not on the warp: each of the 4 warps dequantises + rotates a quarter
+            // (i = 2*warp, 2*warp + 1) and the CTA shares them through 2 KB of shared memory - a quarter of the loads and of
+            // the ALU work per warp on the prologue every CTA pays.  Loads are issued before the first use.
+            __shared__ uint32_t qsh[16][32];
+            float2 xa[2], xb[2];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
+            for (int u = 0; u < 2; ++u) {
+                const int i = 2 * warp + u;
                 const int d = I8 ? (i >> 1) * 16 + 4 * t + 2 * (i & 1) : (i >> 1) * 16 + (i & 1) * 8 + 2 * t;   // < 64; partner at d + 64
-                xa[i] = make_float2(0.f, 0.f);
-                xb[i] = make_float2(0.f, 0.f);
+                xa[u] = make_float2(0.f, 0.f);
+                xb[u] = make_float2(0.f, 0.f);
                 if (g < p.G) {
-                    asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(xa[i].x), "=f"(xa[i].y) : "l"(hq + d));
-                    asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(xb[i].x), "=f"(xb[i].y) : "l"(hq + d + 64));
+                    asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(xa[u].x), "=f"(xa[u].y) : "l"(hq + d));
+                    asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(xb[u].x), "=f"(xb[u].y) : "l"(hq + d + 64));
                 }
             }
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
+            for (int u = 0; u < 2; ++u) {
+                const int i = 2 * warp + u;
                 const int ks = i >> 1, half = i & 1;
                 const int d = I8 ? ks * 16 + 4 * t + 2 * half : ks * 16 + half * 8 + 2 * t;
-                const float a[2] = {xa[i].x, xa[i].y}, bq[2] = {xb[i].x, xb[i].y};
+                const float a[2] = {xa[u].x, xa[u].y}, bq[2] = {xb[u].x, xb[u].y};
                 float o1[2], o2[2];
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
@@ -296,9 +301,12 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
                     o1[e] = bf16_round(x1 * c) - bf16_round(x2 * sn);
                     o2[e] = bf16_round(x1 * sn) + bf16_round(x2 * c);
                 }
-                qa[ks][half] = I8 ? pack_f16x2(bf16_round(o1[0]), bf16_round(o1[1])) : pack_bf16x2(o1[0], o1[1]);
-                qa[ks + 4][half] = I8 ? pack_f16x2(bf16_round(o2[0]), bf16_round(o2[1])) : pack_bf16x2(o2[0], o2[1]);
+                qsh[ks * 2 + half][lane] = I8 ? pack_f16x2(bf16_round(o1[0]), bf16_round(o1[1])) : pack_bf16x2(o1[0], o1[1]);
+                qsh[(ks + 4) * 2 + half][lane] = I8 ? pack_f16x2(bf16_round(o2[0]), bf16_round(o2[1])) : pack_bf16x2(o2[0], o2[1]);
             }
+            __syncthreads();
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks) { qa[ks][0] = qsh[ks * 2][lane]; qa[ks][1] = qsh[ks * 2 + 1][lane]; }
         }
         // the CTA whose chunk holds the new token appends k (RoPE'd) and v before it streams that block
         const int blk_pos = pos / AT_BLK;
