@@ -139,3 +139,27 @@ def test_sglang_model_mirror_imports_without_gpu():
     assert EntryClass is BitNetForCausalLM and BitNetLinear is not None
     assert _is_packed_weight(torch.zeros(8, 4, dtype=torch.uint8)) and not _is_packed_weight(torch.zeros(8, 16))
     assert _is_ternary_float(torch.tensor([[-1.0, 0.0, 1.0]])) and not _is_ternary_float(torch.tensor([[0.5]]))
+
+
+def test_loader_shards_like_tp_shard_weights():
+    """The checkpoint loader's on-the-fly sharding (device tensors) must cut exactly what wf_bitnet.tp.shard_rows / shard_cols
+    cut from the numpy form: q/k/v/gate/up by output rows, o/down by input columns in whole 128-blocks (32 packed bytes)."""
+    import numpy as np
+    import torch
+    from wf_bitnet import loader, tp
+    rng = np.random.default_rng(0)
+    full = rng.integers(0, 256, size=(64, 96), dtype=np.uint8)          # N = 64, K = 384 (three 128-blocks)
+    t = torch.from_numpy(full)
+    for size in (1, 2):
+        for rank in range(size):
+            for name in ("q", "k", "v", "gate", "up"):
+                want = full if size == 1 else tp.shard_rows(full, rank, size)
+                assert np.array_equal(loader._shard(t, name, rank, size).numpy(), want)
+    for rank in range(3):
+        for name in ("o", "down"):
+            assert np.array_equal(loader._shard(t, name, rank, 3).numpy(), tp.shard_cols(full, rank, 3))
+    import pytest
+    with pytest.raises(ValueError):
+        loader._shard(t, "o", 0, 2)          # 96 bytes do not split into two runs of whole 32-byte blocks
+    with pytest.raises(ValueError):
+        loader._shard(t, "q", 0, 5)
