@@ -262,3 +262,67 @@ def test_kvcache_mirror_int8_update_get_attention(golden):
     assert m8["total_mb"] * 2 == m16["total_mb"]
     cache.clear()
     assert cache.current_seq_len == 0
+
+
+@pytest.mark.parametrize("mode", ["FP8_E4M3", "FP8_E5M2"])
+def test_kvcache_mirror_fp8_modes_match_the_reference_class(golden, mode):
+    """The reference's two "FP8" cache modes are int8 storage with an absmax / 127 scale (kv_cache.py:150-196).
+    tests/golden/kv_modes.npz holds what the reference's own KVCache stores and returns in those modes, row by row:
+    the mirror's update / get must reproduce the dequantised rows and the stored scale bit for bit, and the pool the
+    codes."""
+    from wrinklefree_inference.kv_cache import KVCache, KVCacheConfig, KVCacheDtype, attention_with_kv_cache
+    g = golden["kv_modes"]
+    x = torch.from_numpy(g["x"])
+    H, D, S, R0 = 4, 128, 8, 32
+    cfg = KVCacheConfig(max_seq_len=32, num_layers=2, num_heads=H, head_dim=D, dtype=getattr(KVCacheDtype, mode))
+    assert cfg.bytes_per_token_per_layer == 2 * H * D
+    cache = KVCache(cfg)
+    rows = x[R0: R0 + S * H].view(S, H, D)
+    for pos in range(S):
+        cache.update(1, rows[pos].view(1, 1, H, D), rows[pos].flip(0).contiguous().view(1, 1, H, D), pos)
+    k, v = cache.get(1)
+    want = torch.from_numpy(g[f"{mode}_deq"])[R0: R0 + S * H].view(S, H, D)
+    assert torch.equal(k.float().cpu(), want)
+    assert torch.equal(v.float().cpu(), want.flip(1))
+    assert cache.k_scales[1].item() == np.float32(g[f"{mode}_scales"][R0 + S * H - 1])
+    codes = cache.kv.codes().cpu()[0, 1, 0].permute(1, 0, 2)[:S]          # page 0, layer 1, K: [slot][head][D]
+    assert torch.equal(codes, torch.from_numpy(g[f"{mode}_codes"])[R0: R0 + S * H].view(S, H, D))
+    gen = torch.Generator().manual_seed(6)
+    q = torch.randn(1, H, 1, D, generator=gen)
+    nk, nv = torch.randn(1, 1, H, D, generator=gen), torch.randn(1, 1, H, D, generator=gen)
+    out = attention_with_kv_cache(q, cache, 1, nk, nv, S)
+    k2, v2 = cache.get(1)
+    ref = OM.attention_gqa_fp32(q.view(H, D).to(torch.bfloat16), k2.cpu(), v2.cpu())
+    assert torch.allclose(out.view(H, D).cpu(), ref, atol=2e-2 * ref.abs().max().item(), rtol=2e-2)
+
+
+def test_kvcache_mirror_fp16_and_fp32_caches(golden):
+    """FP16 / FP32 caches: update / get are exact (the golden rows are what the reference's FP16 cache returns), and
+    attention_with_kv_cache over an FP16 cache matches the output of the reference's own attention_with_kv_cache
+    (tests/golden/kv_modes.npz attn_*) within bf16 tolerance."""
+    from wrinklefree_inference.kv_cache import KVCache, KVCacheConfig, KVCacheDtype, attention_with_kv_cache
+    g = golden["kv_modes"]
+    x = torch.from_numpy(g["x"])
+    R, D = x.shape
+    cache = KVCache(KVCacheConfig(max_seq_len=R, num_layers=1, num_heads=1, head_dim=D, dtype=KVCacheDtype.FP16))
+    for r in range(R):
+        cache.update(0, x[r].view(1, 1, 1, D), (x[r] * 0.5).view(1, 1, 1, D), r)
+    k, v = cache.get(0)
+    assert k.dtype == torch.float16
+    assert np.array_equal(k.float().cpu().reshape(R, D).numpy(), g["FP16_k"])
+    assert np.array_equal(v.float().cpu().reshape(R, D).numpy(), g["FP16_v"])
+    ks, vs, q = torch.from_numpy(g["attn_k"]), torch.from_numpy(g["attn_v"]), torch.from_numpy(g["attn_q"]).to(torch.bfloat16)
+    S, H = ks.shape[0], ks.shape[1]
+    for dt in (KVCacheDtype.FP16, KVCacheDtype.FP32):
+        cache = KVCache(KVCacheConfig(max_seq_len=32, num_layers=1, num_heads=H, head_dim=D, dtype=dt))
+        for pos in range(S - 1):
+            cache.update(0, ks[pos].view(1, 1, H, D), vs[pos].view(1, 1, H, D), pos)
+        out = attention_with_kv_cache(q, cache, 0, ks[S - 1].view(1, 1, H, D), vs[S - 1].view(1, 1, H, D), S - 1)
+        want = torch.from_numpy(g["attn_out"])
+        assert out.shape == want.shape
+        assert torch.allclose(out.float().cpu(), want, atol=2e-2, rtol=2e-2), (dt, (out.float().cpu() - want).abs().max())
+
+
+def test_kvcache_config_default_dtype_is_the_references():
+    from wrinklefree_inference.kv_cache import KVCacheConfig, KVCacheDtype
+    assert KVCacheConfig().dtype == KVCacheDtype.INT8          # kv_cache.py:56-57

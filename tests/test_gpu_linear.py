@@ -62,6 +62,30 @@ def test_gemv_large_shapes_every_slab_mode(nk, m):
         assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("nk", [(57344, 8192), (8192, 28672)])
+def test_gemv_70b_shapes(nk):
+    """The 70B matrices wf_bench_gemv times and reports bandwidth on: gate|up (57344 x 8192, 117 MB packed) and down
+    (8192 x 28672, 224 k-blocks: the longest row dot of any BASELINE config, |acc| up to 7.3 M), M = 1 (dp4a), 2 and 8 (mma).
+    The expected accumulators come straight from the ternary matrix in exact float64 row chunks (no unpack in between);
+    the packed bytes are the C oracle's (quantize_i2_s restatement)."""
+    from wf_bitnet import ops
+    n, k = nk
+    rng = np.random.default_rng(n + 5 * k)
+    w = rng.integers(-1, 2, size=(n, k), dtype=np.int8)
+    packed = np.concatenate([O.pack_ternary(w[r0:r0 + 8192].astype(np.float32))[0] for r0 in range(0, n, 8192)])
+    tile = ops.i2s_to_tile(cu(packed))
+    for m in (1, 2, 8):
+        q = rng.integers(-128, 128, size=(m, k)).astype(np.int8)
+        q[0, : k // 2] = 127          # drive one row towards the accumulator range limit
+        want = np.empty((m, n), np.int32)
+        qf = q.astype(np.float64).T
+        for r0 in range(0, n, 4096):
+            want[:, r0:r0 + 4096] = np.rint((w[r0:r0 + 4096].astype(np.float64) + 1.0) @ qf).astype(np.int64).astype(np.int32).T
+        for _ in range(2):   # twice: the self-cleaning split-K workspace must be left zero
+            got = ops.ternary_linear(tile, n, k, cu(q), mode="i32_plus1", algo=1).cpu().numpy()
+            assert np.array_equal(got, want), (nk, m)
+
+
 def test_gemv_large_relu2_epilogue():
     """fused gate|up with relu^2*up at the 8B ffn width through the GEMV (two-row-block finalisation groups, two CTAs per SM)."""
     from wf_bitnet import ops

@@ -113,4 +113,10 @@ def test_loader_errors():
     with pytest.raises(ValueError):
         loader.load_state_dict(eng, {"model.layers.0.self_attn.q_proj.qweight": torch.zeros(8, 8, dtype=torch.uint8),
                                      "model.layers.0.self_attn.q_proj.weight_scale": torch.ones(1)})
+    # a float master-weight checkpoint (not ternary) must be rejected, not clipped to {-1,0,+1} silently
+    # (the reference converter guards the same path with _is_ternary_float, cache/bitnet_converter.py:80-103,161)
+    g = torch.Generator().manual_seed(3)
+    with pytest.raises(ValueError, match="not ternary"):
+        loader.load_state_dict(eng, {"model.layers.0.self_attn.q_proj.weight": (0.02 * torch.randn(256, 256, generator=g)).to(torch.bfloat16),
+                                     "model.layers.0.self_attn.q_proj.weight_scale": torch.ones(1)})
     eng.close()

@@ -116,3 +116,37 @@ def test_causal_lm_matches_engine_and_oracle():
     model.reset()
     ref.reset()
     assert model.generate([3, 400, 17], 6) == ref.generate_greedy([3, 400, 17], 6)
+
+
+@pytest.mark.parametrize("batch", [1, 5, 40])
+def test_fused_qkv_and_mlp_ops_match_the_oracle_step(batch):
+    """torch.ops.sgl_kernel.bitnet_qkv_forward_cpu / bitnet_mlp_forward_cpu (sglang_optimization_plan.md:326-331) against the
+    oracle's restatement of scripts/direct_inference_full.py:186-208 (linear) and :253-264 (MLP), row by row (each token is an
+    independent copy of the reference's bs=1 path): bf16 outputs must be IDENTICAL — same integer accumulators, same rounding points."""
+    import sgl_kernel  # noqa: F401
+    from oracle import model as OM
+    hidden, ffn, nq, nkv = 256, 384, 256, 128
+    rng = np.random.default_rng(batch)
+    mats = {n: rng.integers(-1, 2, size=shp).astype(np.float32) for n, shp in
+            (("q", (nq, hidden)), ("k", (nkv, hidden)), ("v", (nkv, hidden)), ("gate", (ffn, hidden)), ("up", (ffn, hidden)), ("down", (hidden, ffn)))}
+    packed = {n: O.pack_ternary(w)[0] for n, w in mats.items()}
+    scales = {n: float(np.float32(rng.uniform(0.5, 2.5))) for n in mats}
+    g = torch.Generator().manual_seed(batch)
+    x = (torch.randn(batch, hidden, generator=g) * 2).to(torch.bfloat16)
+    gamma = (1.0 + 0.1 * torch.randn(ffn, generator=g)).to(torch.bfloat16)
+    dev = {n: torch.from_numpy(p).cuda() for n, p in packed.items()}
+    q, k, v = torch.ops.sgl_kernel.bitnet_qkv_forward_cpu(x.cuda(), dev["q"], dev["k"], dev["v"], scales["q"], scales["k"], scales["v"])
+    y = torch.ops.sgl_kernel.bitnet_mlp_forward_cpu(x.cuda(), dev["gate"], dev["up"], dev["down"], scales["gate"], scales["up"], scales["down"], gamma.cuda(), 1e-5)
+    assert q.shape == (batch, nq) and k.shape == (batch, nkv) and y.shape == (batch, hidden) and y.dtype == torch.bfloat16
+    for m in range(batch):
+        for name, got in (("q", q), ("k", k), ("v", v)):
+            want = OM.bitnet_linear(x[m], packed[name], scales[name], use_ref=False)
+            assert torch.equal(got[m].cpu(), want), (name, m)
+        gate = OM.bitnet_linear(x[m], packed["gate"], scales["gate"])
+        up = OM.bitnet_linear(x[m], packed["up"], scales["up"])
+        act = OM.rms_norm(torch.relu(gate).square() * up, gamma, 1e-5)
+        want = OM.bitnet_linear(act, packed["down"], scales["down"])
+        assert torch.equal(y[m].cpu(), want), ("mlp", m, (y[m].cpu().float() - want.float()).abs().max())
+    # 1-D input (the reference's bs=1 call shape) and a second call through the cached fused tiles
+    q1, _, _ = torch.ops.sgl_kernel.bitnet_qkv_forward_cpu(x[0].cuda(), dev["q"], dev["k"], dev["v"], scales["q"], scales["k"], scales["v"])
+    assert q1.shape == (nq,) and torch.equal(q1.cpu(), q[0].cpu())

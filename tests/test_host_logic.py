@@ -90,6 +90,16 @@ def test_torch_ops_are_registered_under_reference_names():
     assert torch.ops.sgl_kernel.bitnet_gemv_cpu(pw, x[0], 1.0).shape == (24,)
     q, s = torch.ops.sgl_kernel.bitnet_quantize_activations_cpu(torch.empty(3, 128, device="meta"))
     assert q.dtype == torch.int8 and q.shape == (3, 128) and s.shape == (1,)
+    # the optional fused ops (sglang_optimization_plan.md:326-331)
+    for name in ("bitnet_qkv_forward_cpu", "bitnet_mlp_forward_cpu"):
+        assert hasattr(torch.ops.sgl_kernel, name)
+    xm = torch.empty(5, 128, dtype=torch.bfloat16, device="meta")
+    kw = torch.empty(8, 32, dtype=torch.uint8, device="meta")
+    qo, ko, vo = torch.ops.sgl_kernel.bitnet_qkv_forward_cpu(xm, pw, kw, kw, 1.0, 1.0, 1.0)
+    assert qo.shape == (5, 24) and ko.shape == (5, 8) and vo.shape == (5, 8) and qo.dtype == torch.bfloat16
+    dw = torch.empty(128, 6, dtype=torch.uint8, device="meta")          # down: [hidden 128, ffn 24 / 4]
+    y = torch.ops.sgl_kernel.bitnet_mlp_forward_cpu(xm, pw, pw, dw, 1.0, 1.0, 1.0, torch.empty(24, device="meta"), 1e-5)
+    assert y.shape == (5, 128)
 
 
 def test_oracle_model_runs_tiny_config():

@@ -786,13 +786,12 @@ int launch_rope_kv_append(const RopeParams& p, cudaStream_t s, bool pdl) {
 
 // picks the chunking, launches attention (+ merge when sequences span several chunks)
 int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, size_t workspace_bytes, cudaStream_t s, bool pdl) {
-    static bool attr = false;
-    if (!attr) {
+    static DevOnce attr;
+    if (attr.need()) {
         if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM), "attn smem")) return WF_ERR_CUDA;
         if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM), "attn smem")) return WF_ERR_CUDA;
         if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT8_SMEM), "attn smem")) return WF_ERR_CUDA;
         if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT8_SMEM), "attn smem")) return WF_ERR_CUDA;
-        attr = true;
     }
     const int max_blocks16 = (max_seq_hint + AT_BLK - 1) / AT_BLK;
     // chunk size: aim for >= 4 CTAs per SM-slot (2 per SM) over the whole grid, but never below 4 blocks (64 tokens)

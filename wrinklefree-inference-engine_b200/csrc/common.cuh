@@ -23,6 +23,18 @@ int cuda_check(cudaError_t e, const char* what);
 int launch_check(cudaError_t e, const char* what);   // cuda_check + counts one kernel launch
 long long launch_count();
 int sm_count();
+// "once per device" guard: cudaFuncSetAttribute and the SM count are per-device state, and the op-level C ABI may be called
+// from several GPUs of one process (one bit per device ordinal)
+struct DevOnce {
+    unsigned long long done = 0;
+    bool need() {
+        int d = 0;
+        if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d > 63) return true;
+        if ((done >> d) & 1ull) return false;
+        done |= 1ull << d;
+        return true;
+    }
+};
 
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

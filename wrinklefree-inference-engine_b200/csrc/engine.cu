@@ -46,6 +46,8 @@ struct wf_engine {
     void* peer_opened[TP_MAX] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool tp_attached = false;
     int* d_step = nullptr;
+    int* d_err = nullptr;                    // device error word (bounded spins that gave up), mirrored into h_err_pinned at every host sync
+    int* h_err_pinned = nullptr;
     __nv_bfloat16* h_full = nullptr;
     int v_lo = 0, v_n = 0;                   // this rank's vocab slice of the tied LM head
     unsigned long long* trace = nullptr;     // WF_TRACE=1: 16 globaltimer stamps per linear_small launch
@@ -539,10 +541,14 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
         e->tp.peer[c.tp_rank] = e->comm;
         e->tp.off_flags = e->off_flags;
         int* cnt = nullptr;
-        if ((rc = dalloc(e, &cnt, (size_t)4 * c.layers + 1)) || (rc = dalloc(e, &e->d_step, 1))) return fail(rc);
-        if (cuda_check(cudaMemset(cnt, 0, ((size_t)4 * c.layers + 1) * 4), "cnt memset") || cuda_check(cudaMemset(e->d_step, 0, 4), "step memset")) return fail(WF_ERR_CUDA);
+        if ((rc = dalloc(e, &cnt, (size_t)4 * c.layers + 1)) || (rc = dalloc(e, &e->d_step, 1)) || (rc = dalloc(e, &e->d_err, 1))) return fail(rc);
+        if (cuda_check(cudaMemset(cnt, 0, ((size_t)4 * c.layers + 1) * 4), "cnt memset") || cuda_check(cudaMemset(e->d_step, 0, 4), "step memset") ||
+            cuda_check(cudaMemset(e->d_err, 0, 4), "err memset")) return fail(WF_ERR_CUDA);
+        if (cuda_check(cudaMallocHost(&e->h_err_pinned, 4), "pinned")) return fail(WF_ERR_CUDA);
+        *e->h_err_pinned = 0;
         e->tp.done_cnt = cnt;
         e->tp.step = e->d_step;
+        e->tp.err = e->d_err;
         e->tp_attached = (T == 1);
     }
     if ((rc = dalloc(e, &e->hid, (size_t)B * e->hidden)) || (rc = dalloc(e, &e->normed, (size_t)B * e->hidden)) ||
@@ -591,6 +597,7 @@ extern "C" void wf_engine_destroy(wf_engine* e) {
     if (e->h_tok_pinned) cudaFreeHost(e->h_tok_pinned);
     if (e->h_next_pinned) cudaFreeHost(e->h_next_pinned);
     if (e->h_pos_pinned) cudaFreeHost(e->h_pos_pinned);
+    if (e->h_err_pinned) cudaFreeHost(e->h_err_pinned);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -598,7 +605,20 @@ extern "C" void wf_engine_destroy(wf_engine* e) {
 extern "C" size_t wf_engine_device_bytes(const wf_engine* e) { return e ? e->dev_bytes : 0; }
 extern "C" void* wf_engine_stream(wf_engine* e) { return e ? (void*)e->stream : nullptr; }
 extern "C" int wf_engine_launches_per_step(const wf_engine* e) { return e ? e->launches : 0; }
-extern "C" int wf_engine_sync(wf_engine* e) { return e ? cuda_check(cudaStreamSynchronize(e->stream), "engine sync") : WF_ERR_INVALID; }
+// device-side spins are bounded (tp_comm.cuh, layer_tail.cu): a wait that gave up leaves a code in the error word
+static int check_device_error(wf_engine* e) {
+    if (!e->d_err) return WF_OK;
+    if (cuda_check(cudaMemcpyAsync(e->h_err_pinned, e->d_err, 4, cudaMemcpyDeviceToHost, e->stream), "err D2H")) return WF_ERR_CUDA;
+    if (cuda_check(cudaStreamSynchronize(e->stream), "engine sync")) return WF_ERR_CUDA;
+    if (*e->h_err_pinned) {
+        const int code = *e->h_err_pinned;
+        set_error("device-side wait timed out (code %d: %s) — a tensor-parallel peer died, the ranks' step counters disagree, or a grid barrier lost a CTA; "
+                  "the engine state is undefined, destroy it", code, code >= 1000 ? "TP exchange flag" : "grid barrier");
+        return WF_ERR_CUDA;
+    }
+    return WF_OK;
+}
+extern "C" int wf_engine_sync(wf_engine* e) { return e ? check_device_error(e) : WF_ERR_INVALID; }
 
 extern "C" int wf_engine_set_linear(wf_engine* e, int layer, const char* name, const uint8_t* i2s, float weight_scale, int is_host) {
     if (!e || !name || !i2s) { set_error("wf_engine_set_linear: null argument"); return WF_ERR_INVALID; }
@@ -746,9 +766,12 @@ extern "C" int wf_engine_set_context(wf_engine* e, int slot, int len, int fill_r
     }
     e->table_dirty = true;
     e->h_pos[slot] = len;
+    // on the engine stream (it is cudaStreamNonBlocking: a default-stream copy could race an in-flight asynchronous step, whose
+    // advance kernel updates the same words)
     const int32_t pl[2] = {len, len + 1};
-    if (cuda_check(cudaMemcpy(e->d_pos + slot, &pl[0], 4, cudaMemcpyHostToDevice), "ctx pos")) return WF_ERR_CUDA;
-    if (cuda_check(cudaMemcpy(e->d_len + slot, &pl[1], 4, cudaMemcpyHostToDevice), "ctx len")) return WF_ERR_CUDA;
+    if (cuda_check(cudaMemcpyAsync(e->d_pos + slot, &pl[0], 4, cudaMemcpyHostToDevice, e->stream), "ctx pos")) return WF_ERR_CUDA;
+    if (cuda_check(cudaMemcpyAsync(e->d_len + slot, &pl[1], 4, cudaMemcpyHostToDevice, e->stream), "ctx len")) return WF_ERR_CUDA;
+    if (cuda_check(cudaStreamSynchronize(e->stream), "ctx sync")) return WF_ERR_CUDA;
     if (fill_random) {
         // a page is one contiguous run of layers*2*Hkv*page_size*D elements
         const size_t page_elems = (size_t)e->cfg.layers * 2 * e->Hkv * ps * e->D;
@@ -791,7 +814,7 @@ extern "C" int wf_engine_decode(wf_engine* e, const int32_t* host_tokens, int B,
     rc = step_graph(e, B, /*feed_back=*/0, 1);
     if (rc) return rc;
     if (cuda_check(cudaMemcpyAsync(e->h_next_pinned, e->d_next, (size_t)B * 4, cudaMemcpyDeviceToHost, e->stream), "next D2H")) return WF_ERR_CUDA;
-    if (cuda_check(cudaStreamSynchronize(e->stream), "decode sync")) return WF_ERR_CUDA;
+    if ((rc = check_device_error(e))) return rc;
     memcpy(host_next_tokens, e->h_next_pinned, (size_t)B * 4);
     for (int b = 0; b < B; ++b) e->h_pos[b] += 1;
     return WF_OK;
@@ -858,10 +881,34 @@ extern "C" int wf_engine_time_kernel(wf_engine* e, const char* which, int B, int
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     const wf_model_config& c = e->cfg;
+    // "attn" times the kernel the step really runs.  Fused engines: paged_decode_attn_kernel<FUSED> (dequant of q|k|v from the raw
+    // accumulator + RoPE + KV append + attention + in-kernel chunk merge) on a stand-in accumulator of random integers;
+    // "attn_unfused" is the per-op kernel + attn_merge_kernel on a zeroed q.
+    const bool fused_attn = (w == "attn") && e->fused;
+    if (fused_attn) {
+        if ((rc = launch_fill_randint_f32(e->acc_qkv, (size_t)B * e->qkv_rows, 0xA77E, 3000, e->stream))) return rc;
+        if ((rc = launch_fill_f32(e->lin_asc, (size_t)B, 0.01f, e->stream))) return rc;
+        if (cuda_check(cudaMemsetAsync(e->lin_rs, 0, (size_t)B * 4, e->stream), "rs memset")) return WF_ERR_CUDA;
+        if (cuda_check(cudaMemsetAsync(e->merge_cnt, 0, (size_t)B * e->Hkv * 4, e->stream), "cnt memset")) return WF_ERR_CUDA;
+    } else if (w == "attn" || w == "attn_unfused") {
+        if (cuda_check(cudaMemsetAsync(e->qrot, 0, (size_t)B * e->attn_dim * 2, e->stream), "qrot memset")) return WF_ERR_CUDA;
+    }
     auto body = [&](int it) -> int {
         const int l = it % c.layers;
         LayerW& L = e->layers[l];
-        if (w == "attn")
+        if (fused_attn) {
+            FusedAttnArgs a = {};
+            a.pool = e->pool; a.kv_scales = e->kv_scales; a.layers = c.layers; a.layer = l; a.Hkv = e->Hkv; a.page_size = c.page_size;
+            a.block_table = e->d_block_table; a.max_blocks = e->max_blocks; a.seq_lens = e->d_len; a.positions = e->d_pos;
+            a.B = B; a.H = e->H; a.scale = 1.0f / sqrtf((float)e->D); a.out = e->attn;
+            a.n_out = 1; a.out_ld = e->attn_full; a.out_col0 = 0; a.signal_flag = -1; a.tp = e->tp;
+            a.qkv_acc = e->acc_qkv; a.qkv_ld = e->qkv_rows; a.qkv_rowsum = e->lin_rs; a.qkv_ascale = e->lin_asc; a.qkv_wscale = L.scales;
+            a.cos_tab = e->cos_tab; a.sin_tab = e->sin_tab; a.max_pos = c.max_seq;
+            a.merge_cnt = e->merge_cnt;
+            a.max_seq_hint = e->attn_seq_hint; a.ws = e->ws_attn; a.ws_bytes = e->ws_attn_bytes;
+            return attn_decode_fused(a, e->stream, false);
+        }
+        if (w == "attn" || w == "attn_unfused")
             return attn_decode(e->qrot, e->pool, c.layers, l, e->Hkv, c.page_size, e->d_block_table, e->max_blocks, e->d_len, B, e->H,
                                1.0f / sqrtf((float)e->D), e->attn, WF_BF16, e->attn_seq_hint, e->ws_attn, e->ws_attn_bytes, e->stream, false, e->kv_scales);
         if (w == "qkv") { const int seg[3] = {e->H * e->D, (e->H + e->Hkv) * e->D, e->qkv_rows}; return linear(e, L.qkv, e->qkv_rows, e->hidden, B, L.scales, 3, seg, 0, e->qkv, e->qkv_rows, nullptr); }
@@ -893,6 +940,10 @@ extern "C" int wf_engine_time_kernel(wf_engine* e, const char* which, int B, int
     cudaEventElapsedTime(&ms, e0, e1);
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
+    if (fused_attn) {   // the step expects a zero accumulator
+        if (cuda_check(cudaMemsetAsync(e->acc_qkv, 0, (size_t)B * e->qkv_rows * 4, e->stream), "acc memset")) return WF_ERR_CUDA;
+        if (cuda_check(cudaStreamSynchronize(e->stream), "sync")) return WF_ERR_CUDA;
+    }
     *ms_out = ms / iters;
     return WF_OK;
 }

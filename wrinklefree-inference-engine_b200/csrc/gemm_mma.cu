@@ -221,10 +221,9 @@ static int launch_cfg(const GemmParams& p, int splits, cudaStream_t s) {
     constexpr int SM_EPI = MT * (ROWS + 1) * 4;
     constexpr int SMEM = SM_PIPE > SM_EPI ? SM_PIPE : SM_EPI;
     auto kern = ternary_gemm_mma_kernel<LAYOUT, WR, WB, NT>;
-    static bool attr = false;
-    if (!attr) {
+    static DevOnce attr;
+    if (attr.need()) {
         if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM), "smem attr")) return WF_ERR_CUDA;
-        attr = true;
     }
     dim3 grid((p.N + ROWS - 1) / ROWS, (p.M + MT - 1) / MT, splits);
     kern<<<grid, 256, SMEM, s>>>(p);

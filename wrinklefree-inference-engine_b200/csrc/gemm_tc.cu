@@ -480,17 +480,17 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static EncodeTiledFn g_encode = nullptr;
-static bool g_tc_attr = false;
+static DevOnce g_tc_attr;
 static int g_tc_cluster = 0, g_tc_nu = 0;
 
 void gemm_tc_init_attrs() {
-    if (!g_tc_attr) {
+    if (g_tc_attr.need()) {
         bool ok = cudaFuncSetAttribute(ternary_gemm_tc_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
         ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
         ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<1, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
         ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
         ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
-        g_tc_attr = ok;
+        (void)ok;
     }
     if (!g_encode) {
         void* fn = nullptr;
@@ -558,7 +558,7 @@ static int launch_tc_cl(const wf_linear_args* a, const EpiParams& ep, cudaStream
 int launch_gemm_tc_red(const uint8_t* w_tile, int N, int K, const int8_t* q, int M, int ldq, int k_off, float* acc, int acc_ld,
                        cudaStream_t s, bool pdl) {
     gemm_tc_init_attrs();
-    if (!g_tc_attr || !g_encode) { set_error("gemm_tc: tcgen05 path unavailable (driver entry point / smem attribute)"); return WF_ERR_CUDA; }
+    if (!g_encode) { set_error("gemm_tc: tcgen05 path unavailable (driver entry point / smem attribute)"); return WF_ERR_CUDA; }
     if (M < 1 || M > TC_BN || K % WF_QK || k_off % WF_QK || ldq % 16 || acc_ld % 4 || N % 8) { set_error("gemm_tc_red: unsupported shape"); return WF_ERR_UNSUPPORTED; }
     constexpr int NU = 3;
     CUtensorMap tmap;
@@ -599,7 +599,7 @@ int launch_gemm_tc_red(const uint8_t* w_tile, int N, int K, const int8_t* q, int
 
 int launch_gemm_tc(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s) {
     gemm_tc_init_attrs();
-    if (!g_tc_attr || !g_encode) { set_error("gemm_tc: tcgen05 path unavailable (driver entry point / smem attribute)"); return WF_ERR_CUDA; }
+    if (!g_encode) { set_error("gemm_tc: tcgen05 path unavailable (driver entry point / smem attribute)"); return WF_ERR_CUDA; }
     if (g_tc_cluster == 2) return g_tc_nu == 2 ? launch_tc_cl<2, 2>(a, ep, s) : launch_tc_cl<2, 3>(a, ep, s);
     if (g_tc_nu == 1) return launch_tc_cl<1, 1>(a, ep, s);
     return g_tc_nu == 2 ? launch_tc_cl<1, 2>(a, ep, s) : launch_tc_cl<1, 3>(a, ep, s);

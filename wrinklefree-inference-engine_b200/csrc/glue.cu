@@ -300,6 +300,20 @@ int launch_fill_f32(float* out, size_t n, float value, cudaStream_t s) {
     fill_f32_kernel<<<sm_count() * 4, 256, 0, s>>>(out, n, value);
     return launch_check(cudaGetLastError(), "fill_f32");
 }
+// pseudo-random INTEGERS in [-amp, amp] held in fp32: a stand-in for a linear's raw accumulator (bench / timing set-up only)
+__global__ void fill_randint_f32_kernel(float* out, size_t n, uint64_t seed, int amp) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        uint64_t z = (i + 1) * 0x9E3779B97F4A7C15ull + seed;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        out[i] = (float)((int)(z % (uint64_t)(2 * amp + 1)) - amp);
+    }
+}
+int launch_fill_randint_f32(float* out, size_t n, uint64_t seed, int amp, cudaStream_t s) {
+    fill_randint_f32_kernel<<<sm_count() * 4, 256, 0, s>>>(out, n, seed, amp);
+    return launch_check(cudaGetLastError(), "fill_randint_f32");
+}
 int launch_fill_bf16(void* out, size_t n, uint64_t seed, float mean, float std, cudaStream_t s) {
     fill_bf16_kernel<<<sm_count() * 8, 256, 0, s>>>((__nv_bfloat16*)out, n, seed, mean, std);
     return launch_check(cudaGetLastError(), "fill_bf16");
@@ -313,10 +327,9 @@ static int launch_lm(const void* h, const void* E, int B, int V, int K, float* l
     constexpr int SM_EPI = MT * (LM_ROWS + 1) * 4;
     constexpr int SMEM = SM_PIPE > SM_EPI ? SM_PIPE : SM_EPI;
     auto kern = lm_head_kernel<NT>;
-    static bool attr = false;
-    if (!attr) {
+    static DevOnce attr;
+    if (attr.need()) {
         if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM), "lm smem")) return WF_ERR_CUDA;
-        attr = true;
     }
     dim3 grid(nparts, (B + MT - 1) / MT);
     kern<<<grid, 256, SMEM, s>>>((const __nv_bfloat16*)h, (const __nv_bfloat16*)E, B, V, K, logits_out, ldl, v_off, pv, pi);

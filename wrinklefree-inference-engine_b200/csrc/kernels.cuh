@@ -28,6 +28,7 @@ int launch_advance(int32_t* positions, int32_t* seq_lens, int32_t* tokens, const
 int launch_fill_ternary(void* out, size_t bytes, uint64_t seed, cudaStream_t s);
 int launch_fill_bf16(void* out, size_t n, uint64_t seed, float mean, float std, cudaStream_t s);
 int launch_fill_f32(float* out, size_t n, float value, cudaStream_t s);
+int launch_fill_randint_f32(float* out, size_t n, uint64_t seed, int amp, cudaStream_t s);
 int launch_lm_head_argmax(const void* h, const void* E, int B, int V, int K, float* logits_out, int32_t* next_out, void* workspace,
                           cudaStream_t s);
 }  // namespace wf

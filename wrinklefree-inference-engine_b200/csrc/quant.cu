@@ -207,11 +207,8 @@ namespace wf {
 int launch_rmsnorm_quant(const void* x, const void* gamma, float eps, int M, int K, void* y_out, int8_t* q, float* scale_out,
                          int32_t* rowsum_out, cudaStream_t s, bool pdl) {
     const size_t smem = (size_t)K * 2;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(rmsnorm_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
-        attr_set = true;
-    }
+    static DevOnce attr_set;
+    if (attr_set.need()) cudaFuncSetAttribute(rmsnorm_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(M);
     cfg.blockDim = dim3(QT);

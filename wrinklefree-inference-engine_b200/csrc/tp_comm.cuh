@@ -28,7 +28,17 @@ struct TpComm {
     size_t off_flags;              // byte offsets inside a comm buffer
     const int* step;               // local device counter: number of completed decode steps
     int* done_cnt;                 // local, zero-initialised: one grid-arrival counter per flag id
+    int* err;                      // local device word: set non-zero when a bounded spin gave up (checked by the host at every sync)
 };
+
+// Every device-side spin in this library is bounded: a peer that died, or ranks whose step counters disagree, must become an
+// error code on the host, not a hung GPU.  The budget is generous (seconds) against waits that are microseconds when healthy.
+constexpr unsigned long long WF_SPIN_BUDGET_NS = 4000000000ull;
+__device__ __forceinline__ unsigned long long spin_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 __device__ __forceinline__ int* tp_flag_ptr(const TpComm& c, int dst_rank, int id, int src_rank) {
     return reinterpret_cast<int*>(c.peer[dst_rank] + c.off_flags) + id * TP_MAX + src_rank;
@@ -63,8 +73,11 @@ __device__ __forceinline__ void tp_signal_grid_done(const TpComm& c, int id, int
             if (last) { c.done_cnt[id] = 0; __threadfence(); }   // self-cleaning; acquire the other CTAs' arrivals (their fence + atomic)
         }
         last = __shfl_sync(0xffffffffu, last, 0);
+        __syncwarp();                // bar.warp.sync orders memory among the lanes (shfl alone does not): lane 0's acquire of the
+                                     // other CTAs' arrivals happens-before the release stores of lanes 1..T-1
         if (last && lane < c.size) {
-            // one lane per peer: the T release stores (each a fence + an NVLink round trip) go out side by side, not in sequence
+            // one lane per peer: the T release stores (each a fence + an NVLink round trip) go out side by side, not in sequence;
+            // st.release.sys is cumulative over everything ordered before it in this lane, i.e. (through the warp barrier) lane 0's acquire
             const int val = ld_relaxed_gpu(c.step) + 1;
             st_release_sys(tp_flag_ptr(c, lane, id, c.rank), val);
         }
@@ -79,7 +92,16 @@ __device__ __forceinline__ void tp_wait_flags_warp(const TpComm& c, int id) {
     const int want = ld_relaxed_gpu(c.step) + 1;
     if (lane < c.size) {
         const int* f = tp_flag_ptr(c, c.rank, id, lane);
-        while (ld_acquire_sys(f) < want) { __nanosleep(20); }
+        if (ld_acquire_sys(f) < want) {
+            const unsigned long long t0 = spin_now();
+            while (ld_acquire_sys(f) < want) {
+                __nanosleep(20);
+                if (spin_now() - t0 > WF_SPIN_BUDGET_NS) {   // peer dead / step counters out of sync: report, do not hang
+                    if (c.err) atomicExch(c.err, 1000 + id);
+                    break;
+                }
+            }
+        }
     }
     __syncwarp();                    // ld.acquire.sys + the caller's CTA barrier order everything that follows after the peers' writes
 }

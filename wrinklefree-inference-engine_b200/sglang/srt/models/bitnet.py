@@ -33,7 +33,9 @@ def _dev(t: torch.Tensor) -> torch.Tensor:
 
 
 def _pack_ternary_weights(weight: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
-    """Ternary {-1,0,+1} (or unnormalised float: scale = mean|w|, round(w/scale) clamped) -> blocked I2_S + scale[1]."""
+    """Ternary {-1,0,+1} float -> blocked I2_S u8 [N, K/4] + scale[1] (= max|w|, 1.0 for a ternary tensor), the arithmetic of
+    quantize_i2_s (extern/BitNet/src/ggml-bitnet-mad.cpp:46-92) / _pack_ternary_weights (tests/test_bitnet_core.py:56-106):
+    code = round(w) clamped to {-1,0,+1}, + 1.  It packs; it does not quantise master weights."""
     packed, scale = _ops().pack_ternary(_dev(weight.detach()))
     return packed.to(weight.device), scale.to(weight.device)
 

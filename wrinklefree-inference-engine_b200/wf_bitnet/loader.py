@@ -57,7 +57,13 @@ def _i2s_and_scale(sd: Dict[str, torch.Tensor], base: str, N: int, K: int):
         else:                                                     # ternary float [N, K]
             if tuple(w.shape) != (N, K):
                 raise ValueError(f"{base}.weight: expected [{N}, {K}], got {tuple(w.shape)}")
-            packed, s = ops.pack_ternary(w.to("cuda").float())
+            wd = w.to("cuda").float()
+            # the reference converter only packs tensors that ARE ternary (_is_ternary_float, cache/bitnet_converter.py:80-103);
+            # a bf16 master-weight checkpoint would otherwise be clipped to {-1,0,+1} silently and decode garbage
+            if not bool(((wd == -1) | (wd == 0) | (wd == 1)).all().item()):
+                raise ValueError(f"{base}.weight: float tensor is not ternary {{-1, 0, +1}} — quantise the checkpoint first "
+                                 f"(this loader packs, it does not quantise; see cache/bitnet_converter.py:80-103)")
+            packed, s = ops.pack_ternary(wd)
             if scale_t is None:
                 scale_t = s
     if scale_t is None:

@@ -6,14 +6,20 @@ Storage is the paged pool of the CUDA library ([page][layer][K|V][head][slot][D]
 config — the reference declares `page_size=16` but never uses it); a sequence owns pages 0..n in order.
 `attention_with_kv_cache` = append + split-KV flash-decode kernel (wf_paged_decode_attn).
 
-Supported cache dtypes: BF16 and INT8 (attention + update/get), FP32 (update/get only).
-INT8 uses the reference's arithmetic (kv_cache.py:198-228: scale = 127/absmax, round, clamp +-127, dequantise to bf16)
-with one scale per (token, head) row.  The reference keeps ONE scale per layer, re-derived from the most recent update()
-call and applied by get() to everything already cached - with token-by-token decode that rescales old entries by the
-newest token's absmax; a row-wise scale is what that code does when it is handed one row, without the defect
-(tests/golden/kv_int8.npz pins the row arithmetic to the reference's own KVCache).  `k_scales` / `v_scales` are kept for
-API compatibility and hold the scale of the most recent row.  The "FP8" modes (int8 storage with a per-update scale,
-kv_cache.py:150-196) raise NotImplementedError.
+Every cache dtype of the reference is supported:
+  BF16               paged bf16 pool, attention straight from the pool.
+  INT8 (the reference's default, kv_cache.py:56), FP8_E4M3, FP8_E5M2
+                     paged int8 pool, attention straight from the pool.  The reference's two "FP8" modes are int8 storage with
+                     an absmax / 127 scale (kv_cache.py:150-196) — the same arithmetic as INT8 (:198-228); tests/golden/kv_modes.npz,
+                     written by the reference's own class, shows identical codes, scales and dequantised rows for all three.
+  FP16, FP32         16- / 32-bit paged pool (update / get are exact copies); attention casts the cached rows to bf16 into a
+                     scratch pool first (the reference casts them to the query dtype, :344-346) — O(context) per call, kept for
+                     API completeness, not a fast path.
+INT8 / FP8 use the reference's arithmetic (scale = 127/absmax, round, clamp +-127, dequantise to bf16) with one scale per
+(token, head) row.  The reference keeps ONE scale per layer, re-derived from the most recent update() call and applied by get()
+to everything already cached - with token-by-token decode that rescales old entries by the newest token's absmax; a row-wise
+scale is what that code does when it is handed one row, without the defect (tests/golden/kv_int8.npz pins the row arithmetic to
+the reference's own KVCache).  `k_scales` / `v_scales` are kept for API compatibility and hold the scale of the most recent row.
 """
 from __future__ import annotations
 
@@ -40,7 +46,7 @@ class KVCacheConfig:
     num_layers: int = 32
     num_heads: int = 32
     head_dim: int = 128
-    dtype: KVCacheDtype = KVCacheDtype.BF16
+    dtype: KVCacheDtype = KVCacheDtype.INT8   # the reference's default (kv_cache.py:56-57)
     page_size: int = 16
 
     @property
@@ -75,22 +81,28 @@ class KVCache:
         from wf_bitnet import ops
         self.config = config
         self.current_seq_len = 0
+        self._q8 = config.dtype in (KVCacheDtype.INT8, KVCacheDtype.FP8_E4M3, KVCacheDtype.FP8_E5M2)
         if config.dtype == KVCacheDtype.BF16:
             self.storage_dtype = torch.bfloat16
+        elif config.dtype == KVCacheDtype.FP16:
+            self.storage_dtype = torch.float16
         elif config.dtype == KVCacheDtype.FP32:
             self.storage_dtype = torch.float32
-        elif config.dtype == KVCacheDtype.INT8:
+        elif self._q8:
             self.storage_dtype = torch.bfloat16     # dtype of the rows handed to / returned by the int8 pool
         else:
-            raise NotImplementedError(f"KV cache dtype {config.dtype.value} is not implemented on the GPU path yet")
+            raise ValueError(f"unknown KV cache dtype {config.dtype!r}")
+        # fp16 rows travel through the 16-bit pool bit for bit (scatter / gather are copies)
+        self._pool_dtype = torch.int8 if self._q8 else (torch.bfloat16 if self.storage_dtype == torch.float16 else self.storage_dtype)
+        self._scratch = None
         ps = config.page_size
         if ps % 16 != 0:
             raise ValueError("page_size must be a multiple of 16")
         self.num_pages = (config.max_seq_len + ps - 1) // ps
         self.kv = ops.PagedKV(self.num_pages, config.num_layers, config.num_heads, ps, config.head_dim,
-                              dtype=torch.int8 if config.dtype == KVCacheDtype.INT8 else self.storage_dtype, device=device)
+                              dtype=self._pool_dtype, device=device)
         self.block_table = torch.arange(self.num_pages, dtype=torch.int32, device=device).reshape(1, -1)
-        sdev = device if config.dtype == KVCacheDtype.INT8 else "cpu"
+        sdev = device if self._q8 else "cpu"
         self.k_scales = torch.ones(config.num_layers, dtype=torch.float32, device=sdev)
         self.v_scales = torch.ones(config.num_layers, dtype=torch.float32, device=sdev)
 
@@ -111,9 +123,11 @@ class KVCache:
         dev = self.kv.pool.device
         k = key.to(dev, self.storage_dtype).reshape(new_tokens, -1)
         v = value.to(dev, self.storage_dtype).reshape(new_tokens, -1)
+        if self.storage_dtype == torch.float16:
+            k, v = k.view(torch.bfloat16), v.view(torch.bfloat16)
         pages, slots = self._pages_slots(seq_pos, new_tokens)
         ops.kv_scatter(self.kv, k, v, pages, slots, layer_idx)
-        if self.config.dtype == KVCacheDtype.INT8:
+        if self._q8:
             pg, sl, hh = (end_pos - 1) // self.config.page_size, (end_pos - 1) % self.config.page_size, self.config.num_heads - 1
             self.k_scales[layer_idx] = self.kv.scales[pg, layer_idx, 0, hh, sl]      # device-side copies, no sync
             self.v_scales[layer_idx] = self.kv.scales[pg, layer_idx, 1, hh, sl]
@@ -125,21 +139,24 @@ class KVCache:
         if end_pos is None:
             end_pos = self.current_seq_len
         c = self.config
-        k = torch.empty(end_pos, c.num_heads * c.head_dim, dtype=self.storage_dtype, device=self.kv.pool.device)
+        f16 = self.storage_dtype == torch.float16
+        k = torch.empty(end_pos, c.num_heads * c.head_dim, dtype=torch.bfloat16 if f16 else self.storage_dtype, device=self.kv.pool.device)
         v = torch.empty_like(k)
         if end_pos > 0:
             pages, slots = self._pages_slots(0, end_pos)
             ops.kv_gather(self.kv, k, v, pages, slots, layer_idx)
+        if f16:
+            k, v = k.view(torch.float16), v.view(torch.float16)
         return k.view(end_pos, c.num_heads, c.head_dim), v.view(end_pos, c.num_heads, c.head_dim)
 
     def clear(self) -> None:
-        (self.kv.raw if self.config.dtype == KVCacheDtype.INT8 else self.kv.pool).zero_()
+        (self.kv.raw if self._q8 else self.kv.pool).zero_()
         self.k_scales.fill_(1.0)
         self.v_scales.fill_(1.0)
         self.current_seq_len = 0
 
     def memory_usage_mb(self) -> float:
-        t = self.kv.raw if self.config.dtype == KVCacheDtype.INT8 else self.kv.pool
+        t = self.kv.raw if self._q8 else self.kv.pool
         return t.numel() * t.element_size() / (1024 * 1024)
 
 
@@ -147,8 +164,6 @@ def attention_with_kv_cache(query: torch.Tensor, kv_cache: KVCache, layer_idx: i
                             new_value: torch.Tensor, seq_pos: int, scale: Optional[float] = None) -> torch.Tensor:
     """query [1, H, 1, D]; new_key/new_value [1, 1, H, D] -> output [1, H, 1, D] (reference :316-369)."""
     from wf_bitnet import ops
-    if kv_cache.storage_dtype != torch.bfloat16:
-        raise NotImplementedError("attention_with_kv_cache runs on bf16 caches (KVCacheDtype.BF16)")
     if query.dim() != 4 or query.shape[0] != 1 or query.shape[2] != 1:
         raise ValueError("query must be [1, num_heads, 1, head_dim]")
     kv_cache.update(layer_idx, new_key, new_value, seq_pos)
@@ -157,7 +172,18 @@ def attention_with_kv_cache(query: torch.Tensor, kv_cache: KVCache, layer_idx: i
     dev = kv_cache.kv.pool.device
     q = query.to(dev, torch.bfloat16).reshape(1, query.shape[1], query.shape[3])
     seq_lens = torch.tensor([seq_pos + 1], dtype=torch.int32, device=dev)
-    out = ops.paged_decode_attn(q, kv_cache.kv, layer_idx, kv_cache.block_table, seq_lens, scale=scale,
+    kv, layer = kv_cache.kv, layer_idx
+    if kv_cache.storage_dtype != torch.bfloat16:
+        # FP16 / FP32 caches: the reference casts what get() returns to the query dtype (:344-346); here the rows are cast to
+        # bf16 into a one-layer scratch pool the attention kernel can stream.  O(context) per call — completeness, not speed.
+        c = kv_cache.config
+        if kv_cache._scratch is None:
+            kv_cache._scratch = ops.PagedKV(kv_cache.num_pages, 1, c.num_heads, c.page_size, c.head_dim, dtype=torch.bfloat16, device=dev)
+        k_all, v_all = kv_cache.get(layer_idx, seq_pos + 1)
+        pages, slots = kv_cache._pages_slots(0, seq_pos + 1)
+        ops.kv_scatter(kv_cache._scratch, k_all.to(torch.bfloat16).reshape(seq_pos + 1, -1), v_all.to(torch.bfloat16).reshape(seq_pos + 1, -1), pages, slots, 0)
+        kv, layer = kv_cache._scratch, 0
+    out = ops.paged_decode_attn(q, kv, layer, kv_cache.block_table, seq_lens, scale=scale,
                                 out_dtype=torch.bfloat16 if query.dtype == torch.bfloat16 else torch.float32)
     return out.to(query.dtype).reshape(1, query.shape[1], 1, query.shape[3])
 
