@@ -164,6 +164,157 @@ def run_gpu_tp(args):
     return 0
 
 
+# ------------------------------------------------------------------------------------------- tensor-parallel suite (aux.tp)
+def _tp_cfg(wl, K, W, **over):
+    from wf_bitnet.engine import EngineConfig
+    page = 16
+    extra = ((2 * (W + K) + 16 + page - 1) // page) * page + page
+    cfg = getattr(EngineConfig, wl["shape"])(max_seq=wl["ctx"] + extra, page_size=page, max_batch=wl["batch"])
+    for k, v in over.items():
+        setattr(cfg, k, v)
+    return cfg
+
+
+def _tp_time(cfg, wl, K, W, rank, world, dist):
+    """device-timed ms per decode step of one engine (TP = world when world > 1: max over ranks), CUDA-graph replay."""
+    from wf_bitnet import tp
+    from wf_bitnet.engine import Engine
+    eng = Engine(cfg, tp_rank=rank if world > 1 else 0, tp_size=world)
+    eng.init_synthetic(4321)
+    if world > 1:
+        tp.attach(eng)
+    for slot in range(wl["batch"]):
+        eng.set_context(slot, wl["ctx"], fill_random=True)
+    tokens = np.random.default_rng(0).integers(0, cfg.vocab, size=wl["batch"]).astype(np.int32)
+    ext = torch.cuda.ExternalStream(eng.stream)
+    eng.decode(tokens)
+    for _ in range(W):
+        eng.decode_device(wl["batch"])
+    eng.sync()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(ext)
+    for _ in range(K):
+        eng.decode_device(wl["batch"])
+    e1.record(ext)
+    e1.synchronize()
+    eng.sync()
+    ms = e0.elapsed_time(e1) / K
+    launches = eng.launches_per_step()
+    eng.close()
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+    return ms, launches
+
+
+def _tp_parity(rank, world, dist):
+    """TP = world vs TP = 1 at the 8B LAYER shape (hidden 4096, 32/8 heads, ffn 14336; 2 layers, vocab 8192): every rank builds the
+    same seeded model and keeps its shard, rank 0 also runs the unsharded engine; the final normalised hidden state and the greedy
+    tokens must be BIT-identical at batch 1 (GEMV phases, all-reduce by RED) and batch 32 (batched phases, reduce-scatter + pull)."""
+    from wf_bitnet import tp
+    from wf_bitnet.engine import Engine, EngineConfig
+    from wf_bitnet.synth import make_weights
+    ok, detail = True, []
+    for batch, steps, ctx in ((1, 5, 40), (32, 4, 24)):
+        cfg = EngineConfig(hidden=4096, layers=2, heads=32, kv_heads=8, head_dim=128, ffn=14336, vocab=8192, max_seq=128, page_size=16, max_batch=batch)
+        weights = make_weights(cfg, seed=11 + batch)
+        eng = Engine(cfg, tp_rank=rank, tp_size=world)
+        eng.load_weights(tp.shard_weights(weights, rank, world))
+        tp.attach(eng)
+        ref = None
+        if rank == 0:
+            ref = Engine(cfg)
+            ref.load_weights(weights)
+        for e in ([eng, ref] if ref else [eng]):
+            for slot in range(batch):
+                e.set_context(slot, ctx + slot % 7, fill_random=False)
+        toks = np.random.default_rng(batch).integers(0, cfg.vocab, size=batch).astype(np.int32)
+        t_tp, t_ref = toks.copy(), toks.copy()
+        same = True
+        for _ in range(steps):
+            t_tp = eng.decode(t_tp)
+            if ref is not None:
+                t_ref = ref.decode(t_ref)
+                same = same and bool(torch.equal(eng.buffer("normed", (batch, cfg.hidden), torch.bfloat16), ref.buffer("normed", (batch, cfg.hidden), torch.bfloat16)))
+                same = same and bool(np.array_equal(t_tp, t_ref))
+        for _ in range(3):                       # the CUDA-graph replay path
+            eng.decode_device(batch)
+            if ref is not None:
+                ref.decode_device(batch)
+        eng.sync()
+        if ref is not None:
+            ref.sync()
+            same = same and bool(torch.equal(eng.buffer("next", (batch,), torch.int32), ref.buffer("next", (batch,), torch.int32)))
+            detail.append({"batch": batch, "steps": steps + 3, "bit_identical": same})
+        flag = torch.tensor([1 if same else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = ok and bool(flag.item())
+        eng.close()
+        if ref is not None:
+            ref.close()
+        dist.barrier()
+    return ok, detail
+
+
+def run_tp_suite(rank, world, dist, K, W, peak):
+    """BASELINE.json configs[3] / configs[4] in front of the driver: at N ranks, TP = N parity and timing of the
+    8B bs1 / 8B bs32 / 70B bs16 workloads; rank 0 additionally times the TP = 1 engine and a single-GPU stand-in for one rank's
+    shard (heads, KV heads, ffn and vocab divided by N: the rank's compute without the exchanges) on its own GPU, so every line
+    carries speedup_vs_tp1 and the exchange cost measured on the same box in the same run."""
+    out = {}
+    parity, parity_detail = None, None
+    if world > 1:
+        try:
+            parity, parity_detail = _tp_parity(rank, world, dist)
+        except Exception as ex:  # noqa: BLE001
+            parity, parity_detail = False, f"error: {ex}"
+    for name, wl in TP_WORKLOADS.items():
+        row = {"workload": wl["name"].replace("TP = n_gpus", f"TP = {world}")}
+        try:
+            cfg = _tp_cfg(wl, K, W)
+            hd, ffn, hid, L = cfg.head_dim, cfg.ffn, cfg.hidden, cfg.layers
+            w_bytes = L * ((cfg.heads + 2 * cfg.kv_heads) * hd * hid + hid * cfg.heads * hd + 3 * ffn * hid) // 4
+            kv_bytes = 2 * cfg.kv_heads * hd * 2 * L * wl["batch"] * (wl["ctx"] + 1)
+            per_gpu = (w_bytes + kv_bytes + cfg.vocab * hid * 2) / world
+            ms_tp = None
+            if world > 1:
+                ms_tp, launches = _tp_time(cfg, wl, K, W, rank, world, dist)
+            tp1 = shard = None
+            if rank == 0:
+                tp1, l1 = _tp_time(_tp_cfg(wl, K, W), wl, K, W, 0, 1, None)
+                if world > 1:
+                    v_slice = (((cfg.vocab + world - 1) // world) + 127) // 128 * 128
+                    shard, _ = _tp_time(_tp_cfg(wl, K, W, heads=cfg.heads // world, kv_heads=cfg.kv_heads // world, ffn=cfg.ffn // world, vocab=v_slice),
+                                        wl, K, W, 0, 1, None)
+            if world > 1:
+                dist.barrier()
+            if rank == 0:
+                ms = ms_tp if world > 1 else tp1
+                row.update({"tp": world, "ms_per_step": round(ms, 4), "tok_s": round(wl["batch"] / ms * 1e3, 1), "tp1_ms_per_step": round(tp1, 4),
+                            "speedup_vs_tp1": round(tp1 / ms, 3), "hbm_frac_per_gpu": round(per_gpu / (ms * 1e-3) / 1e9 / peak, 4),
+                            "algorithmic_bytes_per_gpu": int(per_gpu), "parity_bit_identical": parity})
+                if world > 1:
+                    row.update({"gpu_launches_per_step": launches, "shard_compute_ms": round(shard, 4), "exchanges_per_step": 4 * L + 1,
+                                "us_per_exchange": round((ms - shard) / (4 * L + 1) * 1e3, 2)})
+        except Exception as ex:  # noqa: BLE001
+            row["error"] = str(ex)[:300]
+            if world > 1:
+                try:
+                    dist.barrier()
+                except Exception:  # noqa: BLE001
+                    pass
+        out[name] = row
+    out["parity"] = {"bit_identical": parity, "shape": "8B layer shape (hidden 4096, 32/8 heads x 128, ffn 14336), 2 layers, vocab 8192; TP=N vs TP=1 on rank 0",
+                     "cases": parity_detail}
+    out["method"] = ("strong scaling: one model sharded over all N ranks (q|k|v, gate|up by output rows, o/down by input columns, KV by head); exchanges are NVLink peer "
+                     "stores / REDs fused into the producing kernels, no NCCL on the data path; device-timed CUDA-graph replay, max over ranks; "
+                     "us_per_exchange = (TP step - single-GPU stand-in for one rank's shard) / exchanges")
+    return out
+
+
 def measured_peaks():
     f = ROOT / "MEASURED_PEAKS.json"
     if f.exists():
@@ -240,47 +391,118 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------- CPU reference arm
-def cpu_reference_step(batch, ctx, threads, reps):
-    """One bounded sample of the reference CPU step: ONE of the 30 layers (7 ternary GEMMs through the
-    reference's AVX2 kernel + GQA decode attention over `ctx` tokens for every sequence, torch CPU as the
-    reference does) and the bf16 LM head.  Returns (seconds per full step extrapolated x30, description)."""
-    import torch.nn.functional as F
-    import oracle as O
-    use_ref = O.ref_available()
-    torch.set_num_threads(threads)
-    if use_ref:
-        O.ref().wfref_set_threads(threads)
-    rng = np.random.default_rng(1234)
-    H, HKV, D, HID, FFN, V = 20, 5, 128, 2560, 6912, 128256
-    shapes = {"q": (H * D, HID), "k": (HKV * D, HID), "v": (HKV * D, HID), "o": (HID, H * D), "gate": (FFN, HID), "up": (FFN, HID), "down": (HID, FFN)}
-    from wf_bitnet.synth import pack_i2s_numpy
-    packed = {n: pack_i2s_numpy(rng.integers(-1, 2, size=s, dtype=np.int8)) for n, s in shapes.items()}
-    acts = {K: rng.integers(-127, 128, size=(batch, K), dtype=np.int8) for K in (HID, FFN)}
-    kc = torch.randn(batch, HKV, ctx, D).to(torch.bfloat16)
-    vc = torch.randn(batch, HKV, ctx, D).to(torch.bfloat16)
-    q = torch.randn(batch, H, 1, D).to(torch.bfloat16)
-    E = (0.02 * torch.randn(V, HID)).to(torch.bfloat16)
-    hcpu = torch.randn(batch, HID).to(torch.bfloat16)
-    gemm = (lambda p, a: O.ref_gemm(p, a, 1.0)) if use_ref else (lambda p, a: O.gemm(p, a, 1.0))
+class CpuReferenceStep:
+    """The reference's CPU decode step at the BitNet-2B-4T shape, batched: a REAL 30-layer step (30 distinct sets of packed
+    weights, 7 ternary GEMMs per layer through the reference's unmodified AVX2 ggml_vec_dot_i2_i8_s under OpenMP, and the glue the
+    CPU path really executes with torch CPU ops as scripts/direct_inference_full.py does: RMSNorm x2, sub-norm x2, per-token int8
+    quantisation x4, Sigma-a correction + dequant, RoPE, GQA SDPA over the KV cache, relu^2*up, residual adds) + final norm + bf16
+    LM head + argmax.  The KV cache of a layer is 2 x batch x 5 x ctx x 128 bf16 (671 MB at batch 64 / 4K); two such buffers are
+    alternated over the 30 layers (each far larger than the host caches) instead of allocating 20 GB of random numbers."""
 
-    def layer():
-        for n, (N, K) in shapes.items():
-            gemm(packed[n], acts[K])
-        F.scaled_dot_product_attention(q, kc, vc, enable_gqa=True)
+    H, HKV, D, HID, FFN, V, L = 20, 5, 128, 2560, 6912, 128256, 30
 
-    layer()  # warm
-    t0 = time.perf_counter()
-    for _ in range(reps):
-        layer()
-    t_layer = (time.perf_counter() - t0) / reps
-    F.linear(hcpu, E)
-    t0 = time.perf_counter()
-    for _ in range(max(1, reps // 2)):
-        F.linear(hcpu, E)
-    t_lm = (time.perf_counter() - t0) / max(1, reps // 2)
-    desc = (f"1 of 30 layers (7 ternary GEMMs, batch {batch}, {'unmodified reference AVX2 ggml_vec_dot_i2_i8_s + OpenMP' if use_ref else 'scalar C oracle port'}; "
-            f"GQA SDPA over {ctx}-token KV for {batch} sequences, torch CPU) x30 + bf16 LM head, {reps} repetitions")
-    return t_layer * 30 + t_lm, desc, ("reference" if use_ref else "port")
+    def __init__(self, batch, ctx):
+        import oracle as O
+        from wf_bitnet.synth import pack_i2s_numpy
+        self.O = O
+        self.batch, self.ctx = batch, ctx
+        self.use_ref = O.ref_available()
+        rng = np.random.default_rng(1234)
+        shapes = {"q": (self.H * self.D, self.HID), "k": (self.HKV * self.D, self.HID), "v": (self.HKV * self.D, self.HID), "o": (self.HID, self.H * self.D),
+                  "gate": (self.FFN, self.HID), "up": (self.FFN, self.HID), "down": (self.HID, self.FFN)}
+        self.layers = []
+        for _ in range(self.L):
+            lw = {n: pack_i2s_numpy(rng.integers(-1, 2, size=s, dtype=np.int8)) for n, s in shapes.items()}
+            lw["scales"] = {n: float(rng.uniform(0.5, 2.5)) for n in shapes}
+            self.layers.append(lw)
+        g = torch.Generator().manual_seed(7)
+        self.gam = [(1.0 + 0.1 * torch.randn(n, generator=g)).to(torch.bfloat16) for n in (self.HID, self.H * self.D, self.HID, self.FFN)]
+        self.kv = [(torch.randn(batch, self.HKV, ctx + 1, self.D, generator=g).to(torch.bfloat16),
+                    torch.randn(batch, self.HKV, ctx + 1, self.D, generator=g).to(torch.bfloat16)) for _ in range(2)]
+        self.E = (0.02 * torch.randn(self.V, self.HID, generator=g)).to(torch.bfloat16)
+        self.tokens = torch.randint(0, self.V, (batch,), generator=g)
+        self.cos = torch.cos(torch.rand(self.D // 2, generator=g)).to(torch.bfloat16)
+        self.sin = torch.sin(torch.rand(self.D // 2, generator=g)).to(torch.bfloat16)
+
+    def describe(self):
+        k = "unmodified reference AVX2 ggml_vec_dot_i2_i8_s + OpenMP" if self.use_ref else "scalar C oracle port"
+        return (f"REAL 30-layer step, batch {self.batch}: 210 ternary GEMMs ({k}), per-token int8 quant / norms / RoPE / relu^2*up / residuals in torch CPU, "
+                f"GQA SDPA over {self.ctx}-token KV for {self.batch} sequences per layer, final norm + bf16 LM head + argmax")
+
+    def _lin(self, x, lw, name):
+        """direct_inference_full.py:186-208 for every row of x (bf16 [B, K]) -> bf16 [B, N]"""
+        O = self.O
+        q, s, rs = O.quantize_act_i8_rows(x.float().numpy())
+        sc = lw["scales"][name]
+        y = O.ref_gemm(lw[name], q, sc) if self.use_ref else O.gemm(lw[name], q, sc)
+        out = (torch.from_numpy(y) - sc * torch.from_numpy(rs.astype(np.float32))[:, None]) * torch.from_numpy(s)[:, None]
+        return out.to(torch.bfloat16)
+
+    @staticmethod
+    def _norm(x, w, eps=1e-5):
+        var = x.float().pow(2).mean(-1, keepdim=True)
+        return (x * torch.rsqrt(var + eps).to(x.dtype)) * w
+
+    def _rope(self, x):
+        half = self.D // 2
+        x1, x2 = x[..., :half], x[..., half:]
+        return torch.cat([x1 * self.cos - x2 * self.sin, x1 * self.sin + x2 * self.cos], dim=-1)
+
+    def step(self, threads):
+        import torch.nn.functional as F
+        torch.set_num_threads(threads)
+        if self.use_ref:
+            self.O.ref().wfref_set_threads(threads)
+        B = self.batch
+        h = self.E[self.tokens]
+        for li, lw in enumerate(self.layers):
+            kc, vc = self.kv[li & 1]
+            n = self._norm(h, self.gam[0])
+            q = self._rope(self._lin(n, lw, "q").view(B, self.H, self.D))
+            k = self._rope(self._lin(n, lw, "k").view(B, self.HKV, self.D))
+            v = self._lin(n, lw, "v").view(B, self.HKV, self.D)
+            kc[:, :, self.ctx] = k
+            vc[:, :, self.ctx] = v
+            a = F.scaled_dot_product_attention(q.unsqueeze(2), kc, vc, enable_gqa=True).reshape(B, self.H * self.D)
+            h = h + self._lin(self._norm(a, self.gam[1]), lw, "o")
+            n = self._norm(h, self.gam[2])
+            act = torch.relu(self._lin(n, lw, "gate")).square() * self._lin(n, lw, "up")
+            h = h + self._lin(self._norm(act, self.gam[3]), lw, "down")
+        logits = F.linear(self._norm(h, self.gam[0]), self.E)
+        self.tokens = logits.argmax(-1)
+
+    def timed(self, threads, reps, pin8=False):
+        old_aff = None
+        if pin8 and hasattr(os, "sched_setaffinity"):
+            try:
+                old_aff = os.sched_getaffinity(0)
+                os.sched_setaffinity(0, set(sorted(old_aff)[:8]))      # the reference's operating point: taskset -c 0-7 (launch_sglang_bitnet.sh:61)
+            except OSError:
+                old_aff = None
+        try:
+            self.step(threads)                                         # warm
+            ts = []
+            for _ in range(reps):
+                t0 = time.perf_counter()
+                self.step(threads)
+                ts.append(time.perf_counter() - t0)
+        finally:
+            if old_aff is not None:
+                os.sched_setaffinity(0, old_aff)
+        return statistics.median(ts)
+
+
+def cpu_baseline_block(batch, ctx, reps):
+    cores = os.cpu_count() or 1
+    ref = CpuReferenceStep(batch, ctx)
+    t_all = ref.timed(cores, reps)
+    out = {"value": batch / t_all, "unit": "tok/s", "cores": cores, "kind": "reference" if ref.use_ref else "port",
+           "sample": f"{ref.describe()}; median of {reps} steps after 1 warm-up", "ms_per_step": t_all * 1e3}
+    if cores > 8:
+        t8 = ref.timed(8, max(1, reps - 1), pin8=True)
+        out["threads8"] = {"value": batch / t8, "unit": "tok/s", "cores": 8, "ms_per_step": t8 * 1e3,
+                           "note": "the reference's operating point: 8 threads pinned to 8 cores (scripts/launch_sglang_bitnet.sh:61 taskset -c 0-7)"}
+    return out, t_all
 
 
 def run_reference(args):
@@ -288,22 +510,15 @@ def run_reference(args):
     if rank != 0:
         return 0
     batch, ctx = (64, 4096) if args.workload == "bs64" else (1, 512)
-    cores = os.cpu_count() or 1
-    times = []
-    desc = kind = None
-    for _ in range(args.warmup):
-        cpu_reference_step(batch, ctx, cores, 1)
-        break   # one warm-up sample is enough on the CPU; keeps the arm within minutes
-    for _ in range(max(1, min(args.steps, 5))):
-        t, desc, kind = cpu_reference_step(batch, ctx, cores, 1)
-        times.append(t)
-    t_step = statistics.median(times)
+    reps = max(1, min(args.steps, 5))
+    cb, t_step = cpu_baseline_block(batch, ctx, reps)
     val = batch / t_step
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "tok/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t_step * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "i8 x i2 -> i32, bf16 glue",
-        "data": "synthetic", "config": {"workload": workload_name(args.workload), "batch": batch, "ctx": ctx},
-        "cpu_baseline": {"value": val, "unit": "tok/s", "cores": cores, "kind": kind, "sample": desc},
+        "data": "synthetic", "config": {"workload": workload_name(args.workload), "batch": batch, "batch_per_gpu": batch, "ctx": ctx,
+                                        "note": "one host, all cores: under torchrun only rank 0 runs this arm, the figure does not scale with n_gpus"},
+        "cpu_baseline": cb,
         "e2e": {"value": val, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
@@ -500,9 +715,26 @@ def run_gpu(args):
     # ---------------- CPU baseline beside it (rank 0, N = 1 only; bounded sample)
     cpu_baseline = None
     if world == 1 and not args.no_cpu:
-        cores = os.cpu_count() or 1
-        t_step, desc, kind = cpu_reference_step(batch, ctx, cores, 2)
-        cpu_baseline = {"value": batch / t_step, "unit": "tok/s", "cores": cores, "kind": kind, "sample": desc}
+        cpu_baseline, _ = cpu_baseline_block(batch, ctx, 2)
+
+    # ---------------- BASELINE configs[2]: prefill 8 x 2048 tokens through the tcgen05 int8 ternary GEMM (N = 1 only)
+    if args.workload == "bs64" and world == 1 and not args.no_aux:
+        try:
+            sys.path.insert(0, str(ROOT / "tools"))
+            import bench_prefill
+            aux["prefill"] = bench_prefill.measure(16384, 8, 3, "2b")
+            aux["prefill"]["workload"] = "BASELINE.json configs[2]: BitNet-2B-4T-shaped prefill, 8 x 2048-token prompts, the 4 fused ternary linears of a layer at M = 16384"
+        except Exception as ex:  # noqa: BLE001
+            aux["prefill"] = {"error": str(ex)[:300]}
+
+    # ---------------- BASELINE configs[3] / [4]: tensor-parallel 8B / 70B-shaped decode at TP = N (every N, incl. the TP = 1 lines at N = 1)
+    if args.workload == "bs64" and not args.no_aux and not args.no_tp:
+        try:
+            tp_aux = run_tp_suite(rank, world, dist, 20, 3, peak)
+            if rank == 0:
+                aux["tp"] = tp_aux
+        except Exception as ex:  # noqa: BLE001
+            aux["tp"] = {"error": str(ex)[:300]}
 
     # ---------------- max over ranks
     t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device="cuda")
@@ -514,7 +746,7 @@ def run_gpu(args):
             "metric": METRIC, "value": world * batch * K / (ms_total * 1e-3), "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "i8 x i2 -> i32, bf16 glue", "data": "synthetic",
-            "config": {"workload": workload_name(args.workload), "batch_per_gpu": batch, "ctx": ctx, "page_size": page,
+            "config": {"workload": workload_name(args.workload), "batch": batch, "batch_per_gpu": batch, "ctx": ctx, "page_size": page,
                        "l2": "inputs larger than L2: every step streams 521 MB of ternary weights, 657 MB of LM head and the KV cache (20 GB at bs64)",
                        "multi_gpu": "replicas only (2B: 5 KV heads do not shard); no data-path collective", "graph": "CUDA graph replay, 1 graph launch per step"},
             "clocks": clocks,
@@ -542,6 +774,7 @@ def main():
     ap.add_argument("--workload", default="bs64", choices=["bs64", "bs1"] + sorted(TP_WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-aux", action="store_true", help="skip the batch-1 aux measurement")
+    ap.add_argument("--no-tp", action="store_true", help="skip the tensor-parallel suite (aux.tp)")
     args = ap.parse_args()
     if args.workload in TP_WORKLOADS:
         if args.impl == "reference":

@@ -28,6 +28,60 @@ def timed(fn, iters, warm=3):
     return e0.elapsed_time(e1) / iters
 
 
+def measure(tokens=16384, iters=10, algo=3, shape="2b", only="", layout="tile"):
+    """-> dict: per-linear and per-layer int8 TOP/s of the ternary GEMM at M = tokens, next to torch._int_mm (cuBLASLt) 8192^3 on the same GPU."""
+    from wf_bitnet import _lib, ops
+    _lib.require_gpu()
+    M = tokens
+    hid, ffn, qkv = (2560, 6912, 3840) if shape == "2b" else (4096, 14336, 6144)
+    shapes = {"qkv": (qkv, hid), "o": (hid, hid), "gate_up": (2 * ffn, hid), "down": (hid, ffn)}
+    g = torch.Generator(device="cuda").manual_seed(0)
+    out = {"tokens": M, "shape": shape, "algo": algo, "kernel": "ternary_gemm_tc_kernel (tcgen05 kind::i8)" if algo == 3 else f"algo {algo}"}
+    total_ms, total_ops = 0.0, 0.0
+    for name, (n, k) in shapes.items():
+        if only and name != only:
+            continue
+        tile = torch.randint(0, 256, (ops.tile_bytes(n, k),), generator=g, device="cuda", dtype=torch.uint8)
+        if layout == "i2s":
+            tile = tile[: n * k // 4].reshape(n, k // 4).contiguous()
+        q = torch.randint(-127, 128, (M, k), generator=g, device="cuda", dtype=torch.int8)
+        rs = q.sum(1, dtype=torch.int32)
+        sc = torch.rand(M, generator=g, device="cuda") * 0.05 + 0.01
+        ws = torch.tensor([1.7], device="cuda")
+        fn = lambda: ops.ternary_linear(tile, n, k, q, mode="linear", rowsum=rs, act_scale=sc, w_scale=ws, out_dtype=torch.bfloat16, algo=algo, layout=layout)  # noqa: E731
+        ms = timed(fn, iters)
+        opsn = 2.0 * M * n * k
+        out[name] = {"N": n, "K": k, "ms": round(ms, 4), "TOPs": round(opsn / ms / 1e9, 1)}
+        total_ms += ms
+        total_ops += opsn
+        del tile, q
+    out["layer_ms"] = round(total_ms, 4)
+    out["layer_TOPs"] = round(total_ops / total_ms / 1e9, 1)
+    out["prefill_30_layers_ms"] = round(30 * total_ms, 2)
+    out["prefill_tok_s_linears_only"] = round(M / (30 * total_ms * 1e-3), 0)
+    if only:
+        return out
+    a = torch.randint(-127, 128, (8192, 8192), device="cuda", dtype=torch.int8)
+    b = torch.randint(-127, 128, (8192, 8192), device="cuda", dtype=torch.int8).t()
+    try:
+        ms = timed(lambda: torch._int_mm(a, b), 10)
+        out["int8_peak_TOPs_cublaslt_8192"] = round(2 * 8192.0 ** 3 / ms / 1e9, 1)
+        out["frac_of_int8_peak"] = round(out["layer_TOPs"] / out["int8_peak_TOPs_cublaslt_8192"], 4)
+        # the same contraction shapes through the library (int8 x int8 -> int32, no unpack, no epilogue): what "matching cuBLASLt" means here
+        lib_ms = 0.0
+        for name, (n, k) in shapes.items():
+            x = torch.randint(-127, 128, (M, k), device="cuda", dtype=torch.int8)
+            w = torch.randint(-1, 2, (n, k), device="cuda", dtype=torch.int8).t()
+            lib_ms += timed(lambda: torch._int_mm(x, w), 5)
+            del x, w
+        out["cublaslt_same_shapes_layer_ms"] = round(lib_ms, 4)
+        out["cublaslt_same_shapes_layer_TOPs"] = round(total_ops / lib_ms / 1e9, 1)
+        out["frac_of_cublaslt_same_shapes"] = round(lib_ms / total_ms, 4)
+    except Exception as ex:  # noqa: BLE001
+        out["int8_peak_error"] = str(ex)[:200]
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--tokens", type=int, default=16384)
@@ -37,47 +91,8 @@ def main():
     ap.add_argument("--only", default="", help="time just this linear (qkv|o|gate_up|down)")
     ap.add_argument("--layout", default="tile", choices=["tile", "i2s"])
     args = ap.parse_args()
-    from wf_bitnet import _lib, ops
-    _lib.require_gpu()
     torch.cuda.set_device(0)
-    M = args.tokens
-    hid, ffn, qkv = (2560, 6912, 3840) if args.shape == "2b" else (4096, 14336, 6144)
-    shapes = {"qkv": (qkv, hid), "o": (hid, hid), "gate_up": (2 * ffn, hid), "down": (hid, ffn)}
-    g = torch.Generator(device="cuda").manual_seed(0)
-    out = {"tokens": M, "shape": args.shape, "algo": args.algo}
-    total_ms, total_ops = 0.0, 0.0
-    for name, (n, k) in shapes.items():
-        if args.only and name != args.only:
-            continue
-        tile = torch.randint(0, 256, (ops.tile_bytes(n, k),), generator=g, device="cuda", dtype=torch.uint8)
-        if args.layout == "i2s":
-            tile = tile[: n * k // 4].reshape(n, k // 4).contiguous()
-        q = torch.randint(-127, 128, (M, k), generator=g, device="cuda", dtype=torch.int8)
-        rs = q.sum(1, dtype=torch.int32)
-        sc = torch.rand(M, generator=g, device="cuda") * 0.05 + 0.01
-        ws = torch.tensor([1.7], device="cuda")
-        fn = lambda: ops.ternary_linear(tile, n, k, q, mode="linear", rowsum=rs, act_scale=sc, w_scale=ws, out_dtype=torch.bfloat16, algo=args.algo, layout=args.layout)  # noqa: E731
-        ms = timed(fn, args.iters)
-        opsn = 2.0 * M * n * k
-        out[name] = {"N": n, "K": k, "ms": round(ms, 4), "TOPs": round(opsn / ms / 1e9, 1)}
-        total_ms += ms
-        total_ops += opsn
-    out["layer_ms"] = round(total_ms, 4)
-    out["layer_TOPs"] = round(total_ops / total_ms / 1e9, 1)
-    out["prefill_30_layers_ms"] = round(30 * total_ms, 2)
-    out["prefill_tok_s_linears_only"] = round(M / (30 * total_ms * 1e-3), 0)
-    if args.only:
-        print(json.dumps(out))
-        return
-    a = torch.randint(-127, 128, (8192, 8192), device="cuda", dtype=torch.int8)
-    b = torch.randint(-127, 128, (8192, 8192), device="cuda", dtype=torch.int8).t()
-    try:
-        ms = timed(lambda: torch._int_mm(a, b), 10)
-        out["int8_peak_TOPs_cublaslt_8192"] = round(2 * 8192.0 ** 3 / ms / 1e9, 1)
-        out["frac_of_int8_peak"] = round(out["layer_TOPs"] / out["int8_peak_TOPs_cublaslt_8192"], 4)
-    except Exception as ex:  # noqa: BLE001
-        out["int8_peak_error"] = str(ex)[:200]
-    print(json.dumps(out))
+    print(json.dumps(measure(args.tokens, args.iters, args.algo, args.shape, args.only, args.layout)))
 
 
 if __name__ == "__main__":
