@@ -81,9 +81,12 @@ def test_gemv_70b_shapes(nk):
         qf = q.astype(np.float64).T
         for r0 in range(0, n, 4096):
             want[:, r0:r0 + 4096] = np.rint((w[r0:r0 + 4096].astype(np.float64) + 1.0) @ qf).astype(np.int64).astype(np.int32).T
-        for _ in range(2):   # twice: the self-cleaning split-K workspace must be left zero
-            got = ops.ternary_linear(tile, n, k, cu(q), mode="i32_plus1", algo=1).cpu().numpy()
-            assert np.array_equal(got, want), (nk, m)
+        # algo 0 = the library's own choice: the streamed GEMV wherever the int8 rows fit in shared memory next to the weight ring,
+        # the tiled GEMM for 8 rows of 28672 (they do not)
+        for algo in ((0, 1) if m * k <= 4 * 28672 else (0,)):
+            for _ in range(2):   # twice: the self-cleaning split-K workspace must be left zero
+                got = ops.ternary_linear(tile, n, k, cu(q), mode="i32_plus1", algo=algo).cpu().numpy()
+                assert np.array_equal(got, want), (nk, m, algo)
 
 
 def test_gemv_large_relu2_epilogue():
@@ -183,12 +186,14 @@ def test_linear_mode_within_1e3(nk, m):
     got = ops.ternary_linear(tile, n, k, cu(q), mode="linear", rowsum=cu(rs), act_scale=cu(s),
                              w_scale=torch.tensor([ws], device="cuda"), out_dtype=torch.float32).cpu().numpy()
     rel = np.linalg.norm(got - want) / np.linalg.norm(want)
-    assert rel <= 1e-3, rel
-    assert rel <= 1e-5, rel            # in practice: fp32 rounding only
+    assert rel <= 1e-3, rel            # the north-star bar
+    # the epilogue follows the reference's own rounding sequence fl32(fl32(fl32(S*s_w) - fl32(s_w*sum a)) * s_a), so the fp32
+    # values are in fact IDENTICAL to the CPU path's, not merely close
+    assert np.array_equal(got, want), np.abs(got - want).max()
     gb = ops.ternary_linear(tile, n, k, cu(q), mode="linear", rowsum=cu(rs), act_scale=cu(s),
                             w_scale=torch.tensor([ws], device="cuda"), out_dtype=torch.bfloat16).float().cpu().numpy()
     wb = torch.from_numpy(want).to(torch.bfloat16).float().numpy()
-    assert np.mean(gb != wb) < 0.01 and np.allclose(gb, wb, rtol=1e-2, atol=1e-3)
+    assert np.array_equal(gb, wb)
     # and against the float matmul on the unquantised input (reference tests ask cos > 0.99)
     full = ws * (x @ w.T)
     cos = (got * full).sum() / (np.linalg.norm(got) * np.linalg.norm(full))

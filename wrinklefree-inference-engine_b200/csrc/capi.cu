@@ -118,7 +118,7 @@ extern "C" int wf_ternary_linear(const wf_linear_args* a, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
     int algo = a->algo;
     if (algo == 0) {
-        if (a->M <= 8 && a->w_layout == WF_W_TILE && a->workspace) algo = 1;
+        if (a->M <= 8 && a->w_layout == WF_W_TILE && a->workspace && gemv_stream_fits(a->M, a->K)) algo = 1;   // else (70B down at M = 8: 8 x 28672 int8 rows) the tiled GEMM
         else if (a->M >= 128) algo = 3;   // a real dense contraction: tcgen05 int8
         else algo = 2;
     }

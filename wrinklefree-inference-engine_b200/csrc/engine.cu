@@ -143,7 +143,7 @@ int linear(wf_engine* e, const uint8_t* w, int N, int K, int B, const float* w_s
     int rc = fill_epi(&a, &ep);
     if (rc) return rc;
     int algo = e->linear_algo;
-    if (algo == 0) algo = (B <= 8) ? 1 : 2;
+    if (algo == 0) algo = (B <= 8 && gemv_stream_fits(B, K)) ? 1 : 2;
     if (algo == 1 && B <= 8) return launch_gemv_stream(&a, ep, e->stream, e->pdl);
     if (algo == 3) return launch_gemm_tc(&a, ep, e->stream);
     return launch_gemm_mma(&a, ep, e->stream);

@@ -83,9 +83,10 @@ __device__ __forceinline__ float ldcg_f(const float* p) {
     asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p));
     return r;
 }
-// exact: |S| < 2^24
+// exact: |S| < 2^24.  The reference's rounding sequence (scripts/direct_inference_full.py:202-206; see linear_value in
+// linear_common.cuh): fl32( fl32( fl32(S*s_w) - fl32(s_w*Sigma a) ) * s_a ) — bit-identical to the CPU path's fp32 value.
 __device__ __forceinline__ float lin_value(float S, int rowsum, float ws, float sa) {
-    return ((float)((int)S - rowsum) * ws) * sa;
+    return __fmul_rn(__fsub_rn(__fmul_rn(S, ws), __fmul_rn(ws, (float)rowsum)), sa);
 }
 __device__ __forceinline__ void red_add_f32(float* p, float v) {
     asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");

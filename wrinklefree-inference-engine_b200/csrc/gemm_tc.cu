@@ -391,7 +391,8 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
                             const float sa = p.ep.act_scale[p.ep.act_scale_per_token ? m : 0];
                             float y[8];
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) y[e] = ((float)(S[e] - rs) * ws8[e]) * sa;
+                            for (int e = 0; e < 8; ++e)   // the reference's rounding sequence (linear_value in linear_common.cuh)
+                                y[e] = __fmul_rn(__fsub_rn(__fmul_rn((float)S[e], ws8[e]), __fmul_rn(ws8[e], (float)rs)), sa);
                             if (relu2) {
                                 const int4 ua = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + (oct + 2) * 32);
                                 const int4 ub = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + (oct + 2) * 32 + 16);
@@ -399,7 +400,7 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
 #pragma unroll
                                 for (int e = 0; e < 8; ++e) {
                                     const float g = bf16_round(y[e]);
-                                    const float u = bf16_round(((float)(U[e] - rs) * wsu) * sa);
+                                    const float u = bf16_round(__fmul_rn(__fsub_rn(__fmul_rn((float)U[e], wsu), __fmul_rn(wsu, (float)rs)), sa));
                                     const float t = fmaxf(g, 0.f);
                                     y[e] = bf16_round(bf16_round(t * t) * u);
                                 }

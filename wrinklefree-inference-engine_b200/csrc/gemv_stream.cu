@@ -393,6 +393,13 @@ void gemv_stream_init_attrs() {
     if (ok) g_stream_attr_smem = 220 * 1024;
 }
 
+// the int8 activations of all M rows stay resident in shared memory next to the weight ring (>= 3 stages) and the accumulators
+bool gemv_stream_fits(int M, int K) {
+    if (M < 1 || M > 8) return false;
+    const size_t act_bytes = (((size_t)M * (K + 16) + 127) & ~(size_t)127);
+    return act_bytes + 3 * (size_t)SV_TPW * SV_CW * WF_TILE_BYTES + 24 * 1024 <= 220 * 1024;
+}
+
 int launch_gemv_stream(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s, bool pdl) {
     if (a->w_layout != WF_W_TILE) { set_error("gemv_stream: needs the b200_tile_v1 layout"); return WF_ERR_UNSUPPORTED; }
     if (a->M < 1 || a->M > 8) { set_error("gemv_stream: M=%d outside 1..8", a->M); return WF_ERR_UNSUPPORTED; }

@@ -35,9 +35,15 @@ __device__ __forceinline__ float seg_scale(const EpiParams& p, int n) {
 
 // value of the (dequantised) linear output for accumulator S (= sum (w+1) a) at (m, n)
 __device__ __forceinline__ float linear_value(const EpiParams& p, int m, float wscale, int S) {
-    const int d = S - p.rowsum[m];                                        // exact sum w*a
+    // the reference's own rounding sequence (scripts/direct_inference_full.py:202-206), so that the fp32 value — and the bf16 it is
+    // rounded to — is bit-identical to the CPU path, not merely within 1e-3:
+    //   out = bitnet_gemv(...)            -> fl32(S * s_w)            (float)sumi * scale, one rounding
+    //   out - scale * act_sum             -> fl32(out - fl32(s_w * Sigma a))   (the python-double product is exact, the scalar is cast to fp32)
+    //   (...) * act_scale                 -> fl32(... * s_a)
     const float sa = p.act_scale[p.act_scale_per_token ? m : 0];
-    return ((float)d * wscale) * sa;
+    const float y = __fmul_rn((float)S, wscale);
+    const float c = __fmul_rn(wscale, (float)p.rowsum[m]);
+    return __fmul_rn(__fsub_rn(y, c), sa);
 }
 
 // Non-fused modes and LINEAR without RELU2_MUL: one element.
@@ -87,6 +93,7 @@ int fill_epi(const wf_linear_args* a, EpiParams* p);  // validates + copies (hos
 // launchers implemented in the kernel files
 int launch_gemm_mma(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s);
 int launch_gemv_stream(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s, bool pdl);
+bool gemv_stream_fits(int M, int K);
 int launch_gemm_tc(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s);
 size_t gemm_mma_workspace_bytes(int M, int N, int K);
 
