@@ -101,11 +101,15 @@ class OracleModel:
         "<p>_proj": u8 I2_S [N,K/4], "<p>_scale": float  for p in q,k,v,o,gate,up,down } ]}
     """
 
-    def __init__(self, cfg: ModelConfig, weights: Dict, use_ref: bool = True, kv_int8: bool = False):
+    def __init__(self, cfg: ModelConfig, weights: Dict, use_ref: bool = True, kv_int8: bool = False, attn_fp32: bool = False):
         self.cfg = cfg
         self.w = weights
         self.use_ref = use_ref
         self.kv_int8 = kv_int8   # KVCacheDtype.INT8: what the cache returns is dequant(quant(x)), see kv_int8_roundtrip
+        # attn_fp32: the same attention evaluated in exact fp32 math and rounded to bf16 once, instead of torch's bf16 SDPA kernel.
+        # Both are "the reference within bf16 tolerance"; running one against the other measures how far a bf16-level change of
+        # the attention arithmetic moves the logits / greedy tokens of a deep random-init model (test sensitivity budget).
+        self.attn_fp32 = attn_fp32
         self.taps: Dict = {}     # ("q"|"k"|"v"|"attn", layer) of the last forward: q, k (after RoPE) / v before the cache, attention output
         self.rope = RotaryEmbedding(cfg.head_dim, cfg.max_seq, cfg.rope_theta)
         self.k_cache = torch.zeros(cfg.layers, cfg.max_seq, cfg.kv_heads, cfg.head_dim, dtype=torch.bfloat16)
@@ -131,8 +135,11 @@ class OracleModel:
         q_attn = q.unsqueeze(0).unsqueeze(2)
         k_attn = k_seq.transpose(0, 1).unsqueeze(0)
         v_attn = v_seq.transpose(0, 1).unsqueeze(0)
-        attn_out = F.scaled_dot_product_attention(q_attn, k_attn, v_attn, enable_gqa=True)
-        attn_out = attn_out.squeeze(0).squeeze(1).flatten()
+        if self.attn_fp32:
+            attn_out = attention_gqa_fp32(q, k_seq, v_seq).to(torch.bfloat16).flatten()
+        else:
+            attn_out = F.scaled_dot_product_attention(q_attn, k_attn, v_attn, enable_gqa=True)
+            attn_out = attn_out.squeeze(0).squeeze(1).flatten()
         self.taps[("attn", li)] = attn_out
         attn_out = rms_norm(attn_out, layer["attn_sub_norm"], c.eps)
         return self._lin(attn_out, layer, "o")

@@ -76,6 +76,9 @@ struct wf_engine {
     int linear_algo = 0;
     int hx = 1;              // relu^2(gate)*up in its own small kernel instead of every down-proj CTA's prologue (WF_HX=0 to fold it back)
     int decode_tc = 0;       // WF_DECODE_TC=1: batched decode linears (B > 32) on tcgen05 split-K REDs instead of the mma.sync one-shot GEMM (parity-identical; measured equal in step time, both latency-bound — see DESIGN.md)
+    int tail = 1;            // 1: persistent layer-tail kernel (layer_tail.cu) for B <= 8 on single-GPU engines: 2 launches per layer (WF_TAIL=0: phase kernels)
+    unsigned long long* tail_bar = nullptr;   // [(layers + 1)][LT_MAX_PHASES] grid-barrier arrival counters, one set per launch site
+    int* tail_epoch = nullptr;
     int fused = 1;           // 1: phase kernels (linear_small / glue_rows + gemm_oneshot / fused attention); 0: one kernel per op
     // fused path state: raw fp32 accumulators of the four linears, their per-token activation scale / Sigma a,
     // a second hidden buffer (residual ping-pong) and the attention merge counters
@@ -188,6 +191,116 @@ int run_step(wf_engine* e, int B, int feed_back) {
     if ((rc = launch_rmsnorm_quant(e->hid, e->final_norm, c.eps, B, e->hidden, e->normed, e->q8, e->a_scale, e->rowsum, s, false))) return rc;
     if ((rc = launch_lm_head_argmax(e->normed, e->embed, B, c.vocab, e->hidden, e->logits, e->d_next, e->ws_lm, s))) return rc;
     if ((rc = launch_advance(e->d_pos, e->d_len, e->d_tok, e->d_next, B, feed_back, s))) return rc;
+    e->launches = (int)(launch_count() - launches0);
+    return WF_OK;
+}
+
+// The step on the persistent layer-tail kernel (layer_tail.cu), B <= 8, single GPU:
+//   embed-phase (input_layernorm + q|k|v of layer 0), then per layer { fused attention, tail }, final norm + LM head.
+// tail(l) = o -> gate|up (+ relu^2*up) -> down -> q|k|v of layer l+1 in ONE launch: 2 launches per layer.
+// Every linear output is written once by the CTA that owns its rows (no split-K), so no accumulator is ever zeroed.
+bool tail_path_ok(const wf_engine* e, int B) {
+    if (!e->tail || e->tp.size > 1 || B > 8) return false;
+    int maxK = e->hidden;
+    if (e->attn_full > maxK) maxK = e->attn_full;
+    if (e->ffn_full > maxK) maxK = e->ffn_full;
+    const int sms = sm_count();
+    int maxrb = (e->qkv_rows / 16 + sms - 1) / sms;
+    const int gu = ((e->ffn / 16 + sms - 1) / sms) * 2;
+    if (gu > maxrb) maxrb = gu;
+    return layer_tail_fits(B, maxK, maxrb);
+}
+
+int run_step_tail(wf_engine* e, int B, int feed_back) {
+    const wf_model_config& c = e->cfg;
+    cudaStream_t s = e->stream;
+    const bool pdl = e->pdl;
+    const long long launches0 = launch_count();
+    const int MB = c.max_batch;
+    float* asc[4] = {e->lin_asc, e->lin_asc + MB, e->lin_asc + 2 * MB, e->lin_asc + 3 * MB};
+    int32_t* rs[4] = {e->lin_rs, e->lin_rs + MB, e->lin_rs + 2 * MB, e->lin_rs + 3 * MB};
+    __nv_bfloat16 *hA = e->hid, *hB = e->hid2;
+    int rc;
+    auto base = [&](int site) {
+        TailArgs t = {};
+        t.M = B; t.bar = e->tail_bar + (size_t)site * LT_MAX_PHASES; t.epoch = e->tail_epoch; t.err = e->d_err;
+        return t;
+    };
+    auto glue = [&](int mode, int K, const __nv_bfloat16* gamma) {
+        GlueParams g = {};
+        g.mode = mode; g.M = B; g.K = K; g.eps = c.eps; g.gamma = gamma; g.wait_flag = -1; g.tp = e->tp;
+        return g;
+    };
+    auto resid_from = [&](GlueParams& g, const __nv_bfloat16* in, __nv_bfloat16* out, const float* acc, int slot, const float* wscale) {
+        g.hid_in = in; g.hid_out = out; g.acc = acc; g.acc_ld = e->hidden; g.acc_rowsum = rs[slot]; g.acc_ascale = asc[slot]; g.acc_wscale = wscale;
+    };
+    auto qkv_phase = [&](TailPhaseArgs& p, const LayerW& L) {
+        p.w = L.qkv; p.N = e->qkv_rows; p.K = e->hidden; p.acc = e->acc_qkv; p.acc_ld = e->qkv_rows; p.lin_ascale = asc[0]; p.lin_rowsum = rs[0];
+    };
+    {   // embed -> input_layernorm -> q|k|v of layer 0
+        TailArgs t = base(c.layers);
+        t.nph = 1; t.bump_epoch = 1;
+        GlueParams g = glue(GL_EMBED, e->hidden, e->layers[0].g_in);
+        g.embed = e->embed; g.tokens = e->d_tok; g.hid_out = hB;
+        t.ph[0].g = g;
+        qkv_phase(t.ph[0], e->layers[0]);
+        if ((rc = launch_layer_tail(t, s, false))) return rc;
+    }
+    const float attn_scale = 1.0f / sqrtf((float)e->D);
+    for (int l = 0; l < c.layers; ++l) {
+        LayerW& L = e->layers[l];
+        {
+            FusedAttnArgs a = {};
+            a.pool = e->pool; a.kv_scales = e->kv_scales; a.layers = c.layers; a.layer = l; a.Hkv = e->Hkv; a.page_size = c.page_size;
+            a.block_table = e->d_block_table; a.max_blocks = e->max_blocks; a.seq_lens = e->d_len; a.positions = e->d_pos;
+            a.B = B; a.H = e->H; a.scale = attn_scale; a.out = e->attn;
+            a.n_out = 1; a.out_ld = e->attn_full; a.out_col0 = 0; a.signal_flag = -1; a.tp = e->tp;
+            a.qkv_acc = e->acc_qkv; a.qkv_ld = e->qkv_rows; a.qkv_rowsum = rs[0]; a.qkv_ascale = asc[0]; a.qkv_wscale = L.scales;
+            a.cos_tab = e->cos_tab; a.sin_tab = e->sin_tab; a.max_pos = c.max_seq;
+            a.merge_cnt = e->merge_cnt;
+            a.max_seq_hint = e->attn_seq_hint; a.ws = e->ws_attn; a.ws_bytes = e->ws_attn_bytes;
+            if ((rc = attn_decode_fused(a, s, pdl))) return rc;
+        }
+        TailArgs t = base(l);
+        const bool last = (l + 1 == c.layers);
+        t.nph = last ? 3 : 4;
+        {   // o: attn_sub_norm over the attention output
+            TailPhaseArgs& p = t.ph[0];
+            p.g = glue(GL_PLAIN, e->attn_full, L.g_attn);
+            p.g.src = e->attn;
+            p.w = L.o; p.N = e->hidden; p.K = e->attn_dim; p.acc = e->acc_o; p.acc_ld = e->hidden; p.lin_ascale = asc[1]; p.lin_rowsum = rs[1];
+        }
+        {   // gate|up: hidden + o -> post_attention_layernorm; epilogue relu^2(gate) * up -> h
+            TailPhaseArgs& p = t.ph[1];
+            p.g = glue(GL_RESID, e->hidden, L.g_post);
+            resid_from(p.g, hB, hA, e->acc_o, 1, L.scales + 3);
+            p.w = L.gu; p.N = 2 * e->ffn; p.K = e->hidden; p.relu2 = true; p.lin_ascale = asc[2]; p.lin_rowsum = rs[2];
+            p.h_out = e->h_full; p.h_ld = e->ffn_full; p.h_wscale = L.scales + 4;
+        }
+        {   // down: ffn_sub_norm over h
+            TailPhaseArgs& p = t.ph[2];
+            p.g = glue(GL_PLAIN, e->ffn_full, L.g_ffn);
+            p.g.src = e->h_full;
+            p.w = L.down; p.N = e->hidden; p.K = e->ffn; p.acc = e->acc_down; p.acc_ld = e->hidden; p.lin_ascale = asc[3]; p.lin_rowsum = rs[3];
+        }
+        if (!last) {   // q|k|v of the next layer: hidden + down -> input_layernorm
+            TailPhaseArgs& p = t.ph[3];
+            p.g = glue(GL_RESID, e->hidden, e->layers[l + 1].g_in);
+            resid_from(p.g, hA, hB, e->acc_down, 3, L.scales + 6);
+            qkv_phase(p, e->layers[l + 1]);
+        }
+        if ((rc = launch_layer_tail(t, s, pdl))) return rc;
+    }
+    {   // hidden + down-proj -> final norm -> tied LM head + greedy argmax
+        GlueParams g = glue(GL_RESID, e->hidden, e->final_norm);
+        resid_from(g, hA, hB, e->acc_down, 3, e->layers[c.layers - 1].scales + 6);
+        g.y_out = e->normed; g.q_out = e->q8;
+        if ((rc = launch_glue_rows(g, s, pdl))) return rc;
+    }
+    TpLm tl = {};
+    tl.tp = e->tp; tl.signal_flag = 4 * c.layers;
+    if ((rc = launch_lm_head_argmax_tp(e->normed, e->embed, B, c.vocab, e->hidden, e->logits, c.vocab, 0, e->d_next, e->ws_lm, &tl, s))) return rc;
+    if ((rc = launch_advance_tp(e->d_pos, e->d_len, e->d_tok, e->d_next, B, feed_back, e->d_step, &tl, s))) return rc;
     e->launches = (int)(launch_count() - launches0);
     return WF_OK;
 }
@@ -372,6 +485,12 @@ int prepare_pages(wf_engine* e, int B) {
     return WF_OK;
 }
 
+int step_dispatch(wf_engine* e, int B, int feed_back) {
+    if (!e->fused) return run_step(e, B, feed_back);
+    if (tail_path_ok(e, B)) return run_step_tail(e, B, feed_back);
+    return run_step_fused(e, B, feed_back);
+}
+
 int seq_hint_for(const wf_engine* e, int B) {
     int mx = 0;
     for (int b = 0; b < B; ++b) mx = e->h_pos[b] + 1 > mx ? e->h_pos[b] + 1 : mx;
@@ -386,7 +505,7 @@ int step_graph(wf_engine* e, int B, int feed_back, int use_graph) {
     const int hint = seq_hint_for(e, B);
     if (!use_graph) {
         e->attn_seq_hint = hint;
-        return e->fused ? run_step_fused(e, B, feed_back) : run_step(e, B, feed_back);
+        return step_dispatch(e, B, feed_back);
     }
     const int gi = feed_back ? 1 : 0;
     if (!e->graph_exec[gi] || e->graph_B[gi] != B || e->graph_hint[gi] != hint) {
@@ -398,7 +517,7 @@ int step_graph(wf_engine* e, int B, int feed_back, int use_graph) {
         // and run them once outside capture in wf_engine_finalize_weights (warm-up step on slot state 0).
         cudaGraph_t graph = nullptr;
         if (cuda_check(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal), "begin capture")) return WF_ERR_CUDA;
-        int rc = e->fused ? run_step_fused(e, B, feed_back) : run_step(e, B, feed_back);
+        int rc = step_dispatch(e, B, feed_back);
         cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
         if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
         if (cuda_check(ce, "end capture")) return WF_ERR_CUDA;
@@ -454,6 +573,7 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     e->fused = env_fused ? atoi(env_fused) != 0 : 1;
     if (T > 1) e->fused = 1;                   // the exchanges live in the phase kernels
     { const char* x = getenv("WF_HX"); if (x) e->hx = atoi(x) != 0; }
+    { const char* x = getenv("WF_TAIL"); if (x) e->tail = atoi(x) != 0; }
     { const char* x = getenv("WF_DECODE_TC"); if (x) e->decode_tc = atoi(x) != 0; }
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
     int rc = WF_OK;
@@ -560,6 +680,9 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
         (rc = dalloc(e, &e->acc_gu, (size_t)B * 2 * e->ffn)) ||
         (rc = dalloc(e, &e->lin_asc, (size_t)4 * B)) || (rc = dalloc(e, &e->lin_rs, (size_t)4 * B)) ||
         (rc = dalloc(e, &e->hid2, (size_t)B * e->hidden)) || (rc = dalloc(e, &e->merge_cnt, (size_t)B * e->Hkv))) return fail(rc);
+    if ((rc = dalloc(e, &e->tail_bar, (size_t)(c.layers + 1) * LT_MAX_PHASES)) || (rc = dalloc(e, &e->tail_epoch, 1))) return fail(rc);
+    if (cuda_check(cudaMemset(e->tail_bar, 0, (size_t)(c.layers + 1) * LT_MAX_PHASES * 8), "bar memset") ||
+        cuda_check(cudaMemset(e->tail_epoch, 0, 4), "epoch memset")) return fail(WF_ERR_CUDA);
     if (cuda_check(cudaMemset(e->acc_qkv, 0, (size_t)B * e->qkv_rows * 4), "acc memset") ||
         cuda_check(cudaMemset(e->acc_gu, 0, (size_t)B * 2 * e->ffn * 4), "acc memset") ||
         cuda_check(cudaMemset(e->merge_cnt, 0, (size_t)B * e->Hkv * 4), "cnt memset")) return fail(WF_ERR_CUDA);

@@ -374,6 +374,34 @@ struct HExchangeArgs {
 int launch_h_exchange(const HExchangeArgs& a, cudaStream_t s, bool pdl);
 int launch_gemm_oneshot(const OneshotArgs& a, cudaStream_t s, bool pdl);
 void fused_init_attrs();
+
+// persistent layer-tail kernel (layer_tail.cu): all linear phases between two attention kernels in one launch
+constexpr int LT_MAX_PHASES = 4;
+struct TailPhaseArgs {
+    GlueParams g;            // the phase's input glue (M is filled in by the launcher)
+    const uint8_t* w;        // b200_tile_v1 [N][K]
+    int N, K;
+    bool relu2;              // gate|up: the epilogue writes h = relu(gate)^2 * up (bf16) instead of raw accumulators
+    float* acc;              // [M][acc_ld] raw fp32 accumulators (plain stores: the CTA owns every k of its rows)
+    int acc_ld;
+    float* lin_ascale;       // [M] out
+    int32_t* lin_rowsum;     // [M] out
+    __nv_bfloat16* h_out;    // relu2: [M][h_ld]
+    int h_ld;
+    const float* h_wscale;   // relu2: device [2]
+};
+struct TailArgs {
+    int nph, M;
+    TailPhaseArgs ph[LT_MAX_PHASES];
+    unsigned long long* bar; // [LT_MAX_PHASES] arrival counters of THIS launch site (zero-initialised once, monotonic)
+    int* epoch;              // device counter of tail-path decode steps: barrier target = grid * epoch
+    int bump_epoch;          // this launch (the first of a step, single phase) increments the epoch
+    int* err;                // device error word (bounded spins)
+};
+int launch_layer_tail(const TailArgs& a, cudaStream_t s, bool pdl);
+bool layer_tail_fits(int M, int Kmax, int max_rb_per_cta);
+void layer_tail_init_attrs();
+
 struct FusedAttnArgs {
     void* pool;
     int layers, layer, Hkv, page_size;

@@ -196,6 +196,7 @@ int launch_gemm_oneshot(const OneshotArgs& a, cudaStream_t s, bool pdl) {
 void linear_small_init_attrs();
 void fused_init_attrs() {
     linear_small_init_attrs();
+    layer_tail_init_attrs();
     cudaFuncSetAttribute(gemm_oneshot_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(gemm_oneshot_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(gemm_oneshot_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
