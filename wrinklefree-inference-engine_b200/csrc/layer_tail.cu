@@ -82,7 +82,7 @@ __device__ __forceinline__ void lt_grid_barrier(unsigned long long* slot, unsign
         asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(slot), "l"(1ull) : "memory");
         unsigned long long v;
         asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
-        if (v < target) {
+        if (v < target && !(err && ld_relaxed_gpu(err))) {      // after one timeout every later barrier falls through: the step is lost anyway
             const unsigned long long t0 = spin_now();
             for (;;) {
                 asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
