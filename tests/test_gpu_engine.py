@@ -161,11 +161,12 @@ def test_phase_kernels_equal_per_op_kernels(B, monkeypatch):
         assert (na == nb).all()
 
 
-@pytest.mark.parametrize("B", [1, 3, 8])
+@pytest.mark.parametrize("B", [1, 3, 8, 12, 33, 64])
 def test_layer_tail_kernel_equals_phase_kernels(B, monkeypatch):
-    """B <= 8 has two fused forms: the persistent layer-tail kernel (default: o -> gate|up -> down -> next q|k|v in one launch, grid
-    barriers between the phases, whole-row-block ownership) and the per-phase kernels with split-K REDs (WF_TAIL=0, the form the
-    tensor-parallel engines use).  Same rounding points, exact integer contraction: identical logits, and far fewer launches."""
+    """Two fused forms exist: the persistent layer-tail kernels (default: o -> gate|up -> down -> next q|k|v in one launch, grid
+    barriers between the phases, whole-row-block ownership; layer_tail.cu for B <= 8, layer_tail_batch.cu above) and the per-phase
+    kernels with split-K REDs (WF_TAIL=0, the form the tensor-parallel engines use).  Same rounding points, exact integer
+    contraction: identical logits, and far fewer launches."""
     from wf_bitnet.synth import make_weights
     cfg = small_cfg(max_batch=B, layers=3)
     w = make_weights(cfg, seed=98)

@@ -11,9 +11,12 @@ for f in tests/test_gpu_engine.py tests/test_gpu_linear.py tests/test_gpu_attent
 done
 grep -h "config0" gpurun_out/test_gpu_engine.log >> gpurun_out/summary.txt
 for t in 1 0; do
+  echo "WF_TAIL=$t" >> gpurun_out/summary.txt
   WF_TAIL=$t timeout 300 python tools/profile_step.py --batch 1 --ctx 512 --steps 50 >> gpurun_out/summary.txt 2>&1
   WF_TAIL=$t timeout 300 python tools/profile_step.py --batch 4 --ctx 512 --steps 50 >> gpurun_out/summary.txt 2>&1
   WF_TAIL=$t timeout 300 python tools/profile_step.py --batch 8 --ctx 512 --steps 50 >> gpurun_out/summary.txt 2>&1
+  WF_TAIL=$t timeout 300 python tools/profile_step.py --batch 16 --ctx 2048 --steps 20 >> gpurun_out/summary.txt 2>&1
+  WF_TAIL=$t timeout 300 python tools/profile_step.py --batch 64 --ctx 4096 --steps 20 >> gpurun_out/summary.txt 2>&1
 done
 timeout 600 python tools/cfg0_diag.py --layers 4,30 --steps 24 > gpurun_out/cfg0_diag.log 2>&1
 echo "cfg0_diag exit=$?" >> gpurun_out/summary.txt

@@ -29,7 +29,7 @@ def main():
         b = ops.ternary_linear(tile, n, k, q, mode="i32_plus1", algo=2)
         assert torch.equal(a, b)
     # engine steps: tail kernel (B <= 8), phase kernels (WF_TAIL=0), batched phases (B > 8), split attention chunks
-    for B, env in ((1, {"WF_TAIL": "1"}), (3, {"WF_TAIL": "1"}), (3, {"WF_TAIL": "0"}), (12, {})):
+    for B, env in ((1, {"WF_TAIL": "1"}), (3, {"WF_TAIL": "1"}), (3, {"WF_TAIL": "0"}), (12, {"WF_TAIL": "1"}), (12, {"WF_TAIL": "0"})):
         os.environ.update(env)
         cfg = EngineConfig(hidden=256, layers=2, heads=4, kv_heads=2, head_dim=128, ffn=384, vocab=512, max_seq=1088, page_size=16, max_batch=B)
         eng = Engine(cfg)

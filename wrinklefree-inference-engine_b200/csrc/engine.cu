@@ -76,9 +76,12 @@ struct wf_engine {
     int linear_algo = 0;
     int hx = 1;              // relu^2(gate)*up in its own small kernel instead of every down-proj CTA's prologue (WF_HX=0 to fold it back)
     int decode_tc = 0;       // WF_DECODE_TC=1: batched decode linears (B > 32) on tcgen05 split-K REDs instead of the mma.sync one-shot GEMM (parity-identical; measured equal in step time, both latency-bound — see DESIGN.md)
+    int tail_batch = 1;      // the same for 8 < B <= 64 (layer_tail_batch.cu; WF_TAIL_BATCH=0: glue_rows + one-shot GEMM per phase)
     int tail = 1;            // 1: persistent layer-tail kernel (layer_tail.cu) for B <= 8 on single-GPU engines: 2 launches per layer (WF_TAIL=0: phase kernels)
-    unsigned long long* tail_bar = nullptr;   // [(layers + 1)][LT_MAX_PHASES] grid-barrier arrival counters, one set per launch site
-    int* tail_epoch = nullptr;
+    // grid-barrier arrival counters, one set per launch site, and the epoch (steps so far) of each kernel family:
+    // [0] layer_tail_kernel (B <= 8, LT_MAX_PHASES slots per site), [1] layer_tail_batch_kernel (B > 8, 2 * LT_MAX_PHASES slots)
+    unsigned long long* tail_bar[2] = {nullptr, nullptr};
+    int* tail_epoch = nullptr;   // [2]
     int fused = 1;           // 1: phase kernels (linear_small / glue_rows + gemm_oneshot / fused attention); 0: one kernel per op
     // fused path state: raw fp32 accumulators of the four linears, their per-token activation scale / Sigma a,
     // a second hidden buffer (residual ping-pong) and the attention merge counters
@@ -200,10 +203,11 @@ int run_step(wf_engine* e, int B, int feed_back) {
 // tail(l) = o -> gate|up (+ relu^2*up) -> down -> q|k|v of layer l+1 in ONE launch: 2 launches per layer.
 // Every linear output is written once by the CTA that owns its rows (no split-K), so no accumulator is ever zeroed.
 bool tail_path_ok(const wf_engine* e, int B) {
-    if (!e->tail || e->tp.size > 1 || B > 8) return false;
+    if (!e->tail || e->tp.size > 1) return false;
     int maxK = e->hidden;
     if (e->attn_full > maxK) maxK = e->attn_full;
     if (e->ffn_full > maxK) maxK = e->ffn_full;
+    if (B > 8) return e->tail_batch && layer_tail_batch_fits(B, maxK) && B <= sm_count();
     const int sms = sm_count();
     int maxrb = (e->qkv_rows / 16 + sms - 1) / sms;
     const int gu = ((e->ffn / 16 + sms - 1) / sms) * 2;
@@ -221,14 +225,17 @@ int run_step_tail(wf_engine* e, int B, int feed_back) {
     int32_t* rs[4] = {e->lin_rs, e->lin_rs + MB, e->lin_rs + 2 * MB, e->lin_rs + 3 * MB};
     __nv_bfloat16 *hA = e->hid, *hB = e->hid2;
     int rc;
+    const int fam = B <= 8 ? 0 : 1;
     auto base = [&](int site) {
         TailArgs t = {};
-        t.M = B; t.bar = e->tail_bar + (size_t)site * LT_MAX_PHASES; t.epoch = e->tail_epoch; t.err = e->d_err;
+        t.M = B; t.bar = e->tail_bar[fam] + (size_t)site * LT_MAX_PHASES * (fam + 1); t.epoch = e->tail_epoch + fam; t.err = e->d_err;
         return t;
     };
-    auto glue = [&](int mode, int K, const __nv_bfloat16* gamma) {
+    auto launch_tail = [&](const TailArgs& t, bool use_pdl) { return fam ? launch_layer_tail_batch(t, s, use_pdl) : launch_layer_tail(t, s, use_pdl); };
+    auto glue = [&](int mode, int K, const __nv_bfloat16* gamma, int slot) {
         GlueParams g = {};
         g.mode = mode; g.M = B; g.K = K; g.eps = c.eps; g.gamma = gamma; g.wait_flag = -1; g.tp = e->tp;
+        g.q_out = e->q8; g.scale_out = asc[slot]; g.rowsum_out = rs[slot];      // batched form: the rows are published once, in global memory
         return g;
     };
     auto resid_from = [&](GlueParams& g, const __nv_bfloat16* in, __nv_bfloat16* out, const float* acc, int slot, const float* wscale) {
@@ -240,11 +247,11 @@ int run_step_tail(wf_engine* e, int B, int feed_back) {
     {   // embed -> input_layernorm -> q|k|v of layer 0
         TailArgs t = base(c.layers);
         t.nph = 1; t.bump_epoch = 1;
-        GlueParams g = glue(GL_EMBED, e->hidden, e->layers[0].g_in);
+        GlueParams g = glue(GL_EMBED, e->hidden, e->layers[0].g_in, 0);
         g.embed = e->embed; g.tokens = e->d_tok; g.hid_out = hB;
         t.ph[0].g = g;
         qkv_phase(t.ph[0], e->layers[0]);
-        if ((rc = launch_layer_tail(t, s, false))) return rc;
+        if ((rc = launch_tail(t, false))) return rc;
     }
     const float attn_scale = 1.0f / sqrtf((float)e->D);
     for (int l = 0; l < c.layers; ++l) {
@@ -266,35 +273,35 @@ int run_step_tail(wf_engine* e, int B, int feed_back) {
         t.nph = last ? 3 : 4;
         {   // o: attn_sub_norm over the attention output
             TailPhaseArgs& p = t.ph[0];
-            p.g = glue(GL_PLAIN, e->attn_full, L.g_attn);
+            p.g = glue(GL_PLAIN, e->attn_full, L.g_attn, 1);
             p.g.src = e->attn;
             p.w = L.o; p.N = e->hidden; p.K = e->attn_dim; p.acc = e->acc_o; p.acc_ld = e->hidden; p.lin_ascale = asc[1]; p.lin_rowsum = rs[1];
         }
         {   // gate|up: hidden + o -> post_attention_layernorm; epilogue relu^2(gate) * up -> h
             TailPhaseArgs& p = t.ph[1];
-            p.g = glue(GL_RESID, e->hidden, L.g_post);
+            p.g = glue(GL_RESID, e->hidden, L.g_post, 2);
             resid_from(p.g, hB, hA, e->acc_o, 1, L.scales + 3);
             p.w = L.gu; p.N = 2 * e->ffn; p.K = e->hidden; p.relu2 = true; p.lin_ascale = asc[2]; p.lin_rowsum = rs[2];
             p.h_out = e->h_full; p.h_ld = e->ffn_full; p.h_wscale = L.scales + 4;
         }
         {   // down: ffn_sub_norm over h
             TailPhaseArgs& p = t.ph[2];
-            p.g = glue(GL_PLAIN, e->ffn_full, L.g_ffn);
+            p.g = glue(GL_PLAIN, e->ffn_full, L.g_ffn, 3);
             p.g.src = e->h_full;
             p.w = L.down; p.N = e->hidden; p.K = e->ffn; p.acc = e->acc_down; p.acc_ld = e->hidden; p.lin_ascale = asc[3]; p.lin_rowsum = rs[3];
         }
         if (!last) {   // q|k|v of the next layer: hidden + down -> input_layernorm
             TailPhaseArgs& p = t.ph[3];
-            p.g = glue(GL_RESID, e->hidden, e->layers[l + 1].g_in);
+            p.g = glue(GL_RESID, e->hidden, e->layers[l + 1].g_in, 0);
             resid_from(p.g, hA, hB, e->acc_down, 3, L.scales + 6);
             qkv_phase(p, e->layers[l + 1]);
         }
-        if ((rc = launch_layer_tail(t, s, pdl))) return rc;
+        if ((rc = launch_tail(t, pdl))) return rc;
     }
     {   // hidden + down-proj -> final norm -> tied LM head + greedy argmax
-        GlueParams g = glue(GL_RESID, e->hidden, e->final_norm);
+        GlueParams g = glue(GL_RESID, e->hidden, e->final_norm, 0);
         resid_from(g, hA, hB, e->acc_down, 3, e->layers[c.layers - 1].scales + 6);
-        g.y_out = e->normed; g.q_out = e->q8;
+        g.y_out = e->normed; g.scale_out = nullptr; g.rowsum_out = nullptr;
         if ((rc = launch_glue_rows(g, s, pdl))) return rc;
     }
     TpLm tl = {};
@@ -574,6 +581,7 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     if (T > 1) e->fused = 1;                   // the exchanges live in the phase kernels
     { const char* x = getenv("WF_HX"); if (x) e->hx = atoi(x) != 0; }
     { const char* x = getenv("WF_TAIL"); if (x) e->tail = atoi(x) != 0; }
+    { const char* x = getenv("WF_TAIL_BATCH"); if (x) e->tail_batch = atoi(x) != 0; }
     { const char* x = getenv("WF_DECODE_TC"); if (x) e->decode_tc = atoi(x) != 0; }
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
     int rc = WF_OK;
@@ -680,9 +688,11 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
         (rc = dalloc(e, &e->acc_gu, (size_t)B * 2 * e->ffn)) ||
         (rc = dalloc(e, &e->lin_asc, (size_t)4 * B)) || (rc = dalloc(e, &e->lin_rs, (size_t)4 * B)) ||
         (rc = dalloc(e, &e->hid2, (size_t)B * e->hidden)) || (rc = dalloc(e, &e->merge_cnt, (size_t)B * e->Hkv))) return fail(rc);
-    if ((rc = dalloc(e, &e->tail_bar, (size_t)(c.layers + 1) * LT_MAX_PHASES)) || (rc = dalloc(e, &e->tail_epoch, 1))) return fail(rc);
-    if (cuda_check(cudaMemset(e->tail_bar, 0, (size_t)(c.layers + 1) * LT_MAX_PHASES * 8), "bar memset") ||
-        cuda_check(cudaMemset(e->tail_epoch, 0, 4), "epoch memset")) return fail(WF_ERR_CUDA);
+    if ((rc = dalloc(e, &e->tail_bar[0], (size_t)(c.layers + 1) * LT_MAX_PHASES)) || (rc = dalloc(e, &e->tail_bar[1], (size_t)(c.layers + 1) * 2 * LT_MAX_PHASES)) ||
+        (rc = dalloc(e, &e->tail_epoch, 2))) return fail(rc);
+    if (cuda_check(cudaMemset(e->tail_bar[0], 0, (size_t)(c.layers + 1) * LT_MAX_PHASES * 8), "bar memset") ||
+        cuda_check(cudaMemset(e->tail_bar[1], 0, (size_t)(c.layers + 1) * 2 * LT_MAX_PHASES * 8), "bar memset") ||
+        cuda_check(cudaMemset(e->tail_epoch, 0, 8), "epoch memset")) return fail(WF_ERR_CUDA);
     if (cuda_check(cudaMemset(e->acc_qkv, 0, (size_t)B * e->qkv_rows * 4), "acc memset") ||
         cuda_check(cudaMemset(e->acc_gu, 0, (size_t)B * 2 * e->ffn * 4), "acc memset") ||
         cuda_check(cudaMemset(e->merge_cnt, 0, (size_t)B * e->Hkv * 4), "cnt memset")) return fail(WF_ERR_CUDA);

@@ -398,9 +398,12 @@ struct TailArgs {
     int bump_epoch;          // this launch (the first of a step, single phase) increments the epoch
     int* err;                // device error word (bounded spins)
 };
-int launch_layer_tail(const TailArgs& a, cudaStream_t s, bool pdl);
+int launch_layer_tail(const TailArgs& a, cudaStream_t s, bool pdl);          // M <= 8  (layer_tail.cu)
 bool layer_tail_fits(int M, int Kmax, int max_rb_per_cta);
 void layer_tail_init_attrs();
+int launch_layer_tail_batch(const TailArgs& a, cudaStream_t s, bool pdl);    // 8 < M <= 64 (layer_tail_batch.cu); bar: 2 * LT_MAX_PHASES slots
+bool layer_tail_batch_fits(int M, int Kmax);
+void layer_tail_batch_init_attrs();
 
 struct FusedAttnArgs {
     void* pool;
