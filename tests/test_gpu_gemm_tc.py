@@ -67,21 +67,21 @@ def test_tc_fused_epilogues_match_mma_path():
     a = ops.ternary_linear(tile, n, k, cu(q), w_scale=ws, seg_end=[384, 512, 640], out_dtype=torch.float32, algo=3, **kw)
     b = ops.ternary_linear(tile, n, k, cu(q), w_scale=ws, seg_end=[384, 512, 640], out_dtype=torch.float32, algo=2, **kw)
     assert torch.equal(a, b)
-    acc = O.gemm_i32_fast(packed, q, 1).astype(np.float32)
+    from test_gpu_linear import ref_dequant          # the reference's fp32 rounding sequence (direct_inference_full.py:202-206)
     scale_n = np.concatenate([np.full(384, 0.7), np.full(128, 1.3), np.full(128, 2.1)]).astype(np.float32)
-    assert np.array_equal(a.cpu().numpy(), (acc * scale_n[None, :]) * s[:, None])
+    assert np.array_equal(a.cpu().numpy(), ref_dequant(packed, q, rs, scale_n, s))
     res = torch.from_numpy(rng.standard_normal((m, n)).astype(np.float32) * 50).to(torch.bfloat16).cuda()
     w1 = torch.tensor([1.1]).cuda()
     a = ops.ternary_linear(tile, n, k, cu(q), w_scale=w1, residual=res, out_dtype=torch.bfloat16, algo=3, **kw)
-    lin = torch.from_numpy((acc * np.float32(1.1)) * s[:, None]).to(torch.bfloat16)
+    lin = torch.from_numpy(ref_dequant(packed, q, rs, np.float32(1.1), s)).to(torch.bfloat16)
     assert torch.equal(a.cpu(), res.cpu() + lin)
     wg = rng.integers(-1, 2, size=(ffn, k)).astype(np.float32)
     wu = rng.integers(-1, 2, size=(ffn, k)).astype(np.float32)
     pg, pu = O.pack_ternary(wg)[0], O.pack_ternary(wu)[0]
     tile_gu = ops.i2s_to_tile(ops.interleave_rows16(cu(pg), cu(pu)))
     sg, su = np.float32(0.9), np.float32(1.6)
-    g = torch.from_numpy((O.gemm_i32_fast(pg, q, 1).astype(np.float32) * sg) * s[:, None]).to(torch.bfloat16)
-    u = torch.from_numpy((O.gemm_i32_fast(pu, q, 1).astype(np.float32) * su) * s[:, None]).to(torch.bfloat16)
+    g = torch.from_numpy(ref_dequant(pg, q, rs, sg, s)).to(torch.bfloat16)
+    u = torch.from_numpy(ref_dequant(pu, q, rs, su, s)).to(torch.bfloat16)
     got = ops.ternary_linear(tile_gu, 2 * ffn, k, cu(q), w_scale=torch.tensor([float(sg), float(su)]).cuda(), relu2_mul=True,
                              out_dtype=torch.bfloat16, algo=3, **kw).cpu()
     assert got.shape == (m, ffn) and torch.equal(got, torch.relu(g).square() * u)

@@ -15,6 +15,17 @@ def cu(a):
     return torch.from_numpy(np.ascontiguousarray(a)).cuda()
 
 
+def ref_dequant(packed, q, rs, ws, s):
+    """The reference's dequantised linear output with ITS fp32 rounding sequence (scripts/direct_inference_full.py:202-206):
+    fl32( fl32( fl32(S * s_w) - fl32(s_w * sum a) ) * s_a ),  S = sum (w+1) a (the kernel's accumulator).  ws: scalar or [N]."""
+    S = O.gemm_i32_fast(packed, q, 0).astype(np.float32)
+    ws = np.asarray(ws, np.float32)
+    wsr = ws[None, :] if ws.ndim else ws
+    y = S * wsr
+    c = (wsr * rs.astype(np.float32)[:, None]).astype(np.float32)
+    return ((y - c).astype(np.float32) * s.astype(np.float32)[:, None]).astype(np.float32)
+
+
 def make(n, k, m, seed):
     rng = np.random.default_rng(seed)
     w = rng.integers(-1, 2, size=(n, k)).astype(np.float32)
@@ -102,8 +113,8 @@ def test_gemv_large_relu2_epilogue():
     pg, pu = O.pack_ternary(wg)[0], O.pack_ternary(wu)[0]
     tile_gu = ops.i2s_to_tile(ops.interleave_rows16(cu(pg), cu(pu)))
     sg, su = np.float32(0.9), np.float32(1.6)
-    g = torch.from_numpy((O.gemm_i32_fast(pg, q, 1).astype(np.float32) * sg) * s[:, None]).to(torch.bfloat16)
-    u = torch.from_numpy((O.gemm_i32_fast(pu, q, 1).astype(np.float32) * su) * s[:, None]).to(torch.bfloat16)
+    g = torch.from_numpy(ref_dequant(pg, q, rs, sg, s)).to(torch.bfloat16)
+    u = torch.from_numpy(ref_dequant(pu, q, rs, su, s)).to(torch.bfloat16)
     want_h = torch.relu(g).square() * u
     got = ops.ternary_linear(tile_gu, 2 * ffn, k, cu(q), mode="linear", rowsum=cu(rs), act_scale=cu(s),
                              w_scale=torch.tensor([float(sg), float(su)]).cuda(), relu2_mul=True, out_dtype=torch.bfloat16, algo=1).cpu()
@@ -210,9 +221,8 @@ def test_fused_epilogues(m):
     _, packed, x, q, s, rs = make(n, k, m, 5)
     ws = torch.tensor([0.7, 1.3, 2.1])
     seg = [384, 512, 640]
-    acc = O.gemm_i32_fast(packed, q, 1).astype(np.float32)
     scale_n = np.concatenate([np.full(384, 0.7), np.full(128, 1.3), np.full(128, 2.1)]).astype(np.float32)
-    want = (acc * scale_n[None, :]) * s[:, None]
+    want = ref_dequant(packed, q, rs, scale_n, s)
     tile = ops.i2s_to_tile(cu(packed))
     for algo in ((1, 2) if m <= 8 else (2,)):
         got = ops.ternary_linear(tile, n, k, cu(q), mode="linear", rowsum=cu(rs), act_scale=cu(s), w_scale=ws.cuda(), seg_end=seg,
@@ -221,7 +231,7 @@ def test_fused_epilogues(m):
     # --- residual: hidden + proj in bf16
     res = torch.from_numpy(rng.standard_normal((m, n)).astype(np.float32) * 50).to(torch.bfloat16)
     w1 = torch.tensor([1.1])
-    lin = torch.from_numpy((acc * np.float32(1.1)) * s[:, None]).to(torch.bfloat16)
+    lin = torch.from_numpy(ref_dequant(packed, q, rs, np.float32(1.1), s)).to(torch.bfloat16)
     want_r = res + lin
     for algo in ((1, 2) if m <= 8 else (2,)):
         got = ops.ternary_linear(tile, n, k, cu(q), mode="linear", rowsum=cu(rs), act_scale=cu(s), w_scale=w1.cuda(),
@@ -234,8 +244,8 @@ def test_fused_epilogues(m):
     il = ops.interleave_rows16(cu(pg), cu(pu))
     tile_gu = ops.i2s_to_tile(il)
     sg, su = np.float32(0.9), np.float32(1.6)
-    g = torch.from_numpy((O.gemm_i32_fast(pg, q, 1).astype(np.float32) * sg) * s[:, None]).to(torch.bfloat16)
-    u = torch.from_numpy((O.gemm_i32_fast(pu, q, 1).astype(np.float32) * su) * s[:, None]).to(torch.bfloat16)
+    g = torch.from_numpy(ref_dequant(pg, q, rs, sg, s)).to(torch.bfloat16)
+    u = torch.from_numpy(ref_dequant(pu, q, rs, su, s)).to(torch.bfloat16)
     want_h = torch.relu(g).square() * u
     for algo in ((1, 2) if m <= 8 else (2,)):
         got = ops.ternary_linear(tile_gu, 2 * ffn, k, cu(q), mode="linear", rowsum=cu(rs), act_scale=cu(s),

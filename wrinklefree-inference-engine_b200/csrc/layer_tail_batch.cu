@@ -27,9 +27,9 @@ constexpr int LB_CW = 16;
 constexpr int LB_CT = LB_CW * 32;            // 512 consumer threads
 constexpr int LB_THREADS = LB_CT + 64;       // + loader warp (16) + producer warp (17)
 constexpr int LB_KC = 4;                     // k-blocks per chunk = k-slots
-constexpr int LB_RBMAX = 6;                  // row-blocks per pass (accumulators: 6 x 2 x 4 registers)
+constexpr int LB_RBMAX = 4;                  // row-blocks per pass (accumulators: 4 x 2 x 4 registers; 18 warps are allocated as 20 -> 96 registers per thread)
 constexpr int LB_WSLOT = LB_RBMAX * LB_KC * WF_TILE_BYTES;   // 12 KB
-constexpr int LB_WSLOTS = 7;
+constexpr int LB_WSLOTS = 10;
 constexpr int LB_ASTRIDE = LB_KC * 128 + 16;                 // 16-byte skew: conflict-free ldmatrix
 constexpr int LB_ASLOT = 64 * LB_ASTRIDE;                    // 33 KB
 constexpr int LB_ASLOTS = 3;
@@ -85,7 +85,7 @@ __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t* bar) {
     asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-__global__ void __maxnreg__(112) layer_tail_batch_kernel(const __grid_constant__ BatchParams p) {
+__global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const __grid_constant__ BatchParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* wring = smem;                                        // LB_WSLOTS * LB_WSLOT
     unsigned char* aring = wring + LB_WSLOTS * LB_WSLOT;                // LB_ASLOTS * LB_ASLOT

@@ -65,8 +65,10 @@ _fused_cache = {}
 def _fused_tile(kind, ws):
     key = (kind,) + tuple((w.data_ptr(), tuple(w.shape), w._version) for w in ws)
     hit = _fused_cache.get(key)
+    if hit is not None and not all(a is b for a, b in zip(hit[3], ws)):
+        hit = None          # same address, other tensor object: never trust a data_ptr whose owner may have been freed
     if hit is None:
-        if len(_fused_cache) > 256:
+        if len(_fused_cache) > 64:
             _fused_cache.clear()
         for w in ws:
             if w.dim() != 2 or w.dtype != torch.uint8 or (w.shape[1] * 4) % 128:
@@ -75,9 +77,9 @@ def _fused_tile(kind, ws):
             cat = torch.cat([w.contiguous() for w in ws], dim=0)
         else:
             cat = _wf.interleave_rows16(ws[0], ws[1])       # gate|up in 16-row blocks: relu^2*up pairs sit in one CTA
-        hit = (_wf.i2s_to_tile(cat), cat.shape[0], cat.shape[1] * 4)
+        hit = (_wf.i2s_to_tile(cat), cat.shape[0], cat.shape[1] * 4, tuple(ws))   # the entry keeps its source tensors alive
         _fused_cache[key] = hit
-    return hit
+    return hit[:3]
 
 
 def _rows(x):
