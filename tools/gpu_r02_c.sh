@@ -17,6 +17,7 @@ for t in 1 0; do
     WF_TAIL=$t timeout 300 python tools/profile_step.py --batch $1 --ctx $2 --steps 30 2>&1 | tail -1 >> gpurun_out/summary.txt
   done
 done
+WF_TRACE=1 timeout 120 python tools/trace_tail.py --batch 1 --ctx 512 > gpurun_out/r02_trace_tail_bs1.txt 2>&1
 bash tools/prefill_experiments.sh > gpurun_out/prefill_experiments.log 2>&1
 NCU="ncu --profile-from-start off --clock-control none --metrics gpu__time_duration.sum --csv"
 python tools/profile_step.py --batch 1 --ctx 512 > gpurun_out/plain1.log 2>&1 && $NCU --log-file gpurun_out/r02_launches_bs1_ctx512.csv python tools/profile_step.py --batch 1 --ctx 512 > gpurun_out/ncu1.log 2>&1

@@ -229,6 +229,7 @@ int run_step_tail(wf_engine* e, int B, int feed_back) {
     auto base = [&](int site) {
         TailArgs t = {};
         t.M = B; t.bar = e->tail_bar[fam] + (size_t)site * LT_MAX_PHASES * (fam + 1); t.epoch = e->tail_epoch + fam; t.err = e->d_err;
+        if (e->trace && site < c.layers) t.trace = e->trace + (size_t)32 * site;
         return t;
     };
     auto launch_tail = [&](const TailArgs& t, bool use_pdl) { return fam ? launch_layer_tail_batch(t, s, use_pdl) : launch_layer_tail(t, s, use_pdl); };
@@ -266,6 +267,7 @@ int run_step_tail(wf_engine* e, int B, int feed_back) {
             a.cos_tab = e->cos_tab; a.sin_tab = e->sin_tab; a.max_pos = c.max_seq;
             a.merge_cnt = e->merge_cnt;
             a.max_seq_hint = e->attn_seq_hint; a.ws = e->ws_attn; a.ws_bytes = e->ws_attn_bytes;
+            if (e->trace) a.trace = e->trace + (size_t)32 * (4 * c.layers + 4 + l);
             if ((rc = attn_decode_fused(a, s, pdl))) return rc;
         }
         TailArgs t = base(l);

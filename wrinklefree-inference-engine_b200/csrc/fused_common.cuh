@@ -397,6 +397,7 @@ struct TailArgs {
     int* epoch;              // device counter of tail-path decode steps: barrier target = grid * epoch
     int bump_epoch;          // this launch (the first of a step, single phase) increments the epoch
     int* err;                // device error word (bounded spins)
+    unsigned long long* trace;   // WF_TRACE timeline taps of this launch site (32 slots) or null
 };
 int launch_layer_tail(const TailArgs& a, cudaStream_t s, bool pdl);          // M <= 8  (layer_tail.cu)
 bool layer_tail_fits(int M, int Kmax, int max_rb_per_cta);

@@ -57,6 +57,7 @@ struct TailParams {
     int* epoch;                  // tail-path decode steps so far (device counter): barrier target = grid * epoch
     int bump_epoch;              // the first launch of a step (single phase, no barrier) increments it
     int* err;
+    unsigned long long* trace;   // WF_TRACE timeline taps (CTA 0): [0] entry, [1] dependency wait done, then per phase 5 stamps
 };
 
 __device__ __forceinline__ int lt_dp4a_us(uint32_t a, uint32_t b, int c) {
@@ -144,8 +145,11 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
     }
 
     // ---------------------------------------------------- consumer warps
+    const bool tr = p.trace != nullptr && cta == 0 && tid == 0;
+    if (tr) p.trace[0] = gtimer();
     glue_prefetch_gamma<LT_CT>(p.ph[0].g);
     pdl_wait_prior();                                   // the attention kernel's output (or the previous step) is complete
+    if (tr) p.trace[1] = gtimer();
     // Barrier counters are monotonic over the decode steps that take this path (no reset, CUDA-graph replay safe).  The epoch is
     // bumped by the step's first launch, which finished (transitively, through the attention kernel) before this one got here.
     if (p.bump_epoch && cta == 0 && tid == 0) atomicAdd(p.epoch, 1);
@@ -161,6 +165,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
             // every CTA of this grid is resident now: letting the next kernel's CTAs in can no longer starve the barrier
             if (pi == 1) pdl_launch_dependents();
         }
+        if (tr) p.trace[2 + 5 * pi] = gtimer();          // barrier passed
         int rb_lo, rb_hi;
         lt_slab(ph, cta, grid, rb_lo, rb_hi);
         const int n_rbs = rb_hi - rb_lo;
@@ -179,6 +184,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
             }
         }
         group_bar<1, LT_CT>();     // activations (and the cleared accumulators) complete
+        if (tr) p.trace[3 + 5 * pi] = gtimer();          // glue done
 
         // ---- main loop: S[m, n] += sum_k code[n, k] * a[m, k] over this CTA's row-blocks
         constexpr int NACC = MR == 0 ? 16 : 8;
@@ -253,6 +259,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
         const unsigned char* wbase = ring + warp * (LT_TPW * WF_TILE_BYTES) + lane * 16;
         for (int it = 0; it < nstages; ++it) {
             mbar_wait(&full_bar[s], ph_bit);
+            if (tr && it == 0) p.trace[4 + 5 * pi] = gtimer();   // first weight stage present
             const int i0 = it * LT_STAGE_TILES + LT_TPW * warp;
             if (i0 < ntiles) {
                 const unsigned char* wp = wbase + s * LT_STAGE_BYTES;
@@ -277,6 +284,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
         }
         flush(cur_rb);
         group_bar<1, LT_CT>();
+        if (tr) p.trace[5 + 5 * pi] = gtimer();          // main loop done
 
         // ---- epilogue: this CTA owns every k of its rows — plain stores
         if (ph.epi == 0) {
@@ -318,6 +326,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
                 }
             }
         }
+        if (tr) p.trace[6 + 5 * pi] = gtimer();          // epilogue stores issued
     }
     if (p.nph == 1) pdl_launch_dependents();
 }
@@ -366,7 +375,7 @@ int launch_layer_tail(const TailArgs& a, cudaStream_t s, bool pdl) {
     if (stages > LT_MAX_STAGES) stages = LT_MAX_STAGES;
     if (stages < 3) { set_error("layer_tail: M*K=%d*%d does not fit in shared memory", a.M, Kmax); return WF_ERR_UNSUPPORTED; }
     p.stages = stages;
-    p.bar = a.bar; p.epoch = a.epoch; p.bump_epoch = a.bump_epoch; p.err = a.err;
+    p.bar = a.bar; p.epoch = a.epoch; p.bump_epoch = a.bump_epoch; p.err = a.err; p.trace = a.trace;
     if (a.bump_epoch && a.nph != 1) { set_error("layer_tail: the epoch-bumping launch must be single-phase"); return WF_ERR_INVALID; }
     const size_t smem = (size_t)stages * LT_STAGE_BYTES + fixed;
     cudaLaunchConfig_t cfg = {};
