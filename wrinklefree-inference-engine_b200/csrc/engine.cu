@@ -65,6 +65,7 @@ struct wf_engine {
     // activations
     __nv_bfloat16 *hid = nullptr, *qkv = nullptr, *qrot = nullptr, *attn = nullptr, *gu = nullptr, *normed = nullptr;
     int8_t* q8 = nullptr;
+    int8_t* q8c = nullptr;   // the same rows in the batched tail kernel's chunk-major image (QMAP_CHUNKED, fused_common.cuh)
     float* a_scale = nullptr;
     int32_t* rowsum = nullptr;
     float* logits = nullptr;
@@ -236,7 +237,7 @@ int run_step_tail(wf_engine* e, int B, int feed_back) {
     auto glue = [&](int mode, int K, const __nv_bfloat16* gamma, int slot) {
         GlueParams g = {};
         g.mode = mode; g.M = B; g.K = K; g.eps = c.eps; g.gamma = gamma; g.wait_flag = -1; g.tp = e->tp;
-        g.q_out = e->q8; g.scale_out = asc[slot]; g.rowsum_out = rs[slot];      // batched form: the rows are published once, in global memory
+        g.q_out = fam ? e->q8c : e->q8; g.scale_out = asc[slot]; g.rowsum_out = rs[slot];      // batched form: the rows are published once, in global memory
         return g;
     };
     auto resid_from = [&](GlueParams& g, const __nv_bfloat16* in, __nv_bfloat16* out, const float* acc, int slot, const float* wscale) {
@@ -684,7 +685,7 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     if ((rc = dalloc(e, &e->hid, (size_t)B * e->hidden)) || (rc = dalloc(e, &e->normed, (size_t)B * e->hidden)) ||
         (rc = dalloc(e, &e->qkv, (size_t)B * e->qkv_rows)) || (rc = dalloc(e, &e->qrot, (size_t)B * e->attn_dim)) ||
         (rc = dalloc(e, &e->gu, (size_t)B * e->ffn)) ||
-        (rc = dalloc(e, &e->q8, (size_t)B * maxK)) || (rc = dalloc(e, &e->a_scale, B)) || (rc = dalloc(e, &e->rowsum, B)) ||
+        (rc = dalloc(e, &e->q8, (size_t)B * maxK)) || (rc = dalloc(e, &e->q8c, (size_t)((maxK + 511) / 512) * QCHUNK_BYTES)) || (rc = dalloc(e, &e->a_scale, B)) || (rc = dalloc(e, &e->rowsum, B)) ||
         (rc = dalloc(e, &e->logits, (size_t)B * c.vocab))) return fail(rc);
     if ((rc = dalloc(e, &e->acc_qkv, (size_t)B * e->qkv_rows)) ||
         (rc = dalloc(e, &e->acc_gu, (size_t)B * 2 * e->ffn)) ||

@@ -174,6 +174,13 @@ __device__ __forceinline__ void glue_prefetch_gamma(const GlueParams& p) {
     for (int o = threadIdx.x * 128; o < p.K * 2; o += NT * 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(g + o));
 }
 
+// where the int8 codes of a row go: plain [K]; the dp4a staging order of gemv_stream.cu; or the chunk-major image the batched
+// tail kernel copies straight into its shared-memory ring — [K/512][64 rows][512 + 16 B skew] (layer_tail_batch.cu), qdst =
+// base + row * QROW_BYTES
+enum { QMAP_PLAIN = 0, QMAP_PERM = 1, QMAP_CHUNKED = 2 };
+constexpr int QROW_BYTES = 4 * 128 + 16;
+constexpr int QCHUNK_BYTES = 64 * QROW_BYTES;
+
 // One activation row through the glue: source -> (residual / relu^2*up) -> RMSNorm -> per-token int8.
 // Executed by the NT-thread group (thread ids 0..NT-1).  ys: K bf16 of scratch (shared); qdst: K int8
 // (shared or global, 8-byte aligned); fs/is: >= 32 floats / ints of shared scratch.
@@ -181,7 +188,7 @@ __device__ __forceinline__ void glue_prefetch_gamma(const GlueParams& p) {
 template <int ID, int NT>
 __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat16* ys, int8_t* qdst, float* fs, int* is,
                                          bool write_side, float& scale_ret, int& rowsum_ret, unsigned long long* tr = nullptr,
-                                         bool perm = false) {
+                                         int qmap = QMAP_PLAIN) {
     const int K = p.K;
     const int tid = threadIdx.x;
     float ss = 0.f;
@@ -311,8 +318,10 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
             const uint32_t pr = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8);
             if (i < 2) w0 |= pr << (16 * i); else w1 |= pr << (16 * (i - 2));
         }
-        if (!perm) {
+        if (qmap == QMAP_PLAIN) {
             *reinterpret_cast<uint2*>(qdst + k) = make_uint2(w0, w1);
+        } else if (qmap == QMAP_CHUNKED) {
+            *reinterpret_cast<uint2*>(qdst + (size_t)(k >> 9) * QCHUNK_BYTES + (k & 511)) = make_uint2(w0, w1);
         } else {
             // dp4a staging order (gemv_stream.cu): word (8g + 4h + t) of a 128-k block goes to word (8t + 2g + h)
             const int w = k >> 2, wi = w & 31;
@@ -322,6 +331,124 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
         }
     }
     if (tr) tr[4] = gtimer();
+    const int total = group_sum_i1<ID, NT>(psum, is);
+    scale_ret = scale;
+    rowsum_ret = total;
+}
+
+// The same glue with the row held in REGISTERS between the passes (no bf16 scratch round trips through shared memory): each
+// thread owns the 8-element granules k = (it*NT + tid)*8, it < MAXIT — the same thread -> k map and the same per-thread
+// summation order as glue_row, so every reduction (and with it every output bit) is identical.  All global loads of the row
+// (source, accumulator, residual, gamma) are issued before the first use.  Modes EMBED / PLAIN / RESID, local accumulator only;
+// requires K <= NT * 8 * MAXIT.
+template <int ID, int NT, int MAXIT>
+__device__ __forceinline__ void glue_row_regs(const GlueParams& p, int m, int8_t* qdst, float* fs, int* is, bool write_side,
+                                              float& scale_ret, int& rowsum_ret, int qmap) {
+    const int K = p.K;
+    const int tid = threadIdx.x;
+    uint4 xv[MAXIT], gv[MAXIT];
+    float ss = 0.f;
+#pragma unroll
+    for (int it = 0; it < MAXIT; ++it) {
+        const int k = (it * NT + tid) * 8;
+        if (k < K) gv[it] = *reinterpret_cast<const uint4*>(p.gamma + k);
+    }
+    if (p.mode == GL_RESID) {
+        const int rs = p.acc_rowsum[m];
+        const float sa = p.acc_ascale[m], ws = p.acc_wscale[0];
+        const float* arow = p.acc + (size_t)m * p.acc_ld;
+        const __nv_bfloat16* hrow = p.hid_in + (size_t)m * K;
+        float4 a0[MAXIT], a1[MAXIT];
+#pragma unroll
+        for (int it = 0; it < MAXIT; ++it) {
+            const int k = (it * NT + tid) * 8;
+            if (k < K) { xv[it] = ldcg_u4(hrow + k); a0[it] = ldcg_f4(arow + k); a1[it] = ldcg_f4(arow + k + 4); }
+        }
+#pragma unroll
+        for (int it = 0; it < MAXIT; ++it) {
+            const int k = (it * NT + tid) * 8;
+            if (k < K) {
+                const float S[8] = {a0[it].x, a0[it].y, a0[it].z, a0[it].w, a1[it].x, a1[it].y, a1[it].z, a1[it].w};
+                const uint32_t hw[4] = {xv[it].x, xv[it].y, xv[it].z, xv[it].w};
+                uint32_t o[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float x0 = bf16_round(bf16lo(hw[i]) + bf16_round(lin_value(S[2 * i], rs, ws, sa)));
+                    const float x1 = bf16_round(bf16hi(hw[i]) + bf16_round(lin_value(S[2 * i + 1], rs, ws, sa)));
+                    ss += x0 * x0 + x1 * x1;
+                    o[i] = pack_bf16x2(x0, x1);
+                }
+                xv[it] = make_uint4(o[0], o[1], o[2], o[3]);
+                if (write_side && p.hid_out) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = xv[it];
+            }
+        }
+    } else {
+        const __nv_bfloat16* row = (p.mode == GL_EMBED) ? p.embed + (size_t)p.tokens[m] * K : p.src + (size_t)m * K;
+#pragma unroll
+        for (int it = 0; it < MAXIT; ++it) {
+            const int k = (it * NT + tid) * 8;
+            if (k < K) xv[it] = ldcg_u4(row + k);
+        }
+#pragma unroll
+        for (int it = 0; it < MAXIT; ++it) {
+            const int k = (it * NT + tid) * 8;
+            if (k < K) {
+                if (write_side && p.hid_out && p.mode == GL_EMBED) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = xv[it];
+                const uint32_t w[4] = {xv[it].x, xv[it].y, xv[it].z, xv[it].w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { const float a = bf16lo(w[i]), b = bf16hi(w[i]); ss += a * a + b * b; }
+            }
+        }
+    }
+    ss = group_sum1<ID, NT>(ss, fs);
+    const float r = bf16_round(1.0f / sqrtf(ss / (float)K + p.eps));
+    float amax = 0.f;
+#pragma unroll
+    for (int it = 0; it < MAXIT; ++it) {
+        const int k = (it * NT + tid) * 8;
+        if (k < K) {
+            const uint32_t xw[4] = {xv[it].x, xv[it].y, xv[it].z, xv[it].w}, gw[4] = {gv[it].x, gv[it].y, gv[it].z, gv[it].w};
+            uint32_t o[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float y0 = bf16_round(bf16_round(bf16lo(xw[i]) * r) * bf16lo(gw[i]));
+                const float y1 = bf16_round(bf16_round(bf16hi(xw[i]) * r) * bf16hi(gw[i]));
+                amax = fmaxf(amax, fmaxf(fabsf(y0), fabsf(y1)));
+                o[i] = pack_bf16x2(y0, y1);
+            }
+            xv[it] = make_uint4(o[0], o[1], o[2], o[3]);
+            if (write_side && p.y_out) *reinterpret_cast<uint4*>(p.y_out + (size_t)m * K + k) = xv[it];
+        }
+    }
+    amax = group_max1<ID, NT>(amax, fs + 16);
+    const float scale = act_scale_from_absmax(amax);
+    const QDiv qd = make_qdiv(scale);
+    int psum = 0;
+#pragma unroll
+    for (int it = 0; it < MAXIT; ++it) {
+        const int k = (it * NT + tid) * 8;
+        if (k < K) {
+            const uint32_t yw[4] = {xv[it].x, xv[it].y, xv[it].z, xv[it].w};
+            uint32_t w0 = 0, w1 = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int q0 = quant_i8(bf16lo(yw[i]), qd), q1 = quant_i8(bf16hi(yw[i]), qd);
+                psum += q0 + q1;
+                const uint32_t pr = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8);
+                if (i < 2) w0 |= pr << (16 * i); else w1 |= pr << (16 * (i - 2));
+            }
+            if (qmap == QMAP_PLAIN) {
+                *reinterpret_cast<uint2*>(qdst + k) = make_uint2(w0, w1);
+            } else if (qmap == QMAP_CHUNKED) {
+                *reinterpret_cast<uint2*>(qdst + (size_t)(k >> 9) * QCHUNK_BYTES + (k & 511)) = make_uint2(w0, w1);
+            } else {   // dp4a staging order (see glue_row)
+                const int w = k >> 2, wi = w & 31;
+                const int d = (w & ~31) + 8 * (wi & 3) + 2 * (wi >> 3) + ((wi >> 2) & 1);
+                reinterpret_cast<uint32_t*>(qdst)[d] = w0;
+                reinterpret_cast<uint32_t*>(qdst)[d + 8] = w1;
+            }
+        }
+    }
     const int total = group_sum_i1<ID, NT>(psum, is);
     scale_ret = scale;
     rowsum_ret = total;

@@ -17,12 +17,14 @@
 //     8-stage x 16 KB ring; one mbarrier per stage collects the TMA transaction bytes AND the four unpack
 //     warps' arrivals, one tcgen05.commit per stage releases both halves;
 //   * one elected thread issues 4 x tcgen05.mma.cta_group::1.kind::i8 (M128 N128 K32) per stage;
-//   * epilogue warps: tcgen05.ld 32x32b.x32 (lane = weight row, columns = tokens) -> per-warp smem transpose ->
-//     the linear epilogue (Sigma-a correction, scales, residual, relu^2*up) on 8 consecutive n -> 16-byte stores.
-// Measured (r01, profiles/): 1.58 PTOP/s on the 2B layer at M = 16384 = 54 % of cuBLASLt int8 on the same box;
-// the stage rate sits at the 256-clk tensor floor, what is left is shared-memory bandwidth (TMA write + MMA read =
-// 128 B/clk at the floor, so the epilogue's transpose traffic serialises) — the cta_group::2 form (each SM holds
-// half of the activation tile) is the next step.
+//   * epilogue warps: tcgen05.ld 32x32b.x32 (lane = weight row, columns = tokens) -> the linear epilogue (Sigma-a
+//     correction, scales, residual, relu^2*up) in registers -> one store per token: a warp's 32 lanes are 32 consecutive n,
+//     so every store instruction is a full coalesced line and nothing is transposed through shared memory.
+// Shared memory is the binding resource of the main loop: TMA write + MMA read of the activation tile = 128 B/clk at the
+// 256-clk/stage tensor floor, i.e. all of an SM's shared-memory bandwidth.  Round 2 measurements (profiles/r02_prefill_*):
+// with the epilogue's math and stores switched off the kernel runs 2.15 PTOP/s (374 clk per stage) — the round-1 epilogue
+// (smem transpose + dependent per-token global loads) cost 40 % on the short-K shapes.  The cta_group::2 form (each SM
+// holds half of the activation tile) is what would lift the 374-clk stage.
 #include "linear_common.cuh"
 #include "fused_common.cuh"
 #include <cuda.h>
@@ -41,8 +43,8 @@ constexpr int TC_A_COL0 = 2 * TC_BN;               // weight ring starts after t
 constexpr int TC_TMEM_COLS = 512;
 constexpr int TC_PF = 4;                           // weight prefetch distance (stages, in registers)
 constexpr int TC_MAX_THREADS = 576;                // warps 0-3 epilogue, 4..4+4*NU-1 unpack (NU groups of 4), then TMA, MMA
-constexpr int TC_EP_STRIDE = 32 * 4 + 16;             // bytes per token row of an epilogue transpose patch (padded: conflict-free)
-constexpr int TC_SMEM = TC_STAGES * TC_STAGE_BYTES + 4 * 32 * TC_EP_STRIDE + 1024;
+constexpr int TC_EP_TOK = 4 * TC_BN * 8;            // per epilogue warp: {Sigma a, activation scale} of the tile's 128 tokens
+constexpr int TC_SMEM = TC_STAGES * TC_STAGE_BYTES + TC_EP_TOK + 1024;
 
 struct TcParams {
     const uint8_t* w;
@@ -309,45 +311,45 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
             if (lane == 0) mbar_arrive(&full_bar[pending]);
         }
     } else {
-        // ------------------------------------------------------------ epilogue warps: TMEM -> registers -> smem transpose -> global
-        // A thread owns one weight row (TMEM lane) and receives 32 tokens per tcgen05.ld, but the output is token-major:
-        // each warp transposes its [32 tokens][32 rows] int32 block through a private padded smem patch, then a thread
-        // finishes 8 consecutive n of one token and writes them with one or two 16-byte stores.
+        // ------------------------------------------------------------ epilogue warps: TMEM -> registers -> global
+        // A thread owns one weight row n (TMEM lane) and receives 32 tokens per tcgen05.ld.  The output is token-major, so a
+        // warp's store of ONE token covers 32 consecutive n: a full 128-byte line in fp32 (64 B in bf16) — coalesced as it
+        // stands, no transpose through shared memory.  gate|up tiles (relu^2*up): the 16 up rows of a 32-row group sit in
+        // lanes 16..31 and are handed to the gate lanes with one shuffle.
         const int q = warp;
         const uint32_t lane_base = (uint32_t)(q * 32) << 16;
-        unsigned char* patch = smem_raw + (ring - smem_u32(smem_raw)) + TC_STAGES * TC_STAGE_BYTES + q * (32 * TC_EP_STRIDE);
-        const int oct = lane & 3, rsub = lane >> 2;
+        // per-token {Sigma a, activation scale} of the current tile, staged per warp BEFORE the accumulator wait (dependent
+        // global loads inside the store loop were ~10 k clk per tile); read back as one broadcast LDS.64 per token
+        int2* tok = reinterpret_cast<int2*>(smem_raw + (ring - smem_u32(smem_raw)) + TC_STAGES * TC_STAGE_BYTES) + q * TC_BN;
         const int mode = p.ep.out_mode;
         const bool relu2 = (mode == WF_OUT_LINEAR) && (p.ep.epi_flags & WF_EPI_RELU2_MUL);
         const bool resid = (mode == WF_OUT_LINEAR) && (p.ep.epi_flags & WF_EPI_RESIDUAL);
         const bool obf16 = (mode == WF_OUT_LINEAR) && p.ep.out_dtype == WF_BF16;
-        const int esize = obf16 ? 2 : 4;
         const int ncols = relu2 ? p.N / 2 : p.N;
-        const bool vec_ok = (((size_t)p.ep.ldo * esize) % 16 == 0) && (((uintptr_t)p.ep.out & 15) == 0) &&
-                            (!resid || (((uintptr_t)p.ep.residual & 15) == 0));
         const bool red = p.red_acc != nullptr;
         if (red) pdl_wait_prior();   // the accumulator buffer was cleared by an earlier phase of the step
         for (int tl = 0; tl < my_tiles; ++tl) {
             int m_blk, n_blk, ks;
             tile_coords(tl, m_blk, n_blk, ks);
             const int buf = tl & 1;
+            if (!red && mode != WF_OUT_I32_PLUS1 && mode != WF_OUT_COMPAT_F32) {
+                __syncwarp();                                                       // the previous tile's readers are done
+#pragma unroll
+                for (int j = 0; j < TC_BN / 32; ++j) {
+                    const int m = min(m_blk * TC_BN + j * 32 + lane, p.M - 1);
+                    const int rs = p.ep.rowsum ? p.ep.rowsum[m] : 0;
+                    const float sa = (mode == WF_OUT_LINEAR) ? p.ep.act_scale[p.ep.act_scale_per_token ? m : 0] : 1.f;
+                    tok[j * 32 + lane] = make_int2(rs, __float_as_int(sa));
+                }
+                __syncwarp();
+            }
+            const int n = n_blk * TC_BM + q * 32 + lane;                           // this thread's weight row
+            const int col = relu2 ? (n >> 5) * 16 + (n & 15) : n;                  // its output column (gate lanes under relu^2*up)
+            const bool store_lane = relu2 ? (lane < 16 && col < ncols) : (n < p.N);
+            float ws = 1.f;
+            if (mode == WF_OUT_LINEAR) ws = relu2 ? p.ep.w_scale[(lane >= 16 && p.ep.nseg > 1) ? 1 : 0] : seg_scale(p.ep, min(n, p.N - 1));
             mbar_wait(&tfull_bar[buf], (uint32_t)((tl >> 1) & 1));
             tc_fence_after();
-            const int n0 = n_blk * TC_BM + q * 32 + oct * 8;                       // first weight row of this thread's 8
-            const int c0 = relu2 ? (n0 >> 5) * 16 + (n0 & 15) : n0;                // first output column
-            const int nvalid = min(8, ncols - c0);                                 // <= 0: nothing to store
-            float ws8[8];
-            float wsu = 1.f;
-            if (mode == WF_OUT_LINEAR) {
-                if (relu2) {
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) ws8[e] = p.ep.w_scale[0];
-                    wsu = p.ep.w_scale[p.ep.nseg > 1 ? 1 : 0];
-                } else {
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) ws8[e] = seg_scale(p.ep, min(n0 + e, p.N - 1));
-                }
-            }
 #pragma unroll 1
             for (int c = 0; c < TC_BN / 32; ++c) {
                 uint32_t v[32];
@@ -361,106 +363,51 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
                     if (lane == 0) mbar_arrive(&tempty_bar[buf]);
                 }
                 if (p.dbg) continue;
-#pragma unroll
-                for (int j = 0; j < 32; ++j) *reinterpret_cast<uint32_t*>(patch + j * TC_EP_STRIDE + lane * 4) = v[j];
-                __syncwarp();
                 const int m0 = m_blk * TC_BN + c * 32;
+                const int mcnt = min(32, p.M - m0);                                // tokens of this chunk that exist (warp-uniform)
+                if (red) {
+                    // decode form: exact fp32 RED of the raw accumulators (split-K partial sums meet in L2)
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int r = rsub + 8 * i, m = m0 + r;
-                    if (m < p.M && nvalid > 0 && !(relu2 && oct >= 2)) {
-                        const int4 sa4 = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + oct * 32);
-                        const int4 sb4 = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + oct * 32 + 16);
-                        const int S[8] = {sa4.x, sa4.y, sa4.z, sa4.w, sb4.x, sb4.y, sb4.z, sb4.w};
-                        if (red) {
-                            // decode form: exact fp32 RED of the raw accumulators (split-K partial sums meet in L2)
-                            float* op = p.red_acc + (size_t)m * p.red_ld + c0;
-                            if (nvalid == 8) {
-                                red_add_v4_f32(op, (float)S[0], (float)S[1], (float)S[2], (float)S[3]);
-                                red_add_v4_f32(op + 4, (float)S[4], (float)S[5], (float)S[6], (float)S[7]);
-                            } else {
+                    for (int j = 0; j < 32; ++j)
+                        if (j < mcnt && store_lane) red_add_f32(p.red_acc + (size_t)(m0 + j) * p.red_ld + col, (float)(int)v[j]);
+                    continue;
+                }
+                if (mode == WF_OUT_LINEAR) {
 #pragma unroll
-                                for (int e = 0; e < 8; ++e)
-                                    if (e < nvalid) red_add_f32(op + e, (float)S[e]);
-                            }
-                            continue;
-                        }
-                        const int rs = p.ep.rowsum ? p.ep.rowsum[m] : 0;
-                        const size_t o = (size_t)m * p.ep.ldo + c0;
-                        if (mode == WF_OUT_LINEAR) {
-                            const float sa = p.ep.act_scale[p.ep.act_scale_per_token ? m : 0];
-                            float y[8];
-#pragma unroll
-                            for (int e = 0; e < 8; ++e)   // the reference's rounding sequence (linear_value in linear_common.cuh)
-                                y[e] = __fmul_rn(__fsub_rn(__fmul_rn((float)S[e], ws8[e]), __fmul_rn(ws8[e], (float)rs)), sa);
+                    for (int j = 0; j < 32; ++j) {
+                        if (j < mcnt) {
+                            const int2 t = tok[c * 32 + j];
+                            const float sa = __int_as_float(t.y);
+                            // the reference's rounding sequence (linear_value in linear_common.cuh)
+                            float y = __fmul_rn(__fsub_rn(__fmul_rn((float)(int)v[j], ws), __fmul_rn(ws, (float)t.x)), sa);
+                            const size_t o = (size_t)(m0 + j) * p.ep.ldo + col;
                             if (relu2) {
-                                const int4 ua = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + (oct + 2) * 32);
-                                const int4 ub = *reinterpret_cast<const int4*>(patch + r * TC_EP_STRIDE + (oct + 2) * 32 + 16);
-                                const int U[8] = {ua.x, ua.y, ua.z, ua.w, ub.x, ub.y, ub.z, ub.w};
-#pragma unroll
-                                for (int e = 0; e < 8; ++e) {
-                                    const float g = bf16_round(y[e]);
-                                    const float u = bf16_round(__fmul_rn(__fsub_rn(__fmul_rn((float)U[e], wsu), __fmul_rn(wsu, (float)rs)), sa));
-                                    const float t = fmaxf(g, 0.f);
-                                    y[e] = bf16_round(bf16_round(t * t) * u);
-                                }
+                                const float g = bf16_round(y);
+                                const float u = __shfl_down_sync(0xffffffffu, g, 16);   // the up row of this column: lane + 16
+                                const float r = fmaxf(g, 0.f);
+                                y = bf16_round(bf16_round(r * r) * u);
                             } else if (resid) {
-                                const __nv_bfloat16* rp = p.ep.residual + o;
-                                if (vec_ok && nvalid == 8) {
-                                    const uint4 rv = *reinterpret_cast<const uint4*>(rp);
-                                    const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
-#pragma unroll
-                                    for (int e = 0; e < 4; ++e) {
-                                        y[2 * e] = bf16lo(rw[e]) + bf16_round(y[2 * e]);
-                                        y[2 * e + 1] = bf16hi(rw[e]) + bf16_round(y[2 * e + 1]);
-                                    }
-                                } else {
-#pragma unroll
-                                    for (int e = 0; e < 8; ++e)
-                                        if (e < nvalid) y[e] = __bfloat162float(rp[e]) + bf16_round(y[e]);
-                                }
+                                if (store_lane) y = __bfloat162float(p.ep.residual[o]) + bf16_round(y);
                             }
-                            if (obf16) {
-                                __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.ep.out) + o;
-                                if (vec_ok && nvalid == 8) {
-                                    *reinterpret_cast<uint4*>(op) = make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]), pack_bf16x2(y[6], y[7]));
-                                } else {
-#pragma unroll
-                                    for (int e = 0; e < 8; ++e)
-                                        if (e < nvalid) op[e] = __float2bfloat16_rn(y[e]);
-                                }
-                            } else {
-                                float* op = reinterpret_cast<float*>(p.ep.out) + o;
-                                if (vec_ok && nvalid == 8) {
-                                    *reinterpret_cast<float4*>(op) = make_float4(y[0], y[1], y[2], y[3]);
-                                    *reinterpret_cast<float4*>(op + 4) = make_float4(y[4], y[5], y[6], y[7]);
-                                } else {
-#pragma unroll
-                                    for (int e = 0; e < 8; ++e)
-                                        if (e < nvalid) op[e] = y[e];
-                                }
-                            }
-                        } else {
-                            uint32_t w[8];
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                if (mode == WF_OUT_I32_PLUS1) w[e] = (uint32_t)S[e];
-                                else if (mode == WF_OUT_I32) w[e] = (uint32_t)(S[e] - rs);
-                                else w[e] = __float_as_uint(__fmul_rn((float)S[e], p.ep.host_scale));   // bitnet_gemv/gemm: (float)sumi * scale
-                            }
-                            uint32_t* op = reinterpret_cast<uint32_t*>(p.ep.out) + o;
-                            if (vec_ok && nvalid == 8) {
-                                *reinterpret_cast<uint4*>(op) = make_uint4(w[0], w[1], w[2], w[3]);
-                                *reinterpret_cast<uint4*>(op + 4) = make_uint4(w[4], w[5], w[6], w[7]);
-                            } else {
-#pragma unroll
-                                for (int e = 0; e < 8; ++e)
-                                    if (e < nvalid) op[e] = w[e];
+                            if (store_lane) {
+                                if (obf16) reinterpret_cast<__nv_bfloat16*>(p.ep.out)[o] = __float2bfloat16_rn(y);
+                                else reinterpret_cast<float*>(p.ep.out)[o] = y;
                             }
                         }
                     }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        if (j < mcnt && store_lane) {
+                            const int S = (int)v[j];
+                            uint32_t w;
+                            if (mode == WF_OUT_I32_PLUS1) w = (uint32_t)S;
+                            else if (mode == WF_OUT_I32) w = (uint32_t)(S - tok[c * 32 + j].x);
+                            else w = __float_as_uint(__fmul_rn((float)S, p.ep.host_scale));   // bitnet_gemv/gemm: (float)sumi * scale
+                            reinterpret_cast<uint32_t*>(p.ep.out)[(size_t)(m0 + j) * p.ep.ldo + col] = w;
+                        }
+                    }
                 }
-                __syncwarp();
             }
         }
     }

@@ -177,7 +177,11 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
         for (int i = tid; i < n_rbs * 128; i += LT_CT) sacc[i] = 0;
         for (int m = 0; m < M; ++m) {
             float sc; int rsum;
-            glue_row<1, LT_CT>(ph.g, m, ys, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, nullptr, MR == 1);
+            // K <= 9216 (every 2B vector): the row stays in registers between the three passes
+            if (ph.g.K <= LT_CT * 8 * 3 && ph.g.mode != GL_RELU2 && ph.g.acc_own_cols == 0)
+                glue_row_regs<1, LT_CT, 3>(ph.g, m, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, MR == 1);
+            else
+                glue_row<1, LT_CT>(ph.g, m, ys, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, nullptr, MR == 1);
             if (tid == 0) {
                 s_scale[m] = sc; s_rsum[m] = rsum;
                 if (cta == 0) { ph.lin_ascale[m] = sc; ph.lin_rowsum[m] = rsum; }

@@ -30,8 +30,9 @@ constexpr int LB_KC = 4;                     // k-blocks per chunk = k-slots
 constexpr int LB_RBMAX = 4;                  // row-blocks per pass (accumulators: 4 x 2 x 4 registers; 18 warps are allocated as 20 -> 96 registers per thread)
 constexpr int LB_WSLOT = LB_RBMAX * LB_KC * WF_TILE_BYTES;   // 12 KB
 constexpr int LB_WSLOTS = 10;
-constexpr int LB_ASTRIDE = LB_KC * 128 + 16;                 // 16-byte skew: conflict-free ldmatrix
-constexpr int LB_ASLOT = 64 * LB_ASTRIDE;                    // 33 KB
+constexpr int LB_ASTRIDE = QROW_BYTES;                       // 512 + 16-byte skew: conflict-free ldmatrix
+constexpr int LB_ASLOT = QCHUNK_BYTES;                       // 33 KB: one chunk of the glue's chunk-major image (QMAP_CHUNKED)
+static_assert(LB_ASTRIDE == LB_KC * 128 + 16, "chunk = LB_KC k-blocks");
 constexpr int LB_ASLOTS = 3;
 constexpr int LB_SS = LB_RBMAX * 16 + 4;                     // reduction buffer row stride (words)
 constexpr int LB_RED_BYTES = 64 * LB_SS * 4;                 // 25.6 KB (also the glue's bf16 row scratch)
@@ -53,6 +54,7 @@ struct BatchParams {
     int* epoch;
     int bump_epoch;
     int* err;
+    unsigned long long* trace;   // WF_TRACE: globaltimer taps of CTA 0 (same slots as layer_tail.cu)
 };
 
 __device__ __forceinline__ void lb_slab(const BatchPhase& ph, int cta, int grid, int& rb_lo, int& rb_hi) {
@@ -81,10 +83,6 @@ __device__ __forceinline__ void lb_grid_barrier(unsigned long long* slot, unsign
     group_bar<1, LB_CT>();
 }
 
-__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t* bar) {
-    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-
 __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const __grid_constant__ BatchParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* wring = smem;                                        // LB_WSLOTS * LB_WSLOT
@@ -101,7 +99,7 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
 
     if (tid == 0) {
         for (int s = 0; s < LB_WSLOTS; ++s) { mbar_init(&wfull[s], 1); mbar_init(&wempty[s], LB_CW); }
-        for (int s = 0; s < LB_ASLOTS; ++s) { mbar_init(&afull[s], 32); mbar_init(&aempty[s], LB_CW); }
+        for (int s = 0; s < LB_ASLOTS; ++s) { mbar_init(&afull[s], 1); mbar_init(&aempty[s], LB_CW); }
         mbar_init(&phase_bar, 1);
         fence_mbar_init();
     }
@@ -133,38 +131,40 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
         return;
     }
     if (warp == LB_CW) {
-        // ------------------------------------------------ activation loader: the phase's int8 rows, chunk by chunk (cp.async, L2 only)
-        int s = 0, bit = 0;
-        for (int pi = 0; pi < p.nph; ++pi) {
-            const BatchPhase& ph = p.ph[pi];
-            int rb_lo, rb_hi;
-            lb_slab(ph, cta, grid, rb_lo, rb_hi);
-            mbar_wait(&phase_bar, pi & 1);          // the rows of this phase are published (second grid barrier of the phase passed)
-            const int nchunks = (ph.KB + LB_KC - 1) / LB_KC;
-            const int8_t* q = ph.g.q_out;
-            for (int rb0 = rb_lo; rb0 < rb_hi; rb0 += LB_RBMAX) {
-                for (int ch = 0; ch < nchunks; ++ch) {
-                    const int kcl = min(LB_KC, ph.KB - ch * LB_KC);
-                    mbar_wait(&aempty[s], bit ^ 1);
-                    unsigned char* dst = aring + s * LB_ASLOT;
-                    const int gpr = kcl * 8;         // 16-byte granules per row
-                    for (int g = lane; g < 64 * gpr; g += 32) {
-                        const int m = g / gpr, gi = g - m * gpr;
-                        const bool ok = m < M;
-                        cp_async16_zfill(dst + m * LB_ASTRIDE + gi * 16, q + (size_t)(ok ? m : 0) * ph.K + (size_t)ch * LB_KC * 128 + gi * 16, ok ? 16 : 0);
+        // ------------------------------------------------ activation producer: the phase's published int8 rows, one bulk copy per
+        // chunk (the glue wrote them chunk-major with the ring's row skew, so rows 0..M-1 of a chunk are one contiguous range;
+        // rows >= M of a slot keep whatever they held — their accumulators are never stored)
+        if (lane == 0) {
+            int s = 0, bit = 0;
+            const uint32_t bytes = (uint32_t)M * LB_ASTRIDE;
+            for (int pi = 0; pi < p.nph; ++pi) {
+                const BatchPhase& ph = p.ph[pi];
+                int rb_lo, rb_hi;
+                lb_slab(ph, cta, grid, rb_lo, rb_hi);
+                mbar_wait(&phase_bar, pi & 1);          // the rows of this phase are published (second grid barrier of the phase passed)
+                fence_proxy_async_global();             // generic-proxy stores of the glue CTAs -> this thread's async-proxy reads
+                const int nchunks = (ph.KB + LB_KC - 1) / LB_KC;
+                const int8_t* q = ph.g.q_out;
+                for (int rb0 = rb_lo; rb0 < rb_hi; rb0 += LB_RBMAX) {
+                    for (int ch = 0; ch < nchunks; ++ch) {
+                        mbar_wait(&aempty[s], bit ^ 1);
+                        mbar_expect_tx(&afull[s], bytes);
+                        bulk_g2s(aring + s * LB_ASLOT, q + (size_t)ch * LB_ASLOT, bytes, &afull[s]);
+                        if (++s == LB_ASLOTS) { s = 0; bit ^= 1; }
                     }
-                    cp_async_mbar_arrive_noinc(&afull[s]);
-                    if (++s == LB_ASLOTS) { s = 0; bit ^= 1; }
                 }
             }
         }
-        cp_async_wait<0>();
         return;
     }
 
     // ---------------------------------------------------- consumer warps
     const int tg = warp & 3, ks = warp >> 2;            // token group (16 tokens), k-slot
+    const bool tg_live = tg * 16 < M;                   // a token group past the batch has nothing to compute
+    unsigned long long* tr = (p.trace && cta == 0 && tid == 0) ? p.trace : nullptr;
+    if (tr) tr[0] = gtimer();
     pdl_wait_prior();
+    if (tr) tr[1] = gtimer();
     const unsigned long long bar_target = (unsigned long long)grid * (unsigned long long)(ld_relaxed_gpu(p.epoch) + (p.bump_epoch ? 1 : 0));
     int ws = 0, wbit = 0, as = 0, abit = 0;
     int nbar = 0;
@@ -176,16 +176,23 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
             ++nbar;
             if (pi == 1) pdl_launch_dependents();               // every CTA of this grid is resident: dependents can no longer starve the barriers
         }
+        if (tr) tr[2 + 5 * pi] = gtimer();
         // ---- row glue, once per row: CTA r handles row r (residual / RMSNorm / absmax / int8 codes -> global)
         if (cta < M) {
             float sc; int rsum;
-            glue_row<1, LB_CT>(ph.g, cta, reinterpret_cast<__nv_bfloat16*>(red), ph.g.q_out + (size_t)cta * ph.g.K, fs, is, true, sc, rsum);
+            if (ph.g.K <= LB_CT * 8 * 2 && ph.g.mode != GL_RELU2 && ph.g.acc_own_cols == 0)      // the row stays in registers between the passes
+                glue_row_regs<1, LB_CT, 2>(ph.g, cta, ph.g.q_out + (size_t)cta * LB_ASTRIDE, fs, is, true, sc, rsum, QMAP_CHUNKED);
+            else
+                glue_row<1, LB_CT>(ph.g, cta, reinterpret_cast<__nv_bfloat16*>(red), ph.g.q_out + (size_t)cta * LB_ASTRIDE, fs, is, true, sc, rsum, nullptr, QMAP_CHUNKED);
             if (tid == 0) { ph.g.scale_out[cta] = sc; ph.g.rowsum_out[cta] = rsum; }
+            fence_proxy_async_global();                         // the codes are read back by bulk copies (async proxy)
         }
+        if (tr) tr[3 + 5 * pi] = gtimer();
         lb_grid_barrier(p.bar + nbar, bar_target, p.err);       // every row is published
         ++nbar;
         if (pi == 0 && p.nph == 1) pdl_launch_dependents();
-        if (tid == 0) mbar_arrive(&phase_bar);                  // release the activation loader
+        if (tid == 0) mbar_arrive(&phase_bar);                  // release the activation producer
+        if (tr) tr[4 + 5 * pi] = gtimer();
         if (ph.epi == 1) {
             for (int m = tid; m < M; m += LB_CT) { s_scale[m] = ldcg_f(ph.g.scale_out + m); s_rsum[m] = ldcg_i32(ph.g.rowsum_out + m); }
         }
@@ -205,7 +212,7 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
             for (int ch = 0; ch < nchunks; ++ch) {
                 mbar_wait(&wfull[ws], wbit);
                 mbar_wait(&afull[as], abit);
-                if (ch * LB_KC + ks < ph.KB) {
+                if (tg_live && ch * LB_KC + ks < ph.KB) {
                     const unsigned char* ab = aring + as * LB_ASLOT;
                     uint32_t b[2][8];
 #pragma unroll
@@ -240,7 +247,7 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
                 const int g = lane >> 2, t = lane & 3;
 #pragma unroll
                 for (int r = 0; r < LB_KC; ++r) {
-                    if (ks == r) {
+                    if (ks == r && tg_live) {
 #pragma unroll
                         for (int i = 0; i < LB_RBMAX; ++i) {
                             if (i < nr) {
@@ -258,6 +265,7 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
                     group_bar<1, LB_CT>();
                 }
             }
+            if (tr && rb0 + LB_RBMAX >= rb_hi) tr[5 + 5 * pi] = gtimer();
             // ---- epilogue: this CTA owns every k of these rows — plain stores
             if (ph.epi == 0) {
                 const int quads = nr * 4;
@@ -300,6 +308,7 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
             }
             group_bar<1, LB_CT>();      // red is reused by the next pass / the next phase's glue
         }
+        if (tr) tr[6 + 5 * pi] = gtimer();
     }
     if (p.bump_epoch && cta == 0 && tid == 0) atomicAdd(p.epoch, 1);   // after CTA 0's last barrier: every CTA has read the epoch
 }
@@ -335,7 +344,7 @@ int launch_layer_tail_batch(const TailArgs& a, cudaStream_t s, bool pdl) {
         ph.rot = (int)(extra % grid);
         extra += units % grid;
     }
-    p.bar = a.bar; p.epoch = a.epoch; p.bump_epoch = a.bump_epoch; p.err = a.err;
+    p.bar = a.bar; p.epoch = a.epoch; p.bump_epoch = a.bump_epoch; p.err = a.err; p.trace = a.trace;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(LB_THREADS);
