@@ -77,7 +77,7 @@ struct wf_engine {
     int linear_algo = 0;
     int hx = 1;              // relu^2(gate)*up in its own small kernel instead of every down-proj CTA's prologue (WF_HX=0 to fold it back)
     int decode_tc = 0;       // WF_DECODE_TC=1: batched decode linears (B > 32) on tcgen05 split-K REDs instead of the mma.sync one-shot GEMM (parity-identical; measured equal in step time, both latency-bound — see DESIGN.md)
-    int tail_batch = 1;      // the same for 8 < B <= 64 (layer_tail_batch.cu; WF_TAIL_BATCH=0: glue_rows + one-shot GEMM per phase)
+    int tail_batch = 0;      // WF_TAIL_BATCH=1: the same for 8 < B <= 64 (layer_tail_batch.cu).  Opt-in: measured 5.74 ms vs 5.44 ms per bs64/4K step for the phase path (profiles/r02d_*)
     int tail = 1;            // 1: persistent layer-tail kernel (layer_tail.cu) for B <= 8 on single-GPU engines: 2 launches per layer (WF_TAIL=0: phase kernels)
     // grid-barrier arrival counters, one set per launch site, and the epoch (steps so far) of each kernel family:
     // [0] layer_tail_kernel (B <= 8, LT_MAX_PHASES slots per site), [1] layer_tail_batch_kernel (B > 8, 2 * LT_MAX_PHASES slots)
