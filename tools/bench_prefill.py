@@ -28,7 +28,43 @@ def timed(fn, iters, warm=3):
     return e0.elapsed_time(e1) / iters
 
 
-def measure(tokens=16384, iters=10, algo=3, shape="2b", only="", layout="tile"):
+def clocks_under_load(fn, seconds=2.0):
+    """SM clock (MHz) and board power (W) sampled with NVML while `fn` runs back to back: median over the loaded samples."""
+    import threading
+    import time
+    import pynvml
+    pynvml.nvmlInit()
+    h = pynvml.nvmlDeviceGetHandleByIndex(torch.cuda.current_device())
+    stop, sm, pw = [False], [], []
+
+    def sampler():
+        while not stop[0]:
+            sm.append(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+            pw.append(pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0)
+            time.sleep(0.02)
+    t = threading.Thread(target=sampler)
+    t0 = time.time()
+    fn()
+    torch.cuda.synchronize()
+    t.start()
+    n = 0
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    while time.time() - t0 < seconds:
+        for _ in range(20):
+            fn()
+        n += 20
+        torch.cuda.synchronize()
+    e1.record()
+    e1.synchronize()
+    stop[0] = True
+    t.join()
+    k = len(sm) // 2
+    return {"sm_mhz_median": sorted(sm[k:])[len(sm[k:]) // 2] if sm[k:] else None, "power_w_median": round(sorted(pw[k:])[len(pw[k:]) // 2], 1) if pw[k:] else None,
+            "ms_sustained": round(e0.elapsed_time(e1) / max(n, 1), 4), "samples": len(sm)}
+
+
+def measure(tokens=16384, iters=10, algo=3, shape="2b", only="", layout="tile", clocks=False):
     """-> dict: per-linear and per-layer int8 TOP/s of the ternary GEMM at M = tokens, next to torch._int_mm (cuBLASLt) 8192^3 on the same GPU."""
     from wf_bitnet import _lib, ops
     _lib.require_gpu()
@@ -52,6 +88,12 @@ def measure(tokens=16384, iters=10, algo=3, shape="2b", only="", layout="tile"):
         ms = timed(fn, iters)
         opsn = 2.0 * M * n * k
         out[name] = {"N": n, "K": k, "ms": round(ms, 4), "TOPs": round(opsn / ms / 1e9, 1)}
+        if clocks:
+            out[name]["under_load"] = clocks_under_load(fn)
+            x8 = torch.randint(-127, 128, (M, k), device="cuda", dtype=torch.int8)
+            w8 = torch.randint(-1, 2, (n, k), device="cuda", dtype=torch.int8).t()
+            out[name]["cublaslt_under_load"] = clocks_under_load(lambda: torch._int_mm(x8, w8))
+            del x8, w8
         total_ms += ms
         total_ops += opsn
         del tile, q
@@ -90,9 +132,10 @@ def main():
     ap.add_argument("--shape", default="2b", choices=["2b", "8b"])
     ap.add_argument("--only", default="", help="time just this linear (qkv|o|gate_up|down)")
     ap.add_argument("--layout", default="tile", choices=["tile", "i2s"])
+    ap.add_argument("--clocks", action="store_true", help="also run each linear (and the same shape through cuBLASLt) back to back for 2 s and report SM clock / power under load")
     args = ap.parse_args()
     torch.cuda.set_device(0)
-    print(json.dumps(measure(args.tokens, args.iters, args.algo, args.shape, args.only, args.layout)))
+    print(json.dumps(measure(args.tokens, args.iters, args.algo, args.shape, args.only, args.layout, args.clocks)))
 
 
 if __name__ == "__main__":

@@ -42,8 +42,10 @@ constexpr int TC_A_COLS = TC_BK / 4;               // TMEM columns per weight st
 constexpr int TC_A_COL0 = 2 * TC_BN;               // weight ring starts after the two accumulator buffers
 constexpr int TC_TMEM_COLS = 512;
 constexpr int TC_PF = 4;                           // weight prefetch distance (stages, in registers)
-constexpr int TC_MAX_THREADS = 576;                // warps 0-3 epilogue, 4..4+4*NU-1 unpack (NU groups of 4), then TMA, MMA
-constexpr int TC_EP_TOK = 4 * TC_BN * 8;            // per epilogue warp: {Sigma a, activation scale} of the tile's 128 tokens
+constexpr int TC_EPW = 8;                          // epilogue warps: two per TMEM lane quarter, 64 of the tile's 128 tokens each
+constexpr int TC_EP_TOKS = TC_BN / (TC_EPW / 4);   // tokens per epilogue warp
+constexpr int TC_EP_TOK = TC_EPW * TC_EP_TOKS * 8;  // per epilogue warp: {(float) Sigma a, activation scale} of its tokens
+constexpr int tc_threads(int nu) { return (TC_EPW + 4 * nu + 2) * 32; }   // warps 0..7 epilogue, then 4*NU unpack (NU groups of 4), TMA, MMA
 constexpr int TC_SMEM = TC_STAGES * TC_STAGE_BYTES + TC_EP_TOK + 1024;
 
 struct TcParams {
@@ -51,7 +53,7 @@ struct TcParams {
     int w_layout;
     int M, N, K, KB;
     int tiles_n, tiles_m;
-    int dbg;   // timing experiments only (WF_TC_DBG): 1 = epilogue skips math/stores, 2 = also skips the TMEM loads
+    int dbg;   // timing experiments only (WF_TC_DBG, bit mask): 1 = epilogue skips math/stores, 2 = also the TMEM loads, 4 = unpack warps skip the TMEM stores, 8 = no activation TMA
     // batched-decode form (launch_gemm_tc_red): the K dimension is cut into `splitk` equal runs of KBs k-blocks, one CTA
     // tile each, and the epilogue adds the raw accumulators into a global fp32 buffer (exact: integers < 2^24) instead
     // of storing a finished output — the consumer phase of the decode step applies scales / residual / norm.
@@ -119,7 +121,7 @@ constexpr uint32_t tc_idesc(int m, int n) {
 // One warp issues ~190 instructions per stage at IPC ~0.3, so a single group paces the kernel at ~850 clk per stage
 // (measured) against the 256-clk tensor floor; three groups bring the unpack under the floor.
 template <int CL, int NU>
-__global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const TcParams p) {
+__global__ void __launch_bounds__(tc_threads(NU), 1) ternary_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const TcParams p) {
     extern __shared__ unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[TC_STAGES];    // TMA bytes + 4 unpack-warp arrivals
     __shared__ __align__(8) uint64_t empty_bar[TC_STAGES];   // tcgen05.commit: MMAs of the stage retired
@@ -147,10 +149,10 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
 
     if (tid == 0) {
         for (int s = 0; s < TC_STAGES; ++s) { mbar_init(&full_bar[s], 5); mbar_init(&empty_bar[s], CL); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], TC_EPW); }
         fence_mbar_init();
     }
-    constexpr int W_TMA = 4 + 4 * NU, W_MMA = W_TMA + 1;
+    constexpr int W_TMA = TC_EPW + 4 * NU, W_MMA = W_TMA + 1;
     if (warp == W_MMA) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(TC_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -178,6 +180,7 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
                     const int kg = ks * KBs + kb;
                     const int s = it % TC_STAGES;
                     mbar_wait(&empty_bar[s], (uint32_t)(((it / TC_STAGES) & 1) ^ 1));   // all CL CTAs retired this slot
+                    if (CL == 1 && (p.dbg & 8)) { mbar_arrive(&full_bar[s]); continue; }  // timing experiment: no activation traffic
                     mbar_expect_tx(&full_bar[s], TC_STAGE_BYTES);                        // own barrier: all CL slices land here
                     const uint32_t dst = ring + s * TC_STAGE_BYTES + crank * SLICE * TC_BK;
                     if (CL == 1)
@@ -233,9 +236,9 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
             if (lane == 0) tc_commit(&tfull_bar[buf]);
             __syncwarp();
         }
-    } else if (warp >= 4) {
+    } else if (warp >= TC_EPW) {
         // ------------------------------------------------------------ unpack warps: 2-bit weights -> u8 codes -> TMEM
-        const int q = warp & 3, grp = (warp - 4) >> 2;
+        const int q = warp & 3, grp = (warp - TC_EPW) >> 2;
         const uint32_t lane_base = (uint32_t)(q * 32) << 16;
         const int K4 = p.K / 4;
         uint32_t pre[TC_PF][8];
@@ -299,7 +302,7 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
                     mbar_wait(&empty_bar[s], (uint32_t)(((item / TC_STAGES) & 1) ^ 1));
                     tc_fence_after();
                     const uint32_t taddr = tmem + lane_base + TC_A_COL0 + s * TC_A_COLS;
-                    TC_ST32(taddr, v);
+                    if (!(p.dbg & 4)) TC_ST32(taddr, v);                                 // (dbg 4: timing experiment without the TMEM stores)
                     pending = s;
                 }
             }
@@ -314,32 +317,36 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
         // ------------------------------------------------------------ epilogue warps: TMEM -> registers -> global
         // A thread owns one weight row n (TMEM lane) and receives 32 tokens per tcgen05.ld.  The output is token-major, so a
         // warp's store of ONE token covers 32 consecutive n: a full 128-byte line in fp32 (64 B in bf16) — coalesced as it
-        // stands, no transpose through shared memory.  gate|up tiles (relu^2*up): the 16 up rows of a 32-row group sit in
-        // lanes 16..31 and are handed to the gate lanes with one shuffle.
-        const int q = warp;
+        // stands, no transpose through shared memory.  Two warps share a lane quarter and take 64 tokens each: with four warps
+        // and ~34 issued instructions per token the epilogue paced the short-K shapes (ncu r02_full_gemm_tc: the four warps
+        // never idle, the MMA warp 27 % of its time waiting for a drained accumulator).  gate|up tiles (relu^2*up): the 16 up
+        // rows of a 32-row group sit in lanes 16..31 and are handed to the gate lanes with one shuffle.
+        const int q = warp & 3, th = warp >> 2;                                    // lane quarter, token half
         const uint32_t lane_base = (uint32_t)(q * 32) << 16;
-        // per-token {Sigma a, activation scale} of the current tile, staged per warp BEFORE the accumulator wait (dependent
+        // per-token {(float) Sigma a, activation scale} of this warp's 64 tokens, staged BEFORE the accumulator wait (dependent
         // global loads inside the store loop were ~10 k clk per tile); read back as one broadcast LDS.64 per token
-        int2* tok = reinterpret_cast<int2*>(smem_raw + (ring - smem_u32(smem_raw)) + TC_STAGES * TC_STAGE_BYTES) + q * TC_BN;
+        float2* tok = reinterpret_cast<float2*>(smem_raw + (ring - smem_u32(smem_raw)) + TC_STAGES * TC_STAGE_BYTES) + warp * TC_EP_TOKS;
         const int mode = p.ep.out_mode;
         const bool relu2 = (mode == WF_OUT_LINEAR) && (p.ep.epi_flags & WF_EPI_RELU2_MUL);
         const bool resid = (mode == WF_OUT_LINEAR) && (p.ep.epi_flags & WF_EPI_RESIDUAL);
         const bool obf16 = (mode == WF_OUT_LINEAR) && p.ep.out_dtype == WF_BF16;
         const int ncols = relu2 ? p.N / 2 : p.N;
         const bool red = p.red_acc != nullptr;
+        const bool fast_mode = !red && mode == WF_OUT_LINEAR && !relu2 && !resid && obf16 && !p.dbg;
         if (red) pdl_wait_prior();   // the accumulator buffer was cleared by an earlier phase of the step
         for (int tl = 0; tl < my_tiles; ++tl) {
             int m_blk, n_blk, ks;
             tile_coords(tl, m_blk, n_blk, ks);
             const int buf = tl & 1;
+            const int mw0 = m_blk * TC_BN + th * TC_EP_TOKS;                       // first token of this warp
             if (!red && mode != WF_OUT_I32_PLUS1 && mode != WF_OUT_COMPAT_F32) {
                 __syncwarp();                                                       // the previous tile's readers are done
 #pragma unroll
-                for (int j = 0; j < TC_BN / 32; ++j) {
-                    const int m = min(m_blk * TC_BN + j * 32 + lane, p.M - 1);
+                for (int j = 0; j < TC_EP_TOKS / 32; ++j) {
+                    const int m = min(mw0 + j * 32 + lane, p.M - 1);
                     const int rs = p.ep.rowsum ? p.ep.rowsum[m] : 0;
                     const float sa = (mode == WF_OUT_LINEAR) ? p.ep.act_scale[p.ep.act_scale_per_token ? m : 0] : 1.f;
-                    tok[j * 32 + lane] = make_int2(rs, __float_as_int(sa));
+                    tok[j * 32 + lane] = make_float2((float)rs, sa);               // |Sigma a| <= 127 K < 2^24: exact
                 }
                 __syncwarp();
             }
@@ -348,22 +355,38 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
             const bool store_lane = relu2 ? (lane < 16 && col < ncols) : (n < p.N);
             float ws = 1.f;
             if (mode == WF_OUT_LINEAR) ws = relu2 ? p.ep.w_scale[(lane >= 16 && p.ep.nseg > 1) ? 1 : 0] : seg_scale(p.ep, min(n, p.N - 1));
+            const bool fast = fast_mode && mw0 + TC_EP_TOKS <= p.M && n_blk * TC_BM + q * 32 + 32 <= p.N;   // warp-uniform
             mbar_wait(&tfull_bar[buf], (uint32_t)((tl >> 1) & 1));
             tc_fence_after();
 #pragma unroll 1
-            for (int c = 0; c < TC_BN / 32; ++c) {
+            for (int c = 0; c < TC_EP_TOKS / 32; ++c) {
                 uint32_t v[32];
                 if (!(p.dbg & 2)) {
-                    TC_LD32(tmem + lane_base + buf * TC_BN + c * 32, v);
+                    TC_LD32(tmem + lane_base + buf * TC_BN + th * TC_EP_TOKS + c * 32, v);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 }
-                if (c == TC_BN / 32 - 1) {
+                if (c == TC_EP_TOKS / 32 - 1) {
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tempty_bar[buf]);
                 }
                 if (p.dbg) continue;
-                const int m0 = m_blk * TC_BN + c * 32;
+                const int m0 = mw0 + c * 32;
+                if (fast) {
+                    // full tile, bf16 linear output: ~9 issued instructions per token (LDS.64, I2F, 3 FMUL, FADD, F2F, pointer add, STG);
+                    // the reference's rounding sequence (linear_value in linear_common.cuh)
+                    __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.ep.out) + (size_t)m0 * p.ep.ldo + col;
+                    const size_t ldo = (size_t)p.ep.ldo;
+                    const float2* tk = tok + c * 32;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float2 t = tk[j];
+                        const float y = __fmul_rn(__fsub_rn(__fmul_rn((float)(int)v[j], ws), __fmul_rn(ws, t.x)), t.y);
+                        *op = __float2bfloat16_rn(y);
+                        op += ldo;
+                    }
+                    continue;
+                }
                 const int mcnt = min(32, p.M - m0);                                // tokens of this chunk that exist (warp-uniform)
                 if (red) {
                     // decode form: exact fp32 RED of the raw accumulators (split-K partial sums meet in L2)
@@ -376,10 +399,9 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         if (j < mcnt) {
-                            const int2 t = tok[c * 32 + j];
-                            const float sa = __int_as_float(t.y);
+                            const float2 t = tok[c * 32 + j];
                             // the reference's rounding sequence (linear_value in linear_common.cuh)
-                            float y = __fmul_rn(__fsub_rn(__fmul_rn((float)(int)v[j], ws), __fmul_rn(ws, (float)t.x)), sa);
+                            float y = __fmul_rn(__fsub_rn(__fmul_rn((float)(int)v[j], ws), __fmul_rn(ws, t.x)), t.y);
                             const size_t o = (size_t)(m0 + j) * p.ep.ldo + col;
                             if (relu2) {
                                 const float g = bf16_round(y);
@@ -402,7 +424,7 @@ __global__ void __launch_bounds__(TC_MAX_THREADS, 1) ternary_gemm_tc_kernel(cons
                             const int S = (int)v[j];
                             uint32_t w;
                             if (mode == WF_OUT_I32_PLUS1) w = (uint32_t)S;
-                            else if (mode == WF_OUT_I32) w = (uint32_t)(S - tok[c * 32 + j].x);
+                            else if (mode == WF_OUT_I32) w = (uint32_t)(S - (int)tok[c * 32 + j].x);
                             else w = __float_as_uint(__fmul_rn((float)S, p.ep.host_scale));   // bitnet_gemv/gemm: (float)sumi * scale
                             reinterpret_cast<uint32_t*>(p.ep.out)[(size_t)(m0 + j) * p.ep.ldo + col] = w;
                         }
@@ -438,6 +460,7 @@ void gemm_tc_init_attrs() {
         ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<1, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
         ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
         ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(ternary_gemm_tc_kernel<4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) == cudaSuccess;
         (void)ok;
     }
     if (!g_encode) {
@@ -449,10 +472,10 @@ void gemm_tc_init_attrs() {
     if (!g_tc_cluster) {
         const char* e = getenv("WF_TC_CLUSTER");
         g_tc_cluster = e ? atoi(e) : 1;
-        if (g_tc_cluster != 1 && g_tc_cluster != 2) g_tc_cluster = 1;
+        if (g_tc_cluster != 1 && g_tc_cluster != 2 && g_tc_cluster != 4) g_tc_cluster = 1;
         const char* u = getenv("WF_TC_NU");
-        g_tc_nu = u ? atoi(u) : 3;
-        if (g_tc_nu < 1 || g_tc_nu > 3) g_tc_nu = 3;
+        g_tc_nu = u ? atoi(u) : 2;     // two unpack groups: 18 warps at 112 registers (three groups = 22 warps at 88 spill)
+        if (g_tc_nu < 1 || g_tc_nu > 3) g_tc_nu = 2;
     }
 }
 
@@ -476,7 +499,7 @@ static int launch_tc_cl(const wf_linear_args* a, const EpiParams& ep, cudaStream
     { const char* d = getenv("WF_TC_DBG"); p.dbg = d ? atoi(d) : 0; }
     const int total = ((p.tiles_n + CL - 1) / CL) * p.tiles_m;
     cudaLaunchConfig_t cfg = {};
-    cfg.blockDim = dim3((4 + 4 * NU + 2) * 32);
+    cfg.blockDim = dim3(tc_threads(NU));
     cfg.dynamicSmemBytes = TC_SMEM;
     cfg.stream = s;
     cudaLaunchAttribute at[1];
@@ -508,7 +531,7 @@ int launch_gemm_tc_red(const uint8_t* w_tile, int N, int K, const int8_t* q, int
     gemm_tc_init_attrs();
     if (!g_encode) { set_error("gemm_tc: tcgen05 path unavailable (driver entry point / smem attribute)"); return WF_ERR_CUDA; }
     if (M < 1 || M > TC_BN || K % WF_QK || k_off % WF_QK || ldq % 16 || acc_ld % 4 || N % 8) { set_error("gemm_tc_red: unsupported shape"); return WF_ERR_UNSUPPORTED; }
-    constexpr int NU = 3;
+    constexpr int NU = 2;
     CUtensorMap tmap;
     const cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)M};
     const cuuint64_t gstride[1] = {(cuuint64_t)ldq};
@@ -534,7 +557,7 @@ int launch_gemm_tc_red(const uint8_t* w_tile, int N, int K, const int8_t* q, int
     const int total = p.tiles_n * split;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(total < sms ? total : sms);
-    cfg.blockDim = dim3((4 + 4 * NU + 2) * 32);
+    cfg.blockDim = dim3(tc_threads(NU));
     cfg.dynamicSmemBytes = TC_SMEM;
     cfg.stream = s;
     cudaLaunchAttribute at[1];
@@ -548,6 +571,7 @@ int launch_gemm_tc_red(const uint8_t* w_tile, int N, int K, const int8_t* q, int
 int launch_gemm_tc(const wf_linear_args* a, const EpiParams& ep, cudaStream_t s) {
     gemm_tc_init_attrs();
     if (!g_encode) { set_error("gemm_tc: tcgen05 path unavailable (driver entry point / smem attribute)"); return WF_ERR_CUDA; }
+    if (g_tc_cluster == 4) return launch_tc_cl<4, 2>(a, ep, s);
     if (g_tc_cluster == 2) return g_tc_nu == 2 ? launch_tc_cl<2, 2>(a, ep, s) : launch_tc_cl<2, 3>(a, ep, s);
     if (g_tc_nu == 1) return launch_tc_cl<1, 1>(a, ep, s);
     return g_tc_nu == 2 ? launch_tc_cl<1, 2>(a, ep, s) : launch_tc_cl<1, 3>(a, ep, s);
