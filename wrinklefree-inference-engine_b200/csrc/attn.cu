@@ -22,6 +22,7 @@
 namespace wf {
 
 constexpr int AT_WARPS = 4;
+constexpr int AT_EVEN_MAXB = 128;   // even work split (fused decode form): the per-sequence block counts are scanned by one CTA-wide pass
 constexpr int AT_STAGES = 3;
 constexpr int AT_BLK = 16;                              // tokens per stage
 constexpr int AT_D = 128;                               // head_dim (all BASELINE shapes)
@@ -97,6 +98,8 @@ struct AttnParams {
     float* part_o;               // [B][H][max_chunks][D]
     float* part_ml;              // [B][H][max_chunks][2]
     int direct;                  // 1: single chunk per sequence everywhere -> write final output
+    int even;                    // 1 (fused form only): the grid is ONE wave of persistent CTAs and the (sequence, kv head, block) space is cut
+                                 // into gridDim.x equal contiguous ranges (see the kernel); chunk_blocks / max_chunks / direct are unused
     // ---- fused prologue / epilogue (decode engine): q, k, v come straight from the qkv linear's raw accumulator
     const float* qkv_acc;        // [B][qkv_ld] fp32 exact integers: sum (w+1)*a, rows q | k | v
     int qkv_ld;
@@ -146,23 +149,100 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
     constexpr int ROW = I8 ? AT8_ROW : AT_ROW;
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int chunk = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
     const int g = lane >> 2, t = lane & 3;
+    const int nctas = gridDim.x * gridDim.y * gridDim.z;
+    const int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
 
-    const bool tr = FUSED && p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0;
+    const bool tr = FUSED && p.trace && bid == 0 && threadIdx.x == 0;
     if (tr) p.trace[0] = gtimer();
     if (FUSED) pdl_launch_dependents();
-    // Everything up to griddepcontrol.wait only touches state that is stable during a decode step (sequence lengths, block
-    // table, the KV of OLD tokens): the first pipeline stages of this warp's K/V stream are in flight before the producer
-    // of q (the qkv linear / the RoPE kernel) has finished.  Only the 16-token block that receives the new token waits.
-    const int seq_len = p.seq_lens[b];
-    const int nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
-    const int blk_pos = (seq_len - 1) / AT_BLK;          // block of the token appended in this step (pos = seq_len - 1)
-    const int blk0 = chunk * p.chunk_blocks;
-    const bool active = !(blk0 >= nblocks && chunk != 0);
-    const int blk1 = min(nblocks, blk0 + p.chunk_blocks);
-    const int my_n = active ? (blk1 - blk0 - warp + AT_WARPS - 1) / AT_WARPS : 0;   // blocks blk0 + warp + 4*i
+
+    // ---- work decomposition.
+    // Legacy form (p.even == 0): CTA = (chunk, kv head, sequence), one segment.
+    // Even form (fused decode step with enough work): the grid is one resident wave; the linearised space
+    //   x = (sequence b, kv head, 16-token block)   — block fastest, W = Hkv * sum_b nblocks(b) points —
+    // is cut into gridDim.x equal contiguous ranges [bid * W / n, (bid + 1) * W / n).  A CTA walks its range as up to a few
+    // SEGMENTS (a segment = a run of blocks of one (b, kv head) pair).  Every CTA streams the same number of KV bytes (+-1
+    // block), so there is no partial last wave (1280 CTAs on 296 slots = 4.32 waves cost 5) and no CTA launch/prologue per
+    // 64 blocks.  A pair that lies inside one range is finished by its CTA; a pair cut by a range boundary leaves one partial
+    // per CTA — only the first and the last segment of a range can be partial, so a CTA owns two partial slots — and the
+    // last CTA to arrive for the pair merges them (merge_cnt, as in the legacy form).
+    // Everything here depends on seq_lens only, which is stable during a decode step: it runs BEFORE griddepcontrol.wait.
+    __shared__ int s_cum[AT_EVEN_MAXB + 1];
+    __shared__ int s_wsum[AT_WARPS];
+    long long W = 0, x_lin = 0, x_hi = 0;
+    if (FUSED && p.even) {
+        int nbv = 0;
+        if (tid < p.B) nbv = max(1, (p.seq_lens[tid] + AT_BLK - 1) / AT_BLK) * p.Hkv;
+        int incl = nbv;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        int base = 0;
+        for (int w = 0; w < warp; ++w) base += s_wsum[w];
+        if (tid < p.B) s_cum[tid + 1] = base + incl;
+        if (tid == 0) s_cum[0] = 0;
+        __syncthreads();
+        W = s_cum[p.B];
+        x_lin = (long long)bid * W / nctas;
+        x_hi = (long long)(bid + 1) * W / nctas;
+    }
+    const long long range_lo = x_lin;
+    int seg_i = 0;          // segments done by this CTA
+    int b_scan = 0;         // even form: sequence of the previous segment (ranges are walked in increasing x)
+    bool waited = false;    // griddepcontrol.wait executed
     unsigned char* wsm = smem + warp * (ST * SB);
+
+    for (;; ++seg_i) {
+    // ---- this segment: blocks [blk0, blk1) of pair (b, kvh)
+    int chunk, kvh, b, seq_len, nblocks, blk0, blk1;
+    bool active, seg_direct;
+    int nch = 1, my_c = 0, seg_c0 = 0, seg_c0_which = 0;   // partials of the pair: count, this CTA's index, first CTA, its slot
+    if (!(FUSED && p.even)) {
+        if (seg_i > 0) break;
+        chunk = blockIdx.x; kvh = blockIdx.y; b = blockIdx.z;
+        seq_len = p.seq_lens[b];
+        nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
+        blk0 = chunk * p.chunk_blocks;
+        active = !(blk0 >= nblocks && chunk != 0);
+        blk1 = min(nblocks, blk0 + p.chunk_blocks);
+        seg_direct = p.direct != 0;
+        nch = (nblocks + p.chunk_blocks - 1) / p.chunk_blocks;
+        my_c = chunk;
+    } else {
+        if (x_lin >= x_hi) break;
+        while (s_cum[b_scan + 1] <= x_lin) ++b_scan;
+        b = b_scan;
+        seq_len = p.seq_lens[b];
+        nblocks = max(1, (seq_len + AT_BLK - 1) / AT_BLK);
+        const int r = (int)(x_lin - s_cum[b]);
+        kvh = r / nblocks;
+        blk0 = r - kvh * nblocks;
+        const long long left = x_hi - x_lin;
+        blk1 = (left < (long long)(nblocks - blk0)) ? blk0 + (int)left : nblocks;
+        chunk = 0;
+        active = true;
+        seg_direct = (blk0 == 0 && blk1 == nblocks);
+        if (!seg_direct) {
+            const long long pair_lo = (long long)s_cum[b] + (long long)kvh * nblocks, pair_hi = pair_lo + nblocks;
+            seg_c0 = (int)(((pair_lo + 1) * nctas - 1) / W);            // CTA whose range holds the pair's first block
+            const int c1 = (int)((pair_hi * nctas - 1) / W);             // ... and its last block
+            nch = c1 - seg_c0 + 1;
+            my_c = bid - seg_c0;
+            seg_c0_which = ((long long)seg_c0 * W / nctas == pair_lo) ? 0 : 1;   // the pair is the first segment of seg_c0's range, or a later (= its last) one
+        }
+        x_lin += blk1 - blk0;
+    }
+    // slot of partial c (0 .. nch-1) of this pair, head hh
+    auto pslot = [&](int c, int hh) -> size_t {
+        if (!(FUSED && p.even)) return ((size_t)b * p.H + (size_t)kvh * p.G + hh) * p.max_chunks + c;
+        const int which = (c == 0) ? seg_c0_which : 0;               // every later CTA starts its range inside the pair
+        return ((size_t)(seg_c0 + c) * 2 + which) * 8 + hh;
+    };
+    const int mstride = (FUSED && p.even) ? nch : p.max_chunks;       // row stride of the merge scratch in shared memory
+    const int blk_pos = (seq_len - 1) / AT_BLK;          // block of the token appended in this step (pos = seq_len - 1)
+    const int my_n = active ? (blk1 - blk0 - warp + AT_WARPS - 1) / AT_WARPS : 0;   // blocks blk0 + warp + 4*i
     const int32_t* bt = p.block_table + (size_t)b * p.max_blocks;
 
     int pg_next;
@@ -222,21 +302,18 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
         }
         cp_async_commit();
     };
-    int pre = 0;   // stages issued before the dependency wait
-    while (pre < ST - 1 && (pre >= my_n || blk0 + warp + AT_WARPS * pre < blk_pos)) { issue(pre); ++pre; }
-
-    pdl_wait_prior();
-    if (tr) p.trace[1] = gtimer();
-    if (FUSED && p.zero0) {
-        const int nb = gridDim.x * gridDim.y * gridDim.z;
-        const int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-        for (int i = (bid * AT_WARPS * 32 + tid) * 4; i < p.zero0_n; i += nb * AT_WARPS * 32 * 4)
-            *reinterpret_cast<float4*>(p.zero0 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+    int pre = 0;   // stages issued before the dependency wait (first segment only)
+    if (!waited) {
+        while (pre < ST - 1 && (pre >= my_n || blk0 + warp + AT_WARPS * pre < blk_pos)) { issue(pre); ++pre; }
+        pdl_wait_prior();
+        waited = true;
+        if (tr) p.trace[1] = gtimer();
+        if (FUSED && p.zero0) {
+            for (int i = (bid * AT_WARPS * 32 + tid) * 4; i < p.zero0_n; i += nctas * AT_WARPS * 32 * 4)
+                *reinterpret_cast<float4*>(p.zero0 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
     }
-    if (!active) {
-        if (FUSED && p.signal_flag >= 0) tp_signal_grid_done(p.tp, p.signal_flag, gridDim.x * gridDim.y * gridDim.z);
-        return;
-    }
+    if (!active) break;
 
     // ---- Q fragments (rows g < G valid; rows 8..15 are zero padding)
     uint32_t qa[8][2];
@@ -545,20 +622,19 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
                 O += mo[(w * 8 + hh) * AT_D + d] * f;
             }
             const int h = kvh * p.G + hh;
-            if (p.direct) {
+            if (seg_direct) {
                 attn_store(p, b, h, d, (L > 0.f) ? O / L : 0.f);
             } else {
-                const size_t slot = ((size_t)b * p.H + h) * p.max_chunks + chunk;
+                const size_t slot = pslot(my_c, hh);
                 p.part_o[slot * AT_D + d] = O;
                 if (d == 0) { p.part_ml[slot * 2] = M; p.part_ml[slot * 2 + 1] = L; }
             }
         }
     }
     if (tr) p.trace[4] = gtimer();
-    if (FUSED && !p.direct) {
+    if (FUSED && !seg_direct) {
         // the last chunk to arrive for this (sequence, kv head) merges all of them — no separate merge launch
         __shared__ int s_last;
-        const int nch = (nblocks + p.chunk_blocks - 1) / p.chunk_blocks;
         __threadfence();
         __syncthreads();
         if (tid == 0) {
@@ -572,26 +648,26 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
             __threadfence();
             // (m, l) of every (head, chunk) pair: one parallel round of loads into smem, factors computed once
             float* fml = reinterpret_cast<float*>(smem);            // [G][nch][2] -> factor, unused
-            float* fL = fml + 2 * 8 * p.max_chunks;                 // [G] total l
+            float* fL = fml + 2 * 8 * mstride;                      // [G] total l
             for (int i = tid; i < p.G * nch; i += AT_WARPS * 32) {
                 const int hh = i / nch, c = i - hh * nch;
-                const size_t slot = ((size_t)b * p.H + kvh * p.G + hh) * p.max_chunks + c;
+                const size_t slot = pslot(c, hh);
                 float2 ml;
                 asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(ml.x), "=f"(ml.y) : "l"(p.part_ml + slot * 2));
-                fml[(hh * p.max_chunks + c) * 2] = ml.x;
-                fml[(hh * p.max_chunks + c) * 2 + 1] = ml.y;
+                fml[(hh * mstride + c) * 2] = ml.x;
+                fml[(hh * mstride + c) * 2 + 1] = ml.y;
             }
             __syncthreads();
             if (tid < p.G) {
                 const int hh = tid;
                 float M = -INFINITY;
-                for (int c = 0; c < nch; ++c) M = fmaxf(M, fml[(hh * p.max_chunks + c) * 2]);
+                for (int c = 0; c < nch; ++c) M = fmaxf(M, fml[(hh * mstride + c) * 2]);
                 float L = 0.f;
                 for (int c = 0; c < nch; ++c) {
-                    const float mc = fml[(hh * p.max_chunks + c) * 2];
+                    const float mc = fml[(hh * mstride + c) * 2];
                     const float f = (mc == -INFINITY) ? 0.f : exp2f(mc - M);
-                    L += fml[(hh * p.max_chunks + c) * 2 + 1] * f;
-                    fml[(hh * p.max_chunks + c) * 2] = f;
+                    L += fml[(hh * mstride + c) * 2 + 1] * f;
+                    fml[(hh * mstride + c) * 2] = f;
                 }
                 fL[hh] = L;
             }
@@ -599,15 +675,14 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
             const int d = tid;
             for (int hh = 0; hh < p.G; ++hh) {
                 const int h = kvh * p.G + hh;
-                const size_t base = ((size_t)b * p.H + h) * p.max_chunks;
                 float O = 0.f;
                 for (int c0 = 0; c0 < nch; c0 += 8) {   // 8 independent loads in flight
                     float v[8];
 #pragma unroll
-                    for (int u = 0; u < 8; ++u) v[u] = (c0 + u < nch) ? ldcg_f(p.part_o + (base + c0 + u) * AT_D + d) : 0.f;
+                    for (int u = 0; u < 8; ++u) v[u] = (c0 + u < nch) ? ldcg_f(p.part_o + pslot(c0 + u, hh) * AT_D + d) : 0.f;
 #pragma unroll
                     for (int u = 0; u < 8; ++u)
-                        if (c0 + u < nch) O += v[u] * fml[(hh * p.max_chunks + c0 + u) * 2];
+                        if (c0 + u < nch) O += v[u] * fml[(hh * mstride + c0 + u) * 2];
                 }
                 const float L = fL[hh];
                 attn_store(p, b, h, d, (L > 0.f) ? O / L : 0.f);
@@ -615,7 +690,16 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
         }
     }
     if (tr) p.trace[5] = gtimer();
-    if (FUSED && p.signal_flag >= 0) tp_signal_grid_done(p.tp, p.signal_flag, gridDim.x * gridDim.y * gridDim.z);
+    __syncthreads();   // the next segment's K/V ring (and its q fragments) reuse the shared memory the merge just read
+    }   // segment loop
+    if (!waited) {     // a CTA without work (legacy form: chunk past the sequence; even form: empty range) still owes the dependency
+        pdl_wait_prior();   // wait and its share of the accumulator clearing
+        if (FUSED && p.zero0) {
+            for (int i = (bid * AT_WARPS * 32 + tid) * 4; i < p.zero0_n; i += nctas * AT_WARPS * 32 * 4)
+                *reinterpret_cast<float4*>(p.zero0 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    if (FUSED && p.signal_flag >= 0) tp_signal_grid_done(p.tp, p.signal_flag, nctas);
     if (!FUSED) pdl_launch_dependents();
 }
 
@@ -810,7 +894,24 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     p.page_shift = -1;
     if ((p.page_size & (p.page_size - 1)) == 0) { p.page_shift = 0; while ((1 << p.page_shift) < p.page_size) ++p.page_shift; }
     p.direct = (nchunks <= 1);
-    if (!p.direct) {
+    // Even work split (see the kernel): the fused decode form with at least 512 tokens of KV per CTA of one resident wave.
+    const bool fused_form = p.qkv_acc != nullptr && p.merge_cnt != nullptr;
+    const bool i8_pool = p.kv_scales != nullptr;
+    static const int even_env = getenv("WF_ATTN_EVEN") ? atoi(getenv("WF_ATTN_EVEN")) : 1;
+    int even_ctas = 0;
+    p.even = 0;
+    if (fused_form && even_env && p.B <= AT_EVEN_MAXB) {
+        long long nc = pairs * max_blocks16 / 32;
+        const long long slots = (long long)(i8_pool ? 3 : 2) * sm_count();
+        if (nc > slots) nc = slots;
+        const size_t need = (size_t)nc * 2 * 8 * (AT_D + 2) * sizeof(float);
+        if (nc >= sm_count() && workspace && workspace_bytes >= need) {
+            p.even = 1; p.direct = 0; even_ctas = (int)nc;
+            p.part_o = (float*)workspace;
+            p.part_ml = p.part_o + (size_t)nc * 2 * 8 * AT_D;
+        }
+    }
+    if (!p.direct && !p.even) {
         const size_t need = (size_t)p.B * p.H * nchunks * (AT_D + 2) * sizeof(float);
         if (!workspace || workspace_bytes < need) { set_error("paged_decode_attn: workspace too small (%zu < %zu)", workspace_bytes, need); return WF_ERR_INVALID; }
         p.part_o = (float*)workspace;
@@ -821,7 +922,7 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     at[0].val.programmaticStreamSerializationAllowed = 1;
     {
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(nchunks < 1 ? 1 : nchunks, p.Hkv, p.B);
+        cfg.gridDim = p.even ? dim3(even_ctas) : dim3(nchunks < 1 ? 1 : nchunks, p.Hkv, p.B);
         cfg.blockDim = dim3(AT_WARPS * 32);
         const bool i8 = p.kv_scales != nullptr;
         cfg.dynamicSmemBytes = i8 ? AT8_SMEM : AT_SMEM;
@@ -965,7 +1066,10 @@ extern "C" int wf_rope_kv_append(const void* qkv, int B, int H, const wf_kv_layo
 
 extern "C" size_t wf_attn_workspace_bytes(int B, int H, int head_dim, int max_seq) {
     const size_t chunks = (size_t)(max_seq + 63) / 64 + 1;
-    return (size_t)B * H * chunks * (head_dim + 2) * sizeof(float);
+    const size_t legacy = (size_t)B * H * chunks * (head_dim + 2) * sizeof(float);
+    // even work split: two partial slots of 8 heads per CTA of one resident wave (<= 3 CTAs on each of <= 160 SMs)
+    const size_t even = (size_t)3 * 160 * 2 * 8 * (head_dim + 2) * sizeof(float);
+    return legacy > even ? legacy : even;
 }
 
 extern "C" int wf_paged_decode_attn(const void* q, const wf_kv_layout* kv, int layer, const int32_t* block_table, int max_blocks,

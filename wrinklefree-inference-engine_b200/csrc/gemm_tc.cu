@@ -195,47 +195,62 @@ __global__ void __launch_bounds__(tc_threads(NU), 1) ternary_gemm_tc_kernel(cons
         }
     } else if (warp == W_MMA) {
         // ------------------------------------------------------------ MMA issuer (whole warp walks the loop, lane 0 issues)
-        // Everything the issue loop needs is a register + immediate: a long dependent chain of address arithmetic per
-        // tcgen05.mma would pace the tensor pipe (measured: ~850 clk per stage against a 256-clk floor).
+        // The issue loop IS the pace of this kernel when it is long: ncu (profiles/r02_full_gemm_tc_noepi) showed ~75 dependent
+        // SASS instructions per stage (R2UR moves, address arithmetic, one ELECT waterfall per tcgen05 instruction) = ~500 clk
+        // against the 256-clk tensor time of a stage, with every other role waiting on this warp.  So the ring position is a
+        // compile-time constant here (the loop walks items in groups of TC_STAGES): operand descriptors and barrier addresses
+        // are base + immediate, and the only per-stage arithmetic left is the tile bookkeeping.
         constexpr uint32_t idesc = tc_idesc(TC_BM, TC_BN);
         const uint64_t bdesc0 = tc_smem_desc_sw128(ring);
-        const uint32_t a_tmem0 = tmem + TC_A_COL0;
+        const uint32_t a_tmem0 = __shfl_sync(0xffffffffu, tmem, 0) + TC_A_COL0;
         const uint32_t full0 = smem_u32(&full_bar[0]), empty0 = smem_u32(&empty_bar[0]);
-        int s = 0;
-        uint32_t ph = 0;
-        for (int tl = 0; tl < my_tiles; ++tl) {
-            const int buf = tl & 1;
-            mbar_wait(&tempty_bar[buf], (uint32_t)(((tl >> 1) & 1) ^ 1));
-            tc_fence_after();
-            const uint32_t d_tmem = tmem + buf * TC_BN;
-            for (int kb = 0; kb < KBs; ++kb) {
-                {   // wait for the TMA bytes and the four unpack warps of this stage
-                    uint32_t ok;
-                    do {
-                        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                                     : "=r"(ok) : "r"(full0 + s * 8), "r"(ph) : "memory");
-                    } while (!ok);
+        const uint32_t tfull0 = smem_u32(&tfull_bar[0]);
+        // One ELECTED thread runs the whole loop (elect.sync, not `lane == 0`: ptxas then knows the region is single-threaded
+        // and issues the tcgen05 instructions straight from uniform registers instead of one ELECT waterfall loop each).
+        uint32_t elected;
+        asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(elected));
+        if (elected) {
+            uint32_t ph = 0;
+            int kb = 0, tl = 0;            // position inside the current tile, tile index
+            uint32_t d_tmem = a_tmem0 - TC_A_COL0;
+            for (int i0 = 0; i0 < n_items; i0 += TC_STAGES) {
+#pragma unroll
+                for (int s = 0; s < TC_STAGES; ++s) {
+                    if (i0 + s < n_items) {
+                        if (kb == 0) {   // a new tile: its accumulator buffer must have been drained by the epilogue warps
+                            const int buf = tl & 1;
+                            mbar_wait(&tempty_bar[buf], (uint32_t)(((tl >> 1) & 1) ^ 1));
+                            d_tmem = a_tmem0 - TC_A_COL0 + buf * TC_BN;
+                        }
+                        {   // wait for the TMA bytes and the four unpack warps of this stage
+                            uint32_t ok;
+                            do {
+                                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                                             : "=r"(ok) : "r"(full0 + s * 8), "r"(ph) : "memory");
+                            } while (!ok);
+                        }
+                        tc_fence_after();
+                        const uint64_t bd = bdesc0 + (uint64_t)(s * (TC_STAGE_BYTES >> 4));
+                        const uint32_t at = a_tmem0 + s * TC_A_COLS;
+                        tc_mma_i8_ts(d_tmem, at, bd, idesc, kb != 0 ? 1u : 0u);
+                        tc_mma_i8_ts(d_tmem, at + 8, bd + 2, idesc, 1u);
+                        tc_mma_i8_ts(d_tmem, at + 16, bd + 4, idesc, 1u);
+                        tc_mma_i8_ts(d_tmem, at + 24, bd + 6, idesc, 1u);
+                        if (CL == 1)
+                            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(empty0 + s * 8) : "memory");
+                        else   // the slot is refilled by every CTA of the cluster: tell all of them
+                            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                                         ::"r"(empty0 + s * 8), "h"((uint16_t)((1u << CL) - 1)) : "memory");
+                        if (++kb == KBs) {
+                            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(tfull0 + (tl & 1) * 8) : "memory");
+                            kb = 0; ++tl;
+                        }
+                    }
                 }
-                tc_fence_after();
-                if (lane == 0) {
-                    const uint64_t bd = bdesc0 + (uint64_t)(s * (TC_STAGE_BYTES >> 4));
-                    const uint32_t at = a_tmem0 + s * TC_A_COLS;
-                    tc_mma_i8_ts(d_tmem, at, bd, idesc, kb != 0 ? 1u : 0u);
-                    tc_mma_i8_ts(d_tmem, at + 8, bd + 2, idesc, 1u);
-                    tc_mma_i8_ts(d_tmem, at + 16, bd + 4, idesc, 1u);
-                    tc_mma_i8_ts(d_tmem, at + 24, bd + 6, idesc, 1u);
-                    if (CL == 1)
-                        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(empty0 + s * 8) : "memory");
-                    else   // the slot is refilled by every CTA of the cluster: tell all of them
-                        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                                     ::"r"(empty0 + s * 8), "h"((uint16_t)((1u << CL) - 1)) : "memory");
-                }
-                __syncwarp();
-                if (++s == TC_STAGES) { s = 0; ph ^= 1u; }
+                ph ^= 1u;
             }
-            if (lane == 0) tc_commit(&tfull_bar[buf]);
-            __syncwarp();
         }
+        __syncwarp();
     } else if (warp >= TC_EPW) {
         // ------------------------------------------------------------ unpack warps: 2-bit weights -> u8 codes -> TMEM
         const int q = warp & 3, grp = (warp - TC_EPW) >> 2;
