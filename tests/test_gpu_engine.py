@@ -123,10 +123,13 @@ def test_full_size_2b_step_runs_and_is_finite():
     eng.close()
 
 
-def _run_tokens(cfg, w, fused, steps, monkeypatch, ctx=None, synthetic=None):
+def _run_tokens(cfg, w, fused, steps, monkeypatch, ctx=None, synthetic=None, even="0", taps=()):
     """logits of every step from a fresh engine built with WF_FUSED=fused"""
     from wf_bitnet.engine import Engine
     monkeypatch.setenv("WF_FUSED", "1" if fused else "0")
+    # bit-identity across the two step forms needs the same split of the softmax sums in both: the even work split of the fused
+    # attention (one resident wave, range boundaries anywhere) changes the fp32 summation order, so it is compared on its own below
+    monkeypatch.setenv("WF_ATTN_EVEN", even)
     eng = Engine(cfg)
     if synthetic is not None:
         eng.init_synthetic(synthetic)
@@ -139,9 +142,34 @@ def _run_tokens(cfg, w, fused, steps, monkeypatch, ctx=None, synthetic=None):
     outs = []
     for toks in steps:
         nxt = eng.decode(toks)
-        outs.append((eng.buffer("logits", (cfg.max_batch, cfg.vocab), torch.float32)[:B].cpu(), nxt.copy(), eng.launches_per_step()))
+        outs.append((eng.buffer("logits", (cfg.max_batch, cfg.vocab), torch.float32)[:B].cpu(), nxt.copy(), eng.launches_per_step()) +
+                    tuple(eng.buffer(n, sh, dt).cpu() for (n, sh, dt) in taps))
     eng.close()
     return outs
+
+
+@pytest.mark.parametrize("B,ctx,kv", [(64, 300, "bf16"), (16, 1200, "bf16"), (64, 1800, "bf16"), (33, 1500, "int8")])
+def test_attention_even_split_matches_chunked_split(B, ctx, kv, monkeypatch):
+    """The fused attention's even work split (one resident wave of CTAs, each an equal contiguous range of the (sequence, kv head,
+    block) space, partials merged by the last CTA of a pair) against the chunked grid on the same engine state: the two differ only
+    in where the online-softmax partial sums are cut, i.e. by fp32 summation order — the bf16 attention output of a 1-layer model
+    must agree to a bf16 ulp or two, and the greedy tokens must be the same."""
+    from wf_bitnet.engine import EngineConfig
+    cfg = EngineConfig.bitnet_2b(max_seq=2048, max_batch=B, layers=1, vocab=4096)
+    if kv == "int8":
+        cfg.kv_dtype = "int8"
+    rng = np.random.default_rng(70 + B)
+    steps = [list(map(int, rng.integers(0, cfg.vocab, B))) for _ in range(2)]
+    taps = (("attn", (cfg.max_batch, cfg.heads * cfg.head_dim), torch.bfloat16),)
+    a = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=ctx, synthetic=5, even="1", taps=taps)
+    b = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=ctx, synthetic=5, even="0", taps=taps)
+    (la, na, _, xa), (lb, nb, _, xb) = a[0], b[0]
+    xa, xb = xa[:B].float(), xb[:B].float()
+    assert torch.isfinite(xa).all() and xa.abs().max() > 0
+    err = (xa - xb).abs().max().item()
+    assert err <= 2.0 ** -7 * xb.abs().max().item(), err          # bf16: 8 significant bits
+    assert (xa != xb).float().mean().item() < 0.2                # most elements round to the same bf16
+    assert (na == nb).all()
 
 
 @pytest.mark.parametrize("B", [1, 3, 8, 12, 33, 40, 64])

@@ -34,6 +34,11 @@ for l in (1, 2, 3):
         print(f"   {names[pi]:8s} barrier {b-prev:6.2f} | glue {g-b:6.2f} | first stage wait {w-g:6.2f} | main loop {m-w:6.2f} | epilogue {ep-m:6.2f} | phase total {ep-prev:6.2f}")
         prev = ep
     print(f"   tail total (entry -> last epilogue) {prev-e0:7.2f};  attention of layer {l+1}: entry {attn[l+1][0]-prev:6.2f} after, its end {attn[l+1][5]-prev:6.2f} after; next tail entry {tail[l+1][0]-prev:6.2f} after")
+print("fused attention kernel, CTA 0 (us): entry -> dependency wait done -> q/RoPE/append done -> KV stream done -> CTA merge / store done -> end")
+for l in (2, 3, 4):
+    t = attn[l]
+    print(f"layer {l}: wait {t[1]-t[0]:6.2f} | prologue {t[2]-t[1]:6.2f} | stream {t[3]-t[2]:6.2f} | merge+store {t[4]-t[3]:6.2f} | chunk merge {t[5]-t[4]:6.2f} | total {t[5]-t[0]:6.2f};"
+          f"  entry {t[0]-tail[l-1][21]:6.2f} after the previous tail's last epilogue, next tail's dependency done {tail[l][1]-t[5]:6.2f} after its end")
 tot = [tail[l][21] - tail[l][1] for l in range(1, L - 1)]
 att = [tail[l + 1][1] - tail[l][21] for l in range(1, L - 2)]
 print(f"median over layers: tail (dependency done -> last epilogue) {np.median(tot):.2f} us; gap tail end -> next tail's dependency done (attention) {np.median(att):.2f} us")

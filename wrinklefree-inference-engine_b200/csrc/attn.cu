@@ -98,6 +98,7 @@ struct AttnParams {
     float* part_o;               // [B][H][max_chunks][D]
     float* part_ml;              // [B][H][max_chunks][2]
     int direct;                  // 1: single chunk per sequence everywhere -> write final output
+    int chunk_major;             // legacy grid order: 1 = (kv head, sequence, chunk), 0 = (chunk, kv head, sequence)
     int even;                    // 1 (fused form only): the grid is ONE wave of persistent CTAs and the (sequence, kv head, block) space is cut
                                  // into gridDim.x equal contiguous ranges (see the kernel); chunk_blocks / max_chunks / direct are unused
     // ---- fused prologue / epilogue (decode engine): q, k, v come straight from the qkv linear's raw accumulator
@@ -201,7 +202,9 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
     int nch = 1, my_c = 0, seg_c0 = 0, seg_c0_which = 0;   // partials of the pair: count, this CTA's index, first CTA, its slot
     if (!(FUSED && p.even)) {
         if (seg_i > 0) break;
-        chunk = blockIdx.x; kvh = blockIdx.y; b = blockIdx.z;
+        // chunk index slowest in the dispatch order: the last (shortest) chunk of every sequence forms the final partial wave
+        if (p.chunk_major) { kvh = blockIdx.x; b = blockIdx.y; chunk = blockIdx.z; }
+        else { chunk = blockIdx.x; kvh = blockIdx.y; b = blockIdx.z; }
         seq_len = p.seq_lens[b];
         nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
         blk0 = chunk * p.chunk_blocks;
@@ -897,7 +900,10 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     // Even work split (see the kernel): the fused decode form with at least 512 tokens of KV per CTA of one resident wave.
     const bool fused_form = p.qkv_acc != nullptr && p.merge_cnt != nullptr;
     const bool i8_pool = p.kv_scales != nullptr;
-    static const int even_env = getenv("WF_ATTN_EVEN") ? atoi(getenv("WF_ATTN_EVEN")) : 1;
+    const char* even_s = getenv("WF_ATTN_EVEN");   // read per launch (launches are graph-captured): tests switch it inside one process
+    const int even_env = even_s ? atoi(even_s) : 0;   // opt-in: measured 5.65 vs 5.46 ms per bs64/4K step (profiles/r02i_*): the per-segment
+                                                       // prologue / merge of a CTA costs what the missing partial wave saves
+    { const char* cm = getenv("WF_ATTN_CHUNK_MAJOR"); p.chunk_major = cm ? atoi(cm) : 1; }
     int even_ctas = 0;
     p.even = 0;
     if (fused_form && even_env && p.B <= AT_EVEN_MAXB) {
@@ -922,7 +928,8 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     at[0].val.programmaticStreamSerializationAllowed = 1;
     {
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = p.even ? dim3(even_ctas) : dim3(nchunks < 1 ? 1 : nchunks, p.Hkv, p.B);
+        const int nchg = nchunks < 1 ? 1 : nchunks;
+        cfg.gridDim = p.even ? dim3(even_ctas) : (p.chunk_major ? dim3(p.Hkv, p.B, nchg) : dim3(nchg, p.Hkv, p.B));
         cfg.blockDim = dim3(AT_WARPS * 32);
         const bool i8 = p.kv_scales != nullptr;
         cfg.dynamicSmemBytes = i8 ? AT8_SMEM : AT_SMEM;

@@ -78,10 +78,12 @@ struct wf_engine {
     int hx = 1;              // relu^2(gate)*up in its own small kernel instead of every down-proj CTA's prologue (WF_HX=0 to fold it back)
     int decode_tc = 0;       // WF_DECODE_TC=1: batched decode linears (B > 32) on tcgen05 split-K REDs instead of the mma.sync one-shot GEMM (parity-identical; measured equal in step time, both latency-bound — see DESIGN.md)
     int tail_batch = 0;      // WF_TAIL_BATCH=1: the same for 8 < B <= 64 (layer_tail_batch.cu).  Opt-in: measured 5.74 ms vs 5.44 ms per bs64/4K step for the phase path (profiles/r02d_*)
+    int small_max = 8;       // WF_SMALL_MAX: largest batch on the GEMV-style kernels (linear_small / layer_tail: the row glue runs per CTA and per row,
+                             // ~3 us x B x 4 phases per layer); above it the batched kernels (row glue once per row in its own CTA + batched GEMM)
     int tail = 1;            // 1: persistent layer-tail kernel (layer_tail.cu) for B <= 8 on single-GPU engines: 2 launches per layer (WF_TAIL=0: phase kernels)
     // grid-barrier arrival counters, one set per launch site, and the epoch (steps so far) of each kernel family:
     // [0] layer_tail_kernel (B <= 8, LT_MAX_PHASES slots per site), [1] layer_tail_batch_kernel (B > 8, 2 * LT_MAX_PHASES slots)
-    unsigned long long* tail_bar[2] = {nullptr, nullptr};
+    unsigned int* tail_bar[2] = {nullptr, nullptr};
     int* tail_epoch = nullptr;   // [2]
     int fused = 1;           // 1: phase kernels (linear_small / glue_rows + gemm_oneshot / fused attention); 0: one kernel per op
     // fused path state: raw fp32 accumulators of the four linears, their per-token activation scale / Sigma a,
@@ -208,7 +210,7 @@ bool tail_path_ok(const wf_engine* e, int B) {
     int maxK = e->hidden;
     if (e->attn_full > maxK) maxK = e->attn_full;
     if (e->ffn_full > maxK) maxK = e->ffn_full;
-    if (B > 8) return e->tail_batch && layer_tail_batch_fits(B, maxK) && B <= sm_count();
+    if (B > e->small_max) return e->tail_batch && layer_tail_batch_fits(B, maxK) && B <= sm_count();
     const int sms = sm_count();
     int maxrb = (e->qkv_rows / 16 + sms - 1) / sms;
     const int gu = ((e->ffn / 16 + sms - 1) / sms) * 2;
@@ -226,10 +228,10 @@ int run_step_tail(wf_engine* e, int B, int feed_back) {
     int32_t* rs[4] = {e->lin_rs, e->lin_rs + MB, e->lin_rs + 2 * MB, e->lin_rs + 3 * MB};
     __nv_bfloat16 *hA = e->hid, *hB = e->hid2;
     int rc;
-    const int fam = B <= 8 ? 0 : 1;
+    const int fam = B <= e->small_max ? 0 : 1;
     auto base = [&](int site) {
         TailArgs t = {};
-        t.M = B; t.bar = e->tail_bar[fam] + (size_t)site * LT_MAX_PHASES * (fam + 1); t.epoch = e->tail_epoch + fam; t.err = e->d_err;
+        t.M = B; t.bar = e->tail_bar[fam] + (size_t)site * LT_MAX_PHASES * (fam + 1) * LT_BAR_WORDS; t.epoch = e->tail_epoch + fam; t.err = e->d_err;
         if (e->trace && site < c.layers) t.trace = e->trace + (size_t)32 * site;
         return t;
     };
@@ -343,7 +345,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
     // Row-parallel linears (o, down) under TP.  B <= 8: every CTA's prologue needs the whole reduced vector locally -> all-reduce
     // (RED into every rank).  B > 8: reduce-scatter (RED into the owner of the column only, 1/T of the NVLink packets) and the
     // per-row glue of the consumer pulls each column from its owner.
-    const bool scatter = tp && B > 8 && (e->hidden % (8 * T)) == 0;
+    const bool scatter = tp && B > e->small_max && (e->hidden % (8 * T)) == 0;
     const int own_cols = scatter ? e->hidden / T : 0;
     auto local_dest = [&](float* acc) { TpDest d = {}; d.n = 1; d.acc[0] = acc; d.signal_flag = -1; return d; };
     auto all_dest = [&](size_t off, int flag) {
@@ -360,7 +362,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
     auto phase = [&](GlueParams g, const uint8_t* w, int N, int Kfull, int K, int k_off, const TpDest& dest, int slot, bool first) -> int {
         g.M = B; g.K = Kfull; g.eps = c.eps; g.tp = e->tp;
         if (e->trace) { g.trace = e->trace + (size_t)trace_slot * 32; ++trace_slot; }
-        if (B <= 8 && linear_small_fits(B, Kfull)) {
+        if (B <= e->small_max && linear_small_fits(B, Kfull)) {
             SmallLinArgs a;
             a.g = g; a.w = w; a.N = N; a.K = K; a.k_off = k_off; a.dest = dest; a.acc_ld = N; a.lin_ascale = asc[slot]; a.lin_rowsum = rs[slot];
             return launch_linear_small(a, s, pdl && !first);
@@ -584,6 +586,7 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     if (T > 1) e->fused = 1;                   // the exchanges live in the phase kernels
     { const char* x = getenv("WF_HX"); if (x) e->hx = atoi(x) != 0; }
     { const char* x = getenv("WF_TAIL"); if (x) e->tail = atoi(x) != 0; }
+    { const char* x = getenv("WF_SMALL_MAX"); if (x) { e->small_max = atoi(x); if (e->small_max < 0) e->small_max = 0; if (e->small_max > 8) e->small_max = 8; } }
     { const char* x = getenv("WF_TAIL_BATCH"); if (x) e->tail_batch = atoi(x) != 0; }
     { const char* x = getenv("WF_DECODE_TC"); if (x) e->decode_tc = atoi(x) != 0; }
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
@@ -691,10 +694,11 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
         (rc = dalloc(e, &e->acc_gu, (size_t)B * 2 * e->ffn)) ||
         (rc = dalloc(e, &e->lin_asc, (size_t)4 * B)) || (rc = dalloc(e, &e->lin_rs, (size_t)4 * B)) ||
         (rc = dalloc(e, &e->hid2, (size_t)B * e->hidden)) || (rc = dalloc(e, &e->merge_cnt, (size_t)B * e->Hkv))) return fail(rc);
-    if ((rc = dalloc(e, &e->tail_bar[0], (size_t)(c.layers + 1) * LT_MAX_PHASES)) || (rc = dalloc(e, &e->tail_bar[1], (size_t)(c.layers + 1) * 2 * LT_MAX_PHASES)) ||
+    if ((rc = dalloc(e, &e->tail_bar[0], (size_t)(c.layers + 1) * LT_MAX_PHASES * LT_BAR_WORDS)) ||
+        (rc = dalloc(e, &e->tail_bar[1], (size_t)(c.layers + 1) * 2 * LT_MAX_PHASES * LT_BAR_WORDS)) ||
         (rc = dalloc(e, &e->tail_epoch, 2))) return fail(rc);
-    if (cuda_check(cudaMemset(e->tail_bar[0], 0, (size_t)(c.layers + 1) * LT_MAX_PHASES * 8), "bar memset") ||
-        cuda_check(cudaMemset(e->tail_bar[1], 0, (size_t)(c.layers + 1) * 2 * LT_MAX_PHASES * 8), "bar memset") ||
+    if (cuda_check(cudaMemset(e->tail_bar[0], 0, (size_t)(c.layers + 1) * LT_MAX_PHASES * LT_BAR_WORDS * 4), "bar memset") ||
+        cuda_check(cudaMemset(e->tail_bar[1], 0, (size_t)(c.layers + 1) * 2 * LT_MAX_PHASES * LT_BAR_WORDS * 4), "bar memset") ||
         cuda_check(cudaMemset(e->tail_epoch, 0, 8), "epoch memset")) return fail(WF_ERR_CUDA);
     if (cuda_check(cudaMemset(e->acc_qkv, 0, (size_t)B * e->qkv_rows * 4), "acc memset") ||
         cuda_check(cudaMemset(e->acc_gu, 0, (size_t)B * 2 * e->ffn * 4), "acc memset") ||

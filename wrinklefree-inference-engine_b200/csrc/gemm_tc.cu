@@ -253,53 +253,63 @@ __global__ void __launch_bounds__(tc_threads(NU), 1) ternary_gemm_tc_kernel(cons
         __syncwarp();
     } else if (warp >= TC_EPW) {
         // ------------------------------------------------------------ unpack warps: 2-bit weights -> u8 codes -> TMEM
+        // The SM is ISSUE-bound in this kernel (unpack + epilogue + issue ~ 1100 warp instructions per 256-clk stage against
+        // 4 issue slots per clk), so the per-item path is kept to the loads, the 7 x 8 shift/mask instructions, one tcgen05.st
+        // and pointer / ring-slot increments: no multiplications, no divisions, no per-item tile arithmetic.
         const int q = warp & 3, grp = (warp - TC_EPW) >> 2;
         const uint32_t lane_base = (uint32_t)(q * 32) << 16;
         const int K4 = p.K / 4;
         uint32_t pre[TC_PF][8];
-        int pending = -1;
-        // loads are issued strictly in item order: (tile, k-block) of the next load is tracked incrementally and the
-        // row's base pointer only changes at a tile boundary (keeps divisions out of the per-stage path)
-        int ld_item = grp, ld_kb = grp, ld_tl = 0;   // this group's items: grp, grp + NU, ...
         const bool i2s = p.w_layout == WF_W_I2S;
         const uint32_t kb_stride = i2s ? 32u : (uint32_t)WF_TILE_BYTES;
-        const uint8_t* rowbase = p.w;
-        auto set_tile = [&](int tl) {
+        // ---- load cursor: (tile, k-block, pointer) of the next item this group fetches; items of a group are NU apart
+        int l_tl = 0, l_kb = grp;
+        const uint8_t* l_src = p.w;
+        bool l_valid = true;
+        auto seek = [&]() {   // off the per-item path: tile boundary (or start)
+            while (l_kb >= KBs) { l_kb -= KBs; ++l_tl; }
+            l_valid = l_tl < my_tiles;
+            if (!l_valid) return;
             int m_blk, n_blk, ks;
-            tile_coords(tl, m_blk, n_blk, ks);
+            tile_coords(l_tl, m_blk, n_blk, ks);
             int row = n_blk * TC_BM + q * 32 + lane;
             if (row >= p.N) row = p.N - 1;   // padded rows compute garbage that the epilogue masks
             // b200_tile_v1: word (16*(r&7) + 4*(j&3) + 2*(j>>2) + (r>>3)) of tile (row/16, kb) holds packed bytes [4j,4j+4) of row r
-            rowbase = i2s ? p.w + (size_t)row * K4
-                          : p.w + (size_t)(row >> 4) * p.KB * WF_TILE_BYTES + (size_t)(16 * (row & 7) + ((row >> 3) & 1)) * 4;
-            rowbase += (size_t)ks * KBs * kb_stride;   // this tile's K run
+            const uint8_t* rowbase = i2s ? p.w + (size_t)row * K4
+                                         : p.w + (size_t)(row >> 4) * p.KB * WF_TILE_BYTES + (size_t)(16 * (row & 7) + ((row >> 3) & 1)) * 4;
+            l_src = rowbase + ((size_t)ks * KBs + l_kb) * kb_stride;   // this tile's K run, this group's first k-block in it
         };
-        while (ld_kb >= KBs) { ld_kb -= KBs; ++ld_tl; }
-        set_tile(ld_tl);
+        seek();
         auto load_item = [&](uint32_t (&r)[8]) {
-            if (ld_item >= n_items) return;
-            const uint8_t* src = rowbase + (size_t)ld_kb * kb_stride;
+            if (!l_valid) return;
             if (i2s) {
-                const uint4 a = __ldg(reinterpret_cast<const uint4*>(src)), b = __ldg(reinterpret_cast<const uint4*>(src) + 1);
+                const uint4 a = __ldg(reinterpret_cast<const uint4*>(l_src)), b = __ldg(reinterpret_cast<const uint4*>(l_src) + 1);
                 r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w; r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
             } else {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) r[j] = __ldg(reinterpret_cast<const uint32_t*>(src) + 4 * (j & 3) + 2 * (j >> 2));
+                for (int j = 0; j < 8; ++j) r[j] = __ldg(reinterpret_cast<const uint32_t*>(l_src) + 4 * (j & 3) + 2 * (j >> 2));
             }
-            ld_item += NU;
-            ld_kb += NU;
-            if (ld_kb >= KBs) {
-                do { ld_kb -= KBs; ++ld_tl; } while (ld_kb >= KBs);
-                set_tile(ld_tl);
-            }
+            l_kb += NU;
+            l_src += NU * kb_stride;
+            if (l_kb >= KBs) seek();
         };
 #pragma unroll
         for (int u = 0; u < TC_PF; ++u) load_item(pre[u]);
+        // ---- ring cursor of the item being written: slot = item % TC_STAGES, parity of its use count
+        uint32_t slot = (uint32_t)grp, par = 1u;       // first pass over the ring waits on parity 1 (fresh barriers: returns at once)
+        const uint32_t full0 = smem_u32(&full_bar[0]), empty0 = smem_u32(&empty_bar[0]);
+        const uint32_t tbase = tmem + lane_base + TC_A_COL0;
+        uint32_t pending = 0xffffffffu;                 // full-barrier address of the stage whose tcgen05.st is still in flight
+        auto retire = [&]() {
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(pending) : "memory");
+        };
         for (int item0 = grp; item0 < n_items; item0 += TC_PF * NU) {
 #pragma unroll
             for (int u = 0; u < TC_PF; ++u) {
-                const int item = item0 + u * NU;
-                if (item < n_items) {
+                if (item0 + u * NU < n_items) {
                     uint32_t v[32];
 #pragma unroll
                     for (int g = 0; g < 4; ++g)
@@ -307,27 +317,23 @@ __global__ void __launch_bounds__(tc_threads(NU), 1) ternary_gemm_tc_kernel(cons
                         for (int j = 0; j < 8; ++j) v[8 * g + j] = (pre[u][j] >> (6 - 2 * g)) & 0x03030303u;   // k = 32g + 4j .. +3
                     load_item(pre[u]);
                     // retire the PREVIOUS stage's tcgen05.st only now: its latency overlapped the unpack above
-                    if (pending >= 0) {
-                        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&full_bar[pending]);
+                    if (pending != 0xffffffffu) retire();
+                    {
+                        uint32_t ok;
+                        do {
+                            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                                         : "=r"(ok) : "r"(empty0 + slot * 8), "r"(par) : "memory");
+                        } while (!ok);
                     }
-                    const int s = item % TC_STAGES;
-                    mbar_wait(&empty_bar[s], (uint32_t)(((item / TC_STAGES) & 1) ^ 1));
                     tc_fence_after();
-                    const uint32_t taddr = tmem + lane_base + TC_A_COL0 + s * TC_A_COLS;
-                    if (!(p.dbg & 4)) TC_ST32(taddr, v);                                 // (dbg 4: timing experiment without the TMEM stores)
-                    pending = s;
+                    if (!(p.dbg & 4)) TC_ST32(tbase + slot * TC_A_COLS, v);              // (dbg 4: timing experiment without the TMEM stores)
+                    pending = full0 + slot * 8;
+                    slot += NU;
+                    if (slot >= TC_STAGES) { slot -= TC_STAGES; par ^= 1u; }
                 }
             }
         }
-        if (pending >= 0) {
-            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&full_bar[pending]);
-        }
+        if (pending != 0xffffffffu) retire();
     } else {
         // ------------------------------------------------------------ epilogue warps: TMEM -> registers -> global
         // A thread owns one weight row n (TMEM lane) and receives 32 tokens per tcgen05.ld.  The output is token-major, so a
@@ -348,6 +354,8 @@ __global__ void __launch_bounds__(tc_threads(NU), 1) ternary_gemm_tc_kernel(cons
         const int ncols = relu2 ? p.N / 2 : p.N;
         const bool red = p.red_acc != nullptr;
         const bool fast_mode = !red && mode == WF_OUT_LINEAR && !relu2 && !resid && obf16 && !p.dbg;
+        const bool fold_ws = fast_mode && p.ep.nseg <= 1;
+        const float ws_all = fold_ws ? p.ep.w_scale[0] : 1.f;
         if (red) pdl_wait_prior();   // the accumulator buffer was cleared by an earlier phase of the step
         for (int tl = 0; tl < my_tiles; ++tl) {
             int m_blk, n_blk, ks;
@@ -361,7 +369,9 @@ __global__ void __launch_bounds__(tc_threads(NU), 1) ternary_gemm_tc_kernel(cons
                     const int m = min(mw0 + j * 32 + lane, p.M - 1);
                     const int rs = p.ep.rowsum ? p.ep.rowsum[m] : 0;
                     const float sa = (mode == WF_OUT_LINEAR) ? p.ep.act_scale[p.ep.act_scale_per_token ? m : 0] : 1.f;
-                    tok[j * 32 + lane] = make_float2((float)rs, sa);               // |Sigma a| <= 127 K < 2^24: exact
+                    // |Sigma a| <= 127 K < 2^24: exact.  One weight scale for the whole matrix: fl(w_s * Sigma a) is staged here, once
+                    // per token, instead of being recomputed by every row (same product, same rounding)
+                    tok[j * 32 + lane] = make_float2(fold_ws ? __fmul_rn(ws_all, (float)rs) : (float)rs, sa);
                 }
                 __syncwarp();
             }
@@ -394,11 +404,20 @@ __global__ void __launch_bounds__(tc_threads(NU), 1) ternary_gemm_tc_kernel(cons
                     const size_t ldo = (size_t)p.ep.ldo;
                     const float2* tk = tok + c * 32;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const float2 t = tk[j];
-                        const float y = __fmul_rn(__fsub_rn(__fmul_rn((float)(int)v[j], ws), __fmul_rn(ws, t.x)), t.y);
-                        *op = __float2bfloat16_rn(y);
-                        op += ldo;
+                    if (fold_ws) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float2 t = tk[j];
+                            *op = __float2bfloat16_rn(__fmul_rn(__fsub_rn(__fmul_rn((float)(int)v[j], ws), t.x), t.y));
+                            op += ldo;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float2 t = tk[j];
+                            *op = __float2bfloat16_rn(__fmul_rn(__fsub_rn(__fmul_rn((float)(int)v[j], ws), __fmul_rn(ws, t.x)), t.y));
+                            op += ldo;
+                        }
                     }
                     continue;
                 }
