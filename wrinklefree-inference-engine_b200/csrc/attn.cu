@@ -82,6 +82,14 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
+__device__ __forceinline__ float ld_dsmem_f32(const float* local_ptr, int cta_rank) {   // the same shared-memory address in CTA `cta_rank` of this cluster
+    uint32_t ra;
+    float v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(smem_u32(local_ptr)), "r"(cta_rank));
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+    return v;
+}
+
 struct AttnParams {
     const __nv_bfloat16* q;      // [B][H][D]
     const __nv_bfloat16* pool;
@@ -98,6 +106,8 @@ struct AttnParams {
     float* part_o;               // [B][H][max_chunks][D]
     float* part_ml;              // [B][H][max_chunks][2]
     int direct;                  // 1: single chunk per sequence everywhere -> write final output
+    int cluster;                 // 1 (fused form, small grids): the chunks of a (sequence, kv head) pair are ONE thread-block cluster; their partials
+                                 // meet in distributed shared memory (two cluster barriers) instead of global memory + fence + atomic + reload
     int chunk_major;             // legacy grid order: 1 = (kv head, sequence, chunk), 0 = (chunk, kv head, sequence)
     int even;                    // 1 (fused form only): the grid is ONE wave of persistent CTAs and the (sequence, kv head, block) space is cut
                                  // into gridDim.x equal contiguous ranges (see the kernel); chunk_blocks / max_chunks / direct are unused
@@ -316,7 +326,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
                 *reinterpret_cast<float4*>(p.zero0 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
     }
-    if (!active) break;
+    if (!active && !p.cluster) break;   // (a cluster member without work still owes the cluster barriers: it contributes an empty partial)
 
     // ---- Q fragments (rows g < G valid; rows 8..15 are zero padding)
     uint32_t qa[8][2];
@@ -627,6 +637,10 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
             const int h = kvh * p.G + hh;
             if (seg_direct) {
                 attn_store(p, b, h, d, (L > 0.f) ? O / L : 0.f);
+            } else if (FUSED && p.cluster) {
+                float* cl_o = mml + AT_WARPS * 8 * 2;          // [8][AT_D] + [8][2], behind the 4-warp merge scratch
+                cl_o[hh * AT_D + d] = O;
+                if (d == 0) { cl_o[8 * AT_D + hh * 2] = M; cl_o[8 * AT_D + hh * 2 + 1] = L; }
             } else {
                 const size_t slot = pslot(my_c, hh);
                 p.part_o[slot * AT_D + d] = O;
@@ -635,7 +649,43 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
         }
     }
     if (tr) p.trace[4] = gtimer();
-    if (FUSED && !seg_direct) {
+    if (FUSED && p.cluster && !seg_direct) {
+        // cluster form: every chunk's (M, L, O) sits in its CTA's shared memory and is read over DSMEM.  ~1-2 us instead of the
+        // ~4 us chain of the global form below (partial store, fence, atomic, reload) — at batch 1 that chain was a third of the kernel
+        const float* cl_o = mml + AT_WARPS * 8 * 2;
+        const int ncl = gridDim.x;                                  // cluster = all chunks of the pair (inactive ones hold L = 0)
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+        {   // the pair's heads are dealt round-robin to the cluster's CTAs: each merges its heads from every CTA's partial
+            const int d = tid;
+            for (int hh = chunk; hh < p.G; hh += ncl) {
+                float mc[8], lc[8], oc[8];
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    mc[c] = -INFINITY; lc[c] = 0.f; oc[c] = 0.f;
+                    if (c < ncl) {
+                        mc[c] = ld_dsmem_f32(cl_o + 8 * AT_D + hh * 2, c);
+                        lc[c] = ld_dsmem_f32(cl_o + 8 * AT_D + hh * 2 + 1, c);
+                        oc[c] = ld_dsmem_f32(cl_o + hh * AT_D + d, c);
+                    }
+                }
+                float M = -INFINITY;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) M = fmaxf(M, mc[c]);
+                float L = 0.f, O = 0.f;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {                       // same order and arithmetic as the global form
+                    const float f = (mc[c] == -INFINITY) ? 0.f : exp2f(mc[c] - M);
+                    L += lc[c] * f;
+                    O += oc[c] * f;
+                }
+                attn_store(p, b, kvh * p.G + hh, d, (L > 0.f) ? O / L : 0.f);
+            }
+        }
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");   // nobody leaves while a peer may still read its shared memory
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
+    if (FUSED && !seg_direct && !p.cluster) {
         // the last chunk to arrive for this (sequence, kv head) merges all of them — no separate merge launch
         __shared__ int s_last;
         __threadfence();
@@ -891,7 +941,30 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     // a chunk split costs a partial write + an atomic + a merge (~4 us of dependent round trips): never split below 512 tokens
     if (chunk_blocks < 32) chunk_blocks = 32;
     chunk_blocks = (chunk_blocks + 3) & ~3;
-    const int nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+    int nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+    // Small grids (every CTA resident at once, latency-bound): the chunks of a pair form a thread-block cluster of <= 8 CTAs and
+    // merge through DSMEM.  A split is cheap there (~1 us), so chunks are short (~12 blocks = 3 per warp) instead of >= 32.
+    const bool fused_q = p.qkv_acc != nullptr;
+    const char* cl_s = getenv("WF_ATTN_CLUSTER");
+    p.cluster = 0;
+    if (fused_q && (!cl_s || atoi(cl_s) != 0)) {
+        // measured (profiles/r02k_summary.txt, 2B): batch 1 / 512: 1.375 -> 1.278 ms, batch 1 / 4K: 1.499 -> 1.395, batch 16 / 2K: 2.40 ->
+        // 2.19; but batch 8 / 2K with 7-CTA clusters 1.87 -> 2.01 and batch 1 / 16K with 8 x 129-block chunks 1.84 -> 1.90: clusters
+        // of <= 4 once the grid exceeds one CTA per SM, and only while a chunk stays short (more chunks than a cluster holds = the
+        // global form, which can use every SM)
+        const long long pr = pairs > 0 ? pairs : 1;
+        long long nch_max = 2LL * sm_count() / pr;
+        if (nch_max > 8) nch_max = 8;
+        if (pr * nch_max > sm_count() && nch_max > 4) nch_max = 4;
+        if (nch_max >= 2 && max_blocks16 > 12) {
+            int nch = (max_blocks16 + 11) / 12;
+            if (nch > nch_max) nch = (int)nch_max;
+            const int cb = (((max_blocks16 + nch - 1) / nch) + 3) & ~3;
+            if (cb <= 48) { chunk_blocks = cb; p.cluster = 1; }
+        }
+    }
+    nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+    if (p.cluster && (nchunks < 2 || nchunks > 8)) p.cluster = 0;
     p.chunk_blocks = chunk_blocks;
     p.max_chunks = nchunks;
     p.page_shift = -1;
@@ -903,7 +976,7 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     const char* even_s = getenv("WF_ATTN_EVEN");   // read per launch (launches are graph-captured): tests switch it inside one process
     const int even_env = even_s ? atoi(even_s) : 0;   // opt-in: measured 5.65 vs 5.46 ms per bs64/4K step (profiles/r02i_*): the per-segment
                                                        // prologue / merge of a CTA costs what the missing partial wave saves
-    { const char* cm = getenv("WF_ATTN_CHUNK_MAJOR"); p.chunk_major = cm ? atoi(cm) : 1; }
+    { const char* cm = getenv("WF_ATTN_CHUNK_MAJOR"); p.chunk_major = cm ? atoi(cm) : 0; }   // measured: chunk-major dispatch 5.71 vs 5.47 ms (bs64/4K)
     int even_ctas = 0;
     p.even = 0;
     if (fused_form && even_env && p.B <= AT_EVEN_MAXB) {
@@ -917,15 +990,18 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
             p.part_ml = p.part_o + (size_t)nc * 2 * 8 * AT_D;
         }
     }
-    if (!p.direct && !p.even) {
+    if (p.even) p.cluster = 0;
+    if (!p.direct && !p.even && !p.cluster) {
         const size_t need = (size_t)p.B * p.H * nchunks * (AT_D + 2) * sizeof(float);
         if (!workspace || workspace_bytes < need) { set_error("paged_decode_attn: workspace too small (%zu < %zu)", workspace_bytes, need); return WF_ERR_INVALID; }
         p.part_o = (float*)workspace;
         p.part_ml = p.part_o + (size_t)p.B * p.H * nchunks * AT_D;
     }
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = nchunks < 1 ? 1 : nchunks; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
     {
         cudaLaunchConfig_t cfg = {};
         const int nchg = nchunks < 1 ? 1 : nchunks;
@@ -934,8 +1010,12 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
         const bool i8 = p.kv_scales != nullptr;
         cfg.dynamicSmemBytes = i8 ? AT8_SMEM : AT_SMEM;
         cfg.stream = s;
-        cfg.attrs = at;
-        cfg.numAttrs = pdl ? 1 : 0;
+        cudaLaunchAttribute la[2];
+        int na = 0;
+        if (pdl) la[na++] = at[0];
+        if (p.cluster) la[na++] = at[1];
+        cfg.attrs = la;
+        cfg.numAttrs = na;
         const bool fused = p.qkv_acc != nullptr;
         cudaError_t le;
         if (i8) le = fused ? cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel<true, true>, p) : cudaLaunchKernelEx(&cfg, paged_decode_attn_kernel<false, true>, p);

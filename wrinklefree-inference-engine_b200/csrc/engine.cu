@@ -78,12 +78,13 @@ struct wf_engine {
     int hx = 1;              // relu^2(gate)*up in its own small kernel instead of every down-proj CTA's prologue (WF_HX=0 to fold it back)
     int decode_tc = 0;       // WF_DECODE_TC=1: batched decode linears (B > 32) on tcgen05 split-K REDs instead of the mma.sync one-shot GEMM (parity-identical; measured equal in step time, both latency-bound — see DESIGN.md)
     int tail_batch = 0;      // WF_TAIL_BATCH=1: the same for 8 < B <= 64 (layer_tail_batch.cu).  Opt-in: measured 5.74 ms vs 5.44 ms per bs64/4K step for the phase path (profiles/r02d_*)
-    int small_max = 8;       // WF_SMALL_MAX: largest batch on the GEMV-style kernels (linear_small / layer_tail: the row glue runs per CTA and per row,
-                             // ~3 us x B x 4 phases per layer); above it the batched kernels (row glue once per row in its own CTA + batched GEMM)
+    int small_max = 1;       // WF_SMALL_MAX: largest batch on the GEMV-style kernels (linear_small / layer_tail: the row glue runs per CTA and per row,
+                             // ~3 us x B x 4 phases per layer); above it the batched kernels (row glue once per row in its own CTA + batched GEMM).
+                             // Measured (profiles/r02j_summary.txt, 2B, 512 ctx): B = 2 / 4 / 8: 1.81 / 2.46 / 3.70 ms on the GEMV-style kernels, 1.72 / 1.74 / 1.75 ms batched
     int tail = 1;            // 1: persistent layer-tail kernel (layer_tail.cu) for B <= 8 on single-GPU engines: 2 launches per layer (WF_TAIL=0: phase kernels)
     // grid-barrier arrival counters, one set per launch site, and the epoch (steps so far) of each kernel family:
     // [0] layer_tail_kernel (B <= 8, LT_MAX_PHASES slots per site), [1] layer_tail_batch_kernel (B > 8, 2 * LT_MAX_PHASES slots)
-    unsigned int* tail_bar[2] = {nullptr, nullptr};
+    unsigned long long* tail_bar[2] = {nullptr, nullptr};
     int* tail_epoch = nullptr;   // [2]
     int fused = 1;           // 1: phase kernels (linear_small / glue_rows + gemm_oneshot / fused attention); 0: one kernel per op
     // fused path state: raw fp32 accumulators of the four linears, their per-token activation scale / Sigma a,
@@ -94,6 +95,7 @@ struct wf_engine {
     __nv_bfloat16* hid2 = nullptr;
     int* merge_cnt = nullptr;
     int launches = 0;
+    int last_family = -1;    // step form of the previous step: 0 per-op kernels, 1 tail kernels, 2 phase kernels (see step_graph)
     int attn_seq_hint = 0;   // max sequence length the chunking is sized for (fixed per captured graph)
     cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};   // [feed_back]
     int graph_B[2] = {0, 0};
@@ -231,7 +233,7 @@ int run_step_tail(wf_engine* e, int B, int feed_back) {
     const int fam = B <= e->small_max ? 0 : 1;
     auto base = [&](int site) {
         TailArgs t = {};
-        t.M = B; t.bar = e->tail_bar[fam] + (size_t)site * LT_MAX_PHASES * (fam + 1) * LT_BAR_WORDS; t.epoch = e->tail_epoch + fam; t.err = e->d_err;
+        t.M = B; t.bar = e->tail_bar[fam] + (size_t)site * LT_MAX_PHASES * (fam + 1); t.epoch = e->tail_epoch + fam; t.err = e->d_err;
         if (e->trace && site < c.layers) t.trace = e->trace + (size_t)32 * site;
         return t;
     };
@@ -515,6 +517,21 @@ int seq_hint_for(const wf_engine* e, int B) {
 
 int step_graph(wf_engine* e, int B, int feed_back, int use_graph) {
     const int hint = seq_hint_for(e, B);
+    // The phase kernels keep a steady state between steps: every split-K accumulator is zero on entry because a LATER phase of the
+    // previous step cleared it.  The tail kernels (plain stores by the owner of a row, nothing is ever cleared) do not maintain that
+    // state, so a step that switches from them to the phase kernels (e.g. batch 1 -> batch 3 on one engine) clears the four
+    // accumulators first.  (Found by test_batched_equals_single_sequences once batches 2..8 moved to the batched kernels.)
+    {
+        const int fam = !e->fused ? 0 : (tail_path_ok(e, B) ? 1 : 2);
+        if (fam == 2 && e->last_family != 2) {
+            const size_t MB = (size_t)e->cfg.max_batch;
+            if (cuda_check(cudaMemsetAsync(e->acc_qkv, 0, MB * e->qkv_rows * 4, e->stream), "acc clear") ||
+                cuda_check(cudaMemsetAsync(e->acc_gu, 0, MB * 2 * e->ffn * 4, e->stream), "acc clear") ||
+                cuda_check(cudaMemsetAsync(e->acc_o, 0, MB * e->hidden * 4, e->stream), "acc clear") ||
+                cuda_check(cudaMemsetAsync(e->acc_down, 0, MB * e->hidden * 4, e->stream), "acc clear")) return WF_ERR_CUDA;
+        }
+        e->last_family = fam;
+    }
     if (!use_graph) {
         e->attn_seq_hint = hint;
         return step_dispatch(e, B, feed_back);
@@ -694,11 +711,10 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
         (rc = dalloc(e, &e->acc_gu, (size_t)B * 2 * e->ffn)) ||
         (rc = dalloc(e, &e->lin_asc, (size_t)4 * B)) || (rc = dalloc(e, &e->lin_rs, (size_t)4 * B)) ||
         (rc = dalloc(e, &e->hid2, (size_t)B * e->hidden)) || (rc = dalloc(e, &e->merge_cnt, (size_t)B * e->Hkv))) return fail(rc);
-    if ((rc = dalloc(e, &e->tail_bar[0], (size_t)(c.layers + 1) * LT_MAX_PHASES * LT_BAR_WORDS)) ||
-        (rc = dalloc(e, &e->tail_bar[1], (size_t)(c.layers + 1) * 2 * LT_MAX_PHASES * LT_BAR_WORDS)) ||
+    if ((rc = dalloc(e, &e->tail_bar[0], (size_t)(c.layers + 1) * LT_MAX_PHASES)) || (rc = dalloc(e, &e->tail_bar[1], (size_t)(c.layers + 1) * 2 * LT_MAX_PHASES)) ||
         (rc = dalloc(e, &e->tail_epoch, 2))) return fail(rc);
-    if (cuda_check(cudaMemset(e->tail_bar[0], 0, (size_t)(c.layers + 1) * LT_MAX_PHASES * LT_BAR_WORDS * 4), "bar memset") ||
-        cuda_check(cudaMemset(e->tail_bar[1], 0, (size_t)(c.layers + 1) * 2 * LT_MAX_PHASES * LT_BAR_WORDS * 4), "bar memset") ||
+    if (cuda_check(cudaMemset(e->tail_bar[0], 0, (size_t)(c.layers + 1) * LT_MAX_PHASES * 8), "bar memset") ||
+        cuda_check(cudaMemset(e->tail_bar[1], 0, (size_t)(c.layers + 1) * 2 * LT_MAX_PHASES * 8), "bar memset") ||
         cuda_check(cudaMemset(e->tail_epoch, 0, 8), "epoch memset")) return fail(WF_ERR_CUDA);
     if (cuda_check(cudaMemset(e->acc_qkv, 0, (size_t)B * e->qkv_rows * 4), "acc memset") ||
         cuda_check(cudaMemset(e->acc_gu, 0, (size_t)B * 2 * e->ffn * 4), "acc memset") ||

@@ -464,35 +464,6 @@ __device__ __forceinline__ void glue_zero_duty(const GlueParams& p) {
         for (int i = gtid * 4; i < p.zero1_n; i += gstride * 4) *reinterpret_cast<float4*>(p.zero1 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
-// Grid barrier of the persistent tail kernels: ONE FLAG PER CTA (64 bytes apart), not one arrival counter.  148 release-adds on one
-// address serialise in the L2 atomic unit (~27 clk each: ~2 us per barrier, measured as "barrier 2.0-2.5 us" in
-// profiles/r02d_trace_tail_bs1.txt); a CTA publishing its own flag with st.release and NT threads polling one flag each do not.
-// Flag values are the decode-step epoch (monotonic: nothing is ever reset, CUDA-graph replay safe).
-constexpr int LT_BAR_CTAS = 160;                         // >= SM count
-constexpr int LT_BAR_STRIDE = 16;                        // words between two flags (64 bytes)
-constexpr int LT_BAR_WORDS = LT_BAR_CTAS * LT_BAR_STRIDE;   // words per barrier slot
-// Grid barrier over the NT consumer threads of every CTA of a persistent grid (see LT_BAR_*).  `slot` = this barrier's flag array,
-// `target` = the step epoch.  Bounded like every spin in this library (tp_comm.cuh).
-template <int NT>
-__device__ __forceinline__ void lt_flag_barrier(unsigned int* slot, unsigned int target, int grid, int cta, int* err) {
-    group_bar<1, NT>();                                  // this CTA's stores happen-before thread 0's release (CTA barrier + cumulativity)
-    if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(slot + cta * LT_BAR_STRIDE), "r"(target) : "memory");
-    for (int i = threadIdx.x; i < grid; i += NT) {
-        const unsigned int* f = slot + i * LT_BAR_STRIDE;
-        unsigned int v;
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-        if ((int)(v - target) < 0 && !(err && ld_relaxed_gpu(err))) {    // after one timeout every later barrier falls through: the step is lost anyway
-            const unsigned long long t0 = spin_now();
-            for (;;) {
-                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-                if ((int)(v - target) >= 0) break;
-                if (spin_now() - t0 > WF_SPIN_BUDGET_NS) { if (err) atomicExch(err, 1); break; }
-            }
-        }
-    }
-    group_bar<1, NT>();                                  // every thread of the CTA is ordered after all the acquires
-}
-
 // launchers (host)
 struct SmallLinArgs {
     GlueParams g;            // g.K = length of the (full) activation vector the prologue normalises / quantises
@@ -549,8 +520,8 @@ struct TailPhaseArgs {
 struct TailArgs {
     int nph, M;
     TailPhaseArgs ph[LT_MAX_PHASES];
-    unsigned int* bar;       // [LT_MAX_PHASES (batched form: 2x)][LT_BAR_WORDS] flags of THIS launch site (zero-initialised once, monotonic)
-    int* epoch;              // device counter of tail-path decode steps: barrier target = epoch
+    unsigned long long* bar; // [LT_MAX_PHASES] arrival counters of THIS launch site (zero-initialised once, monotonic)
+    int* epoch;              // device counter of tail-path decode steps: barrier target = grid * epoch
     int bump_epoch;          // this launch (the first of a step, single phase) increments the epoch
     int* err;                // device error word (bounded spins)
     unsigned long long* trace;   // WF_TRACE timeline taps of this launch site (32 slots) or null

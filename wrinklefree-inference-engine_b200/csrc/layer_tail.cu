@@ -53,8 +53,8 @@ struct TailPhase {
 struct TailParams {
     int nph, M, stages, act_stride, sacc_rbs, ys_elems;
     TailPhase ph[LT_MAX_PHASES];
-    unsigned int* bar;           // [LT_MAX_PHASES][LT_BAR_WORDS] per-CTA flags of this launch site (fused_common.cuh lt_flag_barrier)
-    int* epoch;                  // tail-path decode steps so far (device counter) = barrier target
+    unsigned long long* bar;     // [LT_MAX_PHASES] monotonic arrival counters of this launch site
+    int* epoch;                  // tail-path decode steps so far (device counter): barrier target = grid * epoch
     int bump_epoch;              // the first launch of a step (single phase, no barrier) increments it
     int* err;
     unsigned long long* trace;   // WF_TRACE timeline taps (CTA 0): [0] entry, [1] dependency wait done, then per phase 5 stamps
@@ -73,6 +73,26 @@ __device__ __forceinline__ void lt_slab(const TailPhase& ph, int cta, int grid, 
     if (c >= grid) c -= grid;
     rb_lo = (int)((long long)c * units / grid) * ph.rb_unit;
     rb_hi = (int)((long long)(c + 1) * units / grid) * ph.rb_unit;
+}
+
+// Grid barrier for the consumer threads of all CTAs (the producer warps keep streaming).  Arrival = release-add, wait =
+// acquire spin; counters are monotonic over decode steps (no reset, CUDA-graph replay safe).  Bounded like every spin here.
+__device__ __forceinline__ void lt_grid_barrier(unsigned long long* slot, unsigned long long target, int* err) {
+    group_bar<1, LT_CT>();
+    if (threadIdx.x == 0) {
+        asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(slot), "l"(1ull) : "memory");
+        unsigned long long v;
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
+        if (v < target && !(err && ld_relaxed_gpu(err))) {      // after one timeout every later barrier falls through: the step is lost anyway
+            const unsigned long long t0 = spin_now();
+            for (;;) {
+                asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
+                if (v >= target) break;
+                if (spin_now() - t0 > WF_SPIN_BUDGET_NS) { if (err) atomicExch(err, 1); break; }
+            }
+        }
+    }
+    group_bar<1, LT_CT>();
 }
 
 template <int MR>
@@ -130,10 +150,10 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
     glue_prefetch_gamma<LT_CT>(p.ph[0].g);
     pdl_wait_prior();                                   // the attention kernel's output (or the previous step) is complete
     if (tr) p.trace[1] = gtimer();
-    // Barrier flags are monotonic over the decode steps that take this path (no reset, CUDA-graph replay safe).  The epoch is
+    // Barrier counters are monotonic over the decode steps that take this path (no reset, CUDA-graph replay safe).  The epoch is
     // bumped by the step's first launch, which finished (transitively, through the attention kernel) before this one got here.
     if (p.bump_epoch && cta == 0 && tid == 0) atomicAdd(p.epoch, 1);
-    const unsigned int bar_target = (unsigned int)ld_relaxed_gpu(p.epoch);
+    const unsigned long long bar_target = (unsigned long long)grid * (unsigned long long)ld_relaxed_gpu(p.epoch);
     int s = 0, ph_bit = 0;                              // ring position, continues across phases
     const int arow = min(lane & 7, M - 1);
 
@@ -141,7 +161,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
         const TailPhase& ph = p.ph[pi];
         if (pi > 0) {
             glue_prefetch_gamma<LT_CT>(ph.g);
-            lt_flag_barrier<LT_CT>(p.bar + (size_t)(pi - 1) * LT_BAR_WORDS, bar_target, grid, cta, p.err);
+            lt_grid_barrier(p.bar + (pi - 1), bar_target, p.err);
             // every CTA of this grid is resident now: letting the next kernel's CTAs in can no longer starve the barrier
             if (pi == 1) pdl_launch_dependents();
         }
@@ -331,7 +351,6 @@ int launch_layer_tail(const TailArgs& a, cudaStream_t s, bool pdl) {
     memset(&p, 0, sizeof p);
     p.nph = a.nph; p.M = a.M;
     const int grid = sm_count();
-    if (grid > LT_BAR_CTAS) { set_error("layer_tail: more SMs than barrier flags"); return WF_ERR_UNSUPPORTED; }
     int Kmax = 0, max_rbs = 0;
     long long extra = 0;   // running rotation: CTAs that received an extra unit in earlier phases come last in later ones
     for (int i = 0; i < a.nph; ++i) {

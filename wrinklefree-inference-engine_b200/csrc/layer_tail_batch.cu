@@ -50,7 +50,7 @@ struct BatchPhase {
 struct BatchParams {
     int nph, M;
     BatchPhase ph[LT_MAX_PHASES];
-    unsigned int* bar;           // [2 * LT_MAX_PHASES][LT_BAR_WORDS] per-CTA flags (fused_common.cuh lt_flag_barrier)
+    unsigned long long* bar;     // [2 * LT_MAX_PHASES]
     int* epoch;
     int bump_epoch;
     int* err;
@@ -63,6 +63,24 @@ __device__ __forceinline__ void lb_slab(const BatchPhase& ph, int cta, int grid,
     if (c >= grid) c -= grid;
     rb_lo = (int)((long long)c * units / grid) * ph.rb_unit;
     rb_hi = (int)((long long)(c + 1) * units / grid) * ph.rb_unit;
+}
+
+__device__ __forceinline__ void lb_grid_barrier(unsigned long long* slot, unsigned long long target, int* err) {
+    group_bar<1, LB_CT>();
+    if (threadIdx.x == 0) {
+        asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(slot), "l"(1ull) : "memory");
+        unsigned long long v;
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
+        if (v < target && !(err && ld_relaxed_gpu(err))) {
+            const unsigned long long t0 = spin_now();
+            for (;;) {
+                asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
+                if (v >= target) break;
+                if (spin_now() - t0 > WF_SPIN_BUDGET_NS) { if (err) atomicExch(err, 2); break; }
+            }
+        }
+    }
+    group_bar<1, LB_CT>();
 }
 
 __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const __grid_constant__ BatchParams p) {
@@ -147,14 +165,14 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
     if (tr) tr[0] = gtimer();
     pdl_wait_prior();
     if (tr) tr[1] = gtimer();
-    const unsigned int bar_target = (unsigned int)(ld_relaxed_gpu(p.epoch) + (p.bump_epoch ? 1 : 0));
+    const unsigned long long bar_target = (unsigned long long)grid * (unsigned long long)(ld_relaxed_gpu(p.epoch) + (p.bump_epoch ? 1 : 0));
     int ws = 0, wbit = 0, as = 0, abit = 0;
     int nbar = 0;
 
     for (int pi = 0; pi < p.nph; ++pi) {
         const BatchPhase& ph = p.ph[pi];
         if (pi > 0) {
-            lt_flag_barrier<LB_CT>(p.bar + (size_t)nbar * LT_BAR_WORDS, bar_target, grid, cta, p.err);   // the previous phase's outputs are complete
+            lb_grid_barrier(p.bar + nbar, bar_target, p.err);   // the previous phase's outputs are complete
             ++nbar;
             if (pi == 1) pdl_launch_dependents();               // every CTA of this grid is resident: dependents can no longer starve the barriers
         }
@@ -170,7 +188,7 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
             fence_proxy_async_global();                         // the codes are read back by bulk copies (async proxy)
         }
         if (tr) tr[3 + 5 * pi] = gtimer();
-        lt_flag_barrier<LB_CT>(p.bar + (size_t)nbar * LT_BAR_WORDS, bar_target, grid, cta, p.err);       // every row is published
+        lb_grid_barrier(p.bar + nbar, bar_target, p.err);       // every row is published
         ++nbar;
         if (pi == 0 && p.nph == 1) pdl_launch_dependents();
         if (tid == 0) mbar_arrive(&phase_bar);                  // release the activation producer
@@ -308,7 +326,7 @@ int launch_layer_tail_batch(const TailArgs& a, cudaStream_t s, bool pdl) {
     memset(&p, 0, sizeof p);
     p.nph = a.nph; p.M = a.M;
     const int grid = sm_count();
-    if (a.M > grid || grid > LT_BAR_CTAS) { set_error("layer_tail_batch: more rows than CTAs / more SMs than barrier flags"); return WF_ERR_UNSUPPORTED; }
+    if (a.M > grid) { set_error("layer_tail_batch: more rows than CTAs"); return WF_ERR_UNSUPPORTED; }
     long long extra = 0;
     for (int i = 0; i < a.nph; ++i) {
         const TailPhaseArgs& x = a.ph[i];
