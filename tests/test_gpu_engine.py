@@ -237,11 +237,13 @@ def test_tcgen05_decode_linears_equal_per_op_kernels(B, ctx, monkeypatch):
     steps = [list(map(int, rng.integers(0, cfg.vocab, B))) for _ in range(3)]
     monkeypatch.setenv("WF_DECODE_TC", "1")
     a = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=ctx, synthetic=5)
-    monkeypatch.setenv("WF_DECODE_TC", "0")
+    monkeypatch.setenv("WF_DECODE_TC", "0")      # the mma.sync one-shot GEMM (the default below WF_DECODE_TC_MIN tokens) at the same batch
+    c = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=ctx, synthetic=5)
     b = _run_tokens(cfg, None, False, steps, monkeypatch, ctx=ctx, synthetic=5)
-    for i, ((la, na, _), (lb, nb, _)) in enumerate(zip(a, b)):
+    for i, ((la, na, _), (lb, nb, _), (lc, nc, _)) in enumerate(zip(a, b, c)):
         assert torch.equal(la, lb), (i, (la - lb).abs().max().item())
-        assert (na == nb).all()
+        assert torch.equal(lc, lb), (i, (lc - lb).abs().max().item())
+        assert (na == nb).all() and (nc == nb).all()
 
 
 # ---------------------------------------------------------------------------------------------------------------------

@@ -76,7 +76,9 @@ struct wf_engine {
     bool pdl = false;
     int linear_algo = 0;
     int hx = 1;              // relu^2(gate)*up in its own small kernel instead of every down-proj CTA's prologue (WF_HX=0 to fold it back)
-    int decode_tc = 0;       // WF_DECODE_TC=1: batched decode linears (B > 32) on tcgen05 split-K REDs instead of the mma.sync one-shot GEMM (parity-identical; measured equal in step time, both latency-bound — see DESIGN.md)
+    int decode_tc = 1;       // batched decode linears (B >= decode_tc_min, single GPU) on tcgen05 split-K REDs (gemm_tc.cu launch_gemm_tc_red) instead of the mma.sync one-shot
+                             // GEMM: bit-identical; with the round-2 issue loop / epilogue 3.65 -> 3.23 ms at batch 40 / 2K, 5.48 -> 5.32 ms at batch 64 / 4K (WF_DECODE_TC=0: off)
+    int decode_tc_min = 33;  // WF_DECODE_TC_MIN
     int tail_batch = 0;      // WF_TAIL_BATCH=1: the same for 8 < B <= 64 (layer_tail_batch.cu).  Opt-in: measured 5.74 ms vs 5.44 ms per bs64/4K step for the phase path (profiles/r02d_*)
     int small_max = 1;       // WF_SMALL_MAX: largest batch on the GEMV-style kernels (linear_small / layer_tail: the row glue runs per CTA and per row,
                              // ~3 us x B x 4 phases per layer); above it the batched kernels (row glue once per row in its own CTA + batched GEMM).
@@ -373,7 +375,10 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
         int r = launch_glue_rows(g, s, pdl && !first);
         if (r) return r;
         // a real dense contraction (33..64 tokens): tcgen05 int8 with split-K REDs; single-GPU engines only for now
-        if (e->decode_tc && !tp && B > 32 && N % 8 == 0) return launch_gemm_tc_red(w, N, K, e->q8, B, Kfull, k_off, dest.acc[0], N, s, pdl);
+        // tcgen05 split-K form: from 33 tokens up, and from 9 tokens up for matrices of >= 16 MB packed (70B shapes: one owner per 128-row
+        // tile streams its whole K, where the one-shot GEMM pays a RED round per 4 k-blocks) — profiles/r02m_summary.txt
+        const bool big = (size_t)N * K / 4 >= ((size_t)16 << 20);
+        if (e->decode_tc && !tp && (B >= e->decode_tc_min || (big && B >= 9)) && N % 8 == 0) return launch_gemm_tc_red(w, N, K, e->q8, B, Kfull, k_off, dest.acc[0], N, s, pdl);
         OneshotArgs o;
         o.w = w; o.N = N; o.K = K; o.q = e->q8; o.M = B; o.ldq = Kfull; o.k_off = k_off; o.dest = dest; o.acc_ld = N; o.tp = e->tp;
         return launch_gemm_oneshot(o, s, pdl);
@@ -606,6 +611,7 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     { const char* x = getenv("WF_SMALL_MAX"); if (x) { e->small_max = atoi(x); if (e->small_max < 0) e->small_max = 0; if (e->small_max > 8) e->small_max = 8; } }
     { const char* x = getenv("WF_TAIL_BATCH"); if (x) e->tail_batch = atoi(x) != 0; }
     { const char* x = getenv("WF_DECODE_TC"); if (x) e->decode_tc = atoi(x) != 0; }
+    { const char* x = getenv("WF_DECODE_TC_MIN"); if (x) e->decode_tc_min = atoi(x) < 2 ? 2 : atoi(x); }
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
     int rc = WF_OK;
     auto fail = [&](int r) { wf_engine_destroy(e); return r; };

@@ -183,7 +183,9 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
             if (ph.g.K <= LB_CT * 8 * 2 && ph.g.mode != GL_RELU2 && ph.g.acc_own_cols == 0)      // the row stays in registers between the passes
                 glue_row_regs<1, LB_CT, 2>(ph.g, cta, ph.g.q_out + (size_t)cta * LB_ASTRIDE, fs, is, true, sc, rsum, QMAP_CHUNKED);
             else
-                glue_row<1, LB_CT>(ph.g, cta, reinterpret_cast<__nv_bfloat16*>(red), ph.g.q_out + (size_t)cta * LB_ASTRIDE, fs, is, true, sc, rsum, nullptr, QMAP_CHUNKED);
+                // bf16 row scratch: the activation ring is idle between a phase's two grid barriers (its loader waits for phase_bar), and
+                // holds rows of up to 50 K elements (8B / 70B ffn vectors) where the reduction buffer holds 13 K
+                glue_row<1, LB_CT>(ph.g, cta, reinterpret_cast<__nv_bfloat16*>(aring), ph.g.q_out + (size_t)cta * LB_ASTRIDE, fs, is, true, sc, rsum, nullptr, QMAP_CHUNKED);
             if (tid == 0) { ph.g.scale_out[cta] = sc; ph.g.rowsum_out[cta] = rsum; }
             fence_proxy_async_global();                         // the codes are read back by bulk copies (async proxy)
         }
@@ -317,7 +319,7 @@ __global__ void __launch_bounds__(LB_THREADS, 1) layer_tail_batch_kernel(const _
 constexpr size_t LB_SMEM = (size_t)LB_WSLOTS * LB_WSLOT + (size_t)LB_ASLOTS * LB_ASLOT + LB_RED_BYTES;
 
 bool layer_tail_batch_fits(int M, int Kmax) {
-    return M >= 1 && M <= 64 && (size_t)Kmax * 2 <= LB_RED_BYTES;
+    return M >= 1 && M <= 64 && (size_t)Kmax * 2 <= (size_t)LB_ASLOTS * LB_ASLOT;
 }
 
 int launch_layer_tail_batch(const TailArgs& a, cudaStream_t s, bool pdl) {
@@ -330,7 +332,7 @@ int launch_layer_tail_batch(const TailArgs& a, cudaStream_t s, bool pdl) {
     long long extra = 0;
     for (int i = 0; i < a.nph; ++i) {
         const TailPhaseArgs& x = a.ph[i];
-        if (x.K % WF_QK || x.g.K != x.K || (size_t)x.K * 2 > LB_RED_BYTES) { set_error("layer_tail_batch: bad K"); return WF_ERR_UNSUPPORTED; }
+        if (x.K % WF_QK || x.g.K != x.K || (size_t)x.K * 2 > (size_t)LB_ASLOTS * LB_ASLOT) { set_error("layer_tail_batch: bad K"); return WF_ERR_UNSUPPORTED; }
         if (!x.g.q_out || !x.g.scale_out || !x.g.rowsum_out) { set_error("layer_tail_batch: the glue needs q_out / scale_out / rowsum_out"); return WF_ERR_INVALID; }
         BatchPhase& ph = p.ph[i];
         ph.g = x.g; ph.g.M = a.M;
