@@ -258,23 +258,22 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
     const int my_n = active ? (blk1 - blk0 - warp + AT_WARPS - 1) / AT_WARPS : 0;   // blocks blk0 + warp + 4*i
     const int32_t* bt = p.block_table + (size_t)b * p.max_blocks;
 
-    int pg_next;
-    {
-        const int tokf = (blk0 + warp) * AT_BLK;
+    // page of this warp's block i, looked up THREE issues ahead (a 3-deep register queue): one issue = one block of compute (~0.3-0.5 us),
+    // an L2 round trip under load is ~1 us — with a single entry ahead 13 % of the kernel's stall samples sat on this dependency
+    // (profiles/r02_full_attn_fused_bs64.summary.txt, attn.cu kv_block_offset)
+    auto page_of = [&](int i) -> int {
+        const int tokf = (blk0 + warp + AT_WARPS * i) * AT_BLK;
         const int pi = p.page_shift >= 0 ? (tokf >> p.page_shift) : tokf / p.page_size;
-        pg_next = bt[min(pi, p.max_blocks - 1)];
-    }
+        return bt[min(pi, p.max_blocks - 1)];
+    };
+    int pg_q0 = page_of(0), pg_q1 = page_of(1), pg_q2 = page_of(2);
     auto issue = [&](int i) {   // i-th block of this warp -> stage i % AT_STAGES
         if (i < my_n) {
             const int blk = blk0 + warp + AT_WARPS * i;
             const int tok0 = blk * AT_BLK;
-            const int page = pg_next;           // looked up one issue ahead: the L2 round trip is off the critical path
+            const int page = pg_q0;
+            pg_q0 = pg_q1; pg_q1 = pg_q2; pg_q2 = page_of(i + 3);
             const int slot0 = p.page_shift >= 0 ? (tok0 & (p.page_size - 1)) : tok0 % p.page_size;
-            {
-                const int tokn = tok0 + AT_WARPS * AT_BLK;
-                const int pi = p.page_shift >= 0 ? (tokn >> p.page_shift) : tokn / p.page_size;
-                pg_next = bt[min(pi, p.max_blocks - 1)];
-            }
             const size_t ko = kv_block_offset(page, p.layers, p.layer, 0, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
             const size_t vo = kv_block_offset(page, p.layers, p.layer, 1, p.Hkv, kvh, p.page_size) + (size_t)slot0 * AT_D;
             unsigned char* ks = wsm + (i % ST) * SB;
@@ -942,6 +941,9 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     if (chunk_blocks < 32) chunk_blocks = 32;
     chunk_blocks = (chunk_blocks + 3) & ~3;
     int nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+    // equal chunks for that count (129 blocks at a floor of 32 would be 32, 32, 32, 32, 1: five CTAs, four of them useful)
+    chunk_blocks = (((max_blocks16 + nchunks - 1) / nchunks) + 3) & ~3;
+    nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
     // Small grids (every CTA resident at once, latency-bound): the chunks of a pair form a thread-block cluster of <= 8 CTAs and
     // merge through DSMEM.  A split is cheap there (~1 us), so chunks are short (~12 blocks = 3 per warp) instead of >= 32.
     const bool fused_q = p.qkv_acc != nullptr;

@@ -375,10 +375,12 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
         int r = launch_glue_rows(g, s, pdl && !first);
         if (r) return r;
         // a real dense contraction (33..64 tokens): tcgen05 int8 with split-K REDs; single-GPU engines only for now
-        // tcgen05 split-K form: from 33 tokens up, and from 9 tokens up for matrices of >= 16 MB packed (70B shapes: one owner per 128-row
-        // tile streams its whole K, where the one-shot GEMM pays a RED round per 4 k-blocks) — profiles/r02m_summary.txt
-        const bool big = (size_t)N * K / 4 >= ((size_t)16 << 20);
-        if (e->decode_tc && !tp && (B >= e->decode_tc_min || (big && B >= 9)) && N % 8 == 0) return launch_gemm_tc_red(w, N, K, e->q8, B, Kfull, k_off, dest.acc[0], N, s, pdl);
+        // tcgen05 split-K form (one owner per 128-row tile streams its whole K; the one-shot GEMM pays a RED round per 4 k-blocks): from 33
+        // tokens up; from 9 tokens for K >= 8192 (70B shapes); from 24 tokens for >= 16 MB matrices.  Measured in profiles/r02q_summary.txt:
+        // 70B bs16 32.2 -> 24.6 ms, 8B bs32 4.95 -> 4.84 ms, while 8B bs16 gate|up (29 MB, K = 4096) is faster on the one-shot GEMM.
+        const size_t wbytes = (size_t)N * K / 4;
+        const bool use_tc = B >= e->decode_tc_min || (B >= 9 && K >= 8192) || (B >= 24 && wbytes >= ((size_t)16 << 20));
+        if (e->decode_tc && !tp && use_tc && N % 8 == 0) return launch_gemm_tc_red(w, N, K, e->q8, B, Kfull, k_off, dest.acc[0], N, s, pdl);
         OneshotArgs o;
         o.w = w; o.N = N; o.K = K; o.q = e->q8; o.M = B; o.ldq = Kfull; o.k_off = k_off; o.dest = dest; o.acc_ld = N; o.tp = e->tp;
         return launch_gemm_oneshot(o, s, pdl);

@@ -42,6 +42,7 @@ constexpr int TC_A_COLS = TC_BK / 4;               // TMEM columns per weight st
 constexpr int TC_A_COL0 = 2 * TC_BN;               // weight ring starts after the two accumulator buffers
 constexpr int TC_TMEM_COLS = 512;
 constexpr int TC_PF = 4;                           // weight prefetch distance (stages, in registers)
+constexpr int TC_L2_AHEAD = 6;                     // decode form: L2 prefetch distance of the weight stream, in items of an unpack group
 constexpr int TC_EPW = 8;                          // epilogue warps: two per TMEM lane quarter, 64 of the tile's 128 tokens each
 constexpr int TC_EP_TOKS = TC_BN / (TC_EPW / 4);   // tokens per epilogue warp
 constexpr int TC_EP_TOK = TC_EPW * TC_EP_TOKS * 8;  // per epilogue warp: {(float) Sigma a, activation scale} of its tokens
@@ -58,6 +59,7 @@ struct TcParams {
     // tile each, and the epilogue adds the raw accumulators into a global fp32 buffer (exact: integers < 2^24) instead
     // of storing a finished output — the consumer phase of the decode step applies scales / residual / norm.
     int splitk, KBs;
+    int l2_ahead;   // decode form: L2 prefetch distance of the weight stream in items of an unpack group (0 = off)
     float* red_acc;
     int red_ld;
     EpiParams ep;
@@ -266,6 +268,11 @@ __global__ void __launch_bounds__(tc_threads(NU), 1) ternary_gemm_tc_kernel(cons
         int l_tl = 0, l_kb = grp;
         const uint8_t* l_src = p.w;
         bool l_valid = true;
+        // Decode form on large matrices (70B shapes: 117 MB per linear, nothing L2-resident): the registers hold 4 items = 32 KB in flight
+        // per SM, half of what HBM latency x bandwidth asks for (Little: ~44 KB), so every thread also pulls its 64-byte window of the
+        // k-block TC_L2_AHEAD items ahead into L2 (rows r and r + 8 share a window: one sector each).
+        const int l2_ahead = p.l2_ahead;
+        uint32_t pf_off = 0;
         auto seek = [&]() {   // off the per-item path: tile boundary (or start)
             while (l_kb >= KBs) { l_kb -= KBs; ++l_tl; }
             l_valid = l_tl < my_tiles;
@@ -278,6 +285,7 @@ __global__ void __launch_bounds__(tc_threads(NU), 1) ternary_gemm_tc_kernel(cons
             const uint8_t* rowbase = i2s ? p.w + (size_t)row * K4
                                          : p.w + (size_t)(row >> 4) * p.KB * WF_TILE_BYTES + (size_t)(16 * (row & 7) + ((row >> 3) & 1)) * 4;
             l_src = rowbase + ((size_t)ks * KBs + l_kb) * kb_stride;   // this tile's K run, this group's first k-block in it
+            pf_off = i2s ? 0u : (uint32_t)(((row >> 3) & 1) * 28);
         };
         seek();
         auto load_item = [&](uint32_t (&r)[8]) {
@@ -289,6 +297,8 @@ __global__ void __launch_bounds__(tc_threads(NU), 1) ternary_gemm_tc_kernel(cons
 #pragma unroll
                 for (int j = 0; j < 8; ++j) r[j] = __ldg(reinterpret_cast<const uint32_t*>(l_src) + 4 * (j & 3) + 2 * (j >> 2));
             }
+            if (l2_ahead && l_kb + l2_ahead * NU < KBs)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(l_src + (size_t)l2_ahead * NU * kb_stride + pf_off));
             l_kb += NU;
             l_src += NU * kb_stride;
             if (l_kb >= KBs) seek();
@@ -529,7 +539,7 @@ static int launch_tc_cl(const wf_linear_args* a, const EpiParams& ep, cudaStream
     p.tiles_n = (a->N + TC_BM - 1) / TC_BM;
     p.tiles_m = (a->M + TC_BN - 1) / TC_BN;
     p.ep = ep;
-    p.splitk = 1; p.KBs = p.KB; p.red_acc = nullptr; p.red_ld = 0;
+    p.splitk = 1; p.KBs = p.KB; p.red_acc = nullptr; p.red_ld = 0; p.l2_ahead = 0;
     { const char* d = getenv("WF_TC_DBG"); p.dbg = d ? atoi(d) : 0; }
     const int total = ((p.tiles_n + CL - 1) / CL) * p.tiles_m;
     cudaLaunchConfig_t cfg = {};
@@ -588,6 +598,7 @@ int launch_gemm_tc_red(const uint8_t* w_tile, int N, int K, const int8_t* q, int
     for (int d = 1; d <= p.KB; ++d)
         if (p.KB % d == 0 && p.tiles_n * d <= sms) split = d;
     p.splitk = split; p.KBs = p.KB / split;
+    { static const int ahead = getenv("WF_TC_L2_AHEAD") ? atoi(getenv("WF_TC_L2_AHEAD")) : TC_L2_AHEAD; p.l2_ahead = ahead; }
     const int total = p.tiles_n * split;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(total < sms ? total : sms);
