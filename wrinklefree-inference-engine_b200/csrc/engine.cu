@@ -83,6 +83,7 @@ struct wf_engine {
     int small_max = 1;       // WF_SMALL_MAX: largest batch on the GEMV-style kernels (linear_small / layer_tail: the row glue runs per CTA and per row,
                              // ~3 us x B x 4 phases per layer); above it the batched kernels (row glue once per row in its own CTA + batched GEMM).
                              // Measured (profiles/r02j_summary.txt, 2B, 512 ctx): B = 2 / 4 / 8: 1.81 / 2.46 / 3.70 ms on the GEMV-style kernels, 1.72 / 1.74 / 1.75 ms batched
+    int tail_lam = 1;        // WF_TAIL_LAM: batch-1 tail kernel hands its phases over flag-in-data (no grid barriers); 0 = grid barriers
     int tail = 1;            // 1: persistent layer-tail kernel (layer_tail.cu) for B <= 8 on single-GPU engines: 2 launches per layer (WF_TAIL=0: phase kernels)
     // grid-barrier arrival counters, one set per launch site, and the epoch (steps so far) of each kernel family:
     // [0] layer_tail_kernel (B <= 8, LT_MAX_PHASES slots per site), [1] layer_tail_batch_kernel (B > 8, 2 * LT_MAX_PHASES slots)
@@ -237,6 +238,7 @@ int run_step_tail(wf_engine* e, int B, int feed_back) {
         TailArgs t = {};
         t.M = B; t.bar = e->tail_bar[fam] + (size_t)site * LT_MAX_PHASES * (fam + 1); t.epoch = e->tail_epoch + fam; t.err = e->d_err;
         if (e->trace && site < c.layers) t.trace = e->trace + (size_t)32 * site;
+        t.lam = e->tail_lam;
         return t;
     };
     auto launch_tail = [&](const TailArgs& t, bool use_pdl) { return fam ? launch_layer_tail_batch(t, s, use_pdl) : launch_layer_tail(t, s, use_pdl); };
@@ -380,7 +382,10 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
         // 70B bs16 32.2 -> 24.6 ms, 8B bs32 4.95 -> 4.84 ms, while 8B bs16 gate|up (29 MB, K = 4096) is faster on the one-shot GEMM.
         const size_t wbytes = (size_t)N * K / 4;
         const bool use_tc = B >= e->decode_tc_min || (B >= 9 && K >= 8192) || (B >= 24 && wbytes >= ((size_t)16 << 20));
-        if (e->decode_tc && !tp && use_tc && N % 8 == 0) return launch_gemm_tc_red(w, N, K, e->q8, B, Kfull, k_off, dest.acc[0], N, s, pdl);
+        // (tensor-parallel engines: the column-parallel linears — q|k|v, gate|up: local accumulator, no exchange — take it too; the
+        //  row-parallel ones RED into peers and stay on the one-shot GEMM)
+        const bool local_only = dest.n == 1 && dest.signal_flag < 0 && dest.own_cols == 0;
+        if (e->decode_tc && local_only && use_tc && N % 8 == 0) return launch_gemm_tc_red(w, N, K, e->q8, B, Kfull, k_off, dest.acc[0], N, s, pdl);
         OneshotArgs o;
         o.w = w; o.N = N; o.K = K; o.q = e->q8; o.M = B; o.ldq = Kfull; o.k_off = k_off; o.dest = dest; o.acc_ld = N; o.tp = e->tp;
         return launch_gemm_oneshot(o, s, pdl);
@@ -530,14 +535,23 @@ int step_graph(wf_engine* e, int B, int feed_back, int use_graph) {
     // accumulators first.  (Found by test_batched_equals_single_sequences once batches 2..8 moved to the batched kernels.)
     {
         const int fam = !e->fused ? 0 : (tail_path_ok(e, B) ? 1 : 2);
-        if (fam == 2 && e->last_family != 2) {
+        if (fam == 2 && e->last_family != 2) {   // (last_family: 0 per-op, 2 phase kernels, 16 + B tail kernels at batch B)
             const size_t MB = (size_t)e->cfg.max_batch;
             if (cuda_check(cudaMemsetAsync(e->acc_qkv, 0, MB * e->qkv_rows * 4, e->stream), "acc clear") ||
                 cuda_check(cudaMemsetAsync(e->acc_gu, 0, MB * 2 * e->ffn * 4, e->stream), "acc clear") ||
                 cuda_check(cudaMemsetAsync(e->acc_o, 0, MB * e->hidden * 4, e->stream), "acc clear") ||
                 cuda_check(cudaMemsetAsync(e->acc_down, 0, MB * e->hidden * 4, e->stream), "acc clear")) return WF_ERR_CUDA;
         }
-        e->last_family = fam;
+        // The batch-1 tail kernel's hand-off buffers (acc_o, acc_down, h) must hold the sentinel wherever their owner has not stored
+        // this layer's data yet; in steady state the kernel re-arms them itself, on entry from any other step form they are filled here.
+        const int famb = fam == 1 ? 16 + B : fam;
+        if (fam == 1 && e->last_family != famb) {
+            const size_t MB = (size_t)e->cfg.max_batch;
+            if (cuda_check(cudaMemsetAsync(e->acc_o, 0xff, MB * e->hidden * 4, e->stream), "hand-off arm") ||
+                cuda_check(cudaMemsetAsync(e->acc_down, 0xff, MB * e->hidden * 4, e->stream), "hand-off arm") ||
+                cuda_check(cudaMemsetAsync(e->h_full, 0xff, MB * e->ffn_full * 2, e->stream), "hand-off arm")) return WF_ERR_CUDA;
+        }
+        e->last_family = famb;
     }
     if (!use_graph) {
         e->attn_seq_hint = hint;
@@ -610,6 +624,7 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     if (T > 1) e->fused = 1;                   // the exchanges live in the phase kernels
     { const char* x = getenv("WF_HX"); if (x) e->hx = atoi(x) != 0; }
     { const char* x = getenv("WF_TAIL"); if (x) e->tail = atoi(x) != 0; }
+    { const char* x = getenv("WF_TAIL_LAM"); if (x) e->tail_lam = atoi(x); }
     { const char* x = getenv("WF_SMALL_MAX"); if (x) { e->small_max = atoi(x); if (e->small_max < 0) e->small_max = 0; if (e->small_max > 8) e->small_max = 8; } }
     { const char* x = getenv("WF_TAIL_BATCH"); if (x) e->tail_batch = atoi(x) != 0; }
     { const char* x = getenv("WF_DECODE_TC"); if (x) e->decode_tc = atoi(x) != 0; }

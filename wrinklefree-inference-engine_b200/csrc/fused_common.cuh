@@ -185,10 +185,48 @@ constexpr int QCHUNK_BYTES = 64 * QROW_BYTES;
 // Executed by the NT-thread group (thread ids 0..NT-1).  ys: K bf16 of scratch (shared); qdst: K int8
 // (shared or global, 8-byte aligned); fs/is: >= 32 floats / ints of shared scratch.
 // Returns the activation scale and Sigma q through the references (identical in every thread).
+// Flag-in-data hand-off (HandOff, optional; the batch-1 tail kernel): the source of the row (the previous phase's accumulator or bf16
+// output) is being written by OTHER CTAs of the same persistent grid.  Instead of a grid barrier followed by a load, the consumer polls
+// the words themselves: the owner of a row stores plain data over a sentinel (0xffffffff: a NaN no integer-valued accumulator and no
+// bf16 pair produced by the epilogue can equal), so one L2 hop replaces release fence + atomic arrival + acquire poll + load.
+constexpr uint32_t WF_HANDOFF_SENTINEL = 0xffffffffu;
+struct HandOff {
+    bool poll;                        // the phase's source (acc for RESID, src for PLAIN) is a hand-off buffer
+    bool use_prev;                    // RESID: activation scale / rowsum of the producing linear come from the caller (computed locally
+    float prev_scale; int prev_rowsum;   //       by every CTA one phase ago) instead of global memory written by CTA 0
+    const __nv_bfloat16* hid_sm_in;   // RESID: residual row in shared memory (kept by this CTA two phases ago) instead of global hid_in
+    __nv_bfloat16* hid_sm_out;        // RESID: keep the new residual row here
+    int* err;
+    int tag;                          // error code reported when a poll times out (identifies the phase)
+};
+// The poll must be a STRONG load (ld.relaxed.gpu): a weak ld.global.cg may be served again and again from a copy of the line in the
+// near L2 partition and never observe the owner's store (measured: every hand-off timed out with .cg loads).
+__device__ __forceinline__ uint4 ld_relaxed_gpu_u4(const void* p) {
+    uint4 r;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ uint4 handoff_poll_u4(const void* p, int* err, int tag = 3) {
+    uint4 v = ld_relaxed_gpu_u4(p);
+    if (v.x == WF_HANDOFF_SENTINEL || v.y == WF_HANDOFF_SENTINEL || v.z == WF_HANDOFF_SENTINEL || v.w == WF_HANDOFF_SENTINEL) {
+        if (err && ld_relaxed_gpu(err)) return v;            // after one timeout nothing waits any more: the step is lost anyway
+        const unsigned long long t0 = spin_now();
+        do {
+            v = ld_relaxed_gpu_u4(p);
+            if (spin_now() - t0 > WF_SPIN_BUDGET_NS) { if (err) atomicExch(err, tag); break; }
+        } while (v.x == WF_HANDOFF_SENTINEL || v.y == WF_HANDOFF_SENTINEL || v.z == WF_HANDOFF_SENTINEL || v.w == WF_HANDOFF_SENTINEL);
+    }
+    return v;
+}
+__device__ __forceinline__ float4 handoff_poll_f4(const float* p, int* err, int tag = 3) {
+    const uint4 v = handoff_poll_u4(p, err, tag);
+    return make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z), __uint_as_float(v.w));
+}
+
 template <int ID, int NT>
 __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat16* ys, int8_t* qdst, float* fs, int* is,
                                          bool write_side, float& scale_ret, int& rowsum_ret, unsigned long long* tr = nullptr,
-                                         int qmap = QMAP_PLAIN) {
+                                         int qmap = QMAP_PLAIN, const HandOff* ho = nullptr) {   // ho: GL_PLAIN sources only
     const int K = p.K;
     const int tid = threadIdx.x;
     float ss = 0.f;
@@ -202,7 +240,7 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
 #pragma unroll
             for (int u = 0; u < GU; ++u) {
                 const int k = k0 + u * NT * 8;
-                if (k < K) t[u] = ldcg_u4(row + k);
+                if (k < K) t[u] = (ho && ho->poll) ? handoff_poll_u4(row + k, ho->err, ho->tag + 1000 * (k >> 3)) : ldcg_u4(row + k);
             }
 #pragma unroll
             for (int u = 0; u < GU; ++u) {
@@ -341,9 +379,10 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
 // summation order as glue_row, so every reduction (and with it every output bit) is identical.  All global loads of the row
 // (source, accumulator, residual, gamma) are issued before the first use.  Modes EMBED / PLAIN / RESID, local accumulator only;
 // requires K <= NT * 8 * MAXIT.
+//
 template <int ID, int NT, int MAXIT>
 __device__ __forceinline__ void glue_row_regs(const GlueParams& p, int m, int8_t* qdst, float* fs, int* is, bool write_side,
-                                              float& scale_ret, int& rowsum_ret, int qmap) {
+                                              float& scale_ret, int& rowsum_ret, int qmap, const HandOff* ho = nullptr) {
     const int K = p.K;
     const int tid = threadIdx.x;
     uint4 xv[MAXIT], gv[MAXIT];
@@ -354,15 +393,20 @@ __device__ __forceinline__ void glue_row_regs(const GlueParams& p, int m, int8_t
         if (k < K) gv[it] = *reinterpret_cast<const uint4*>(p.gamma + k);
     }
     if (p.mode == GL_RESID) {
-        const int rs = p.acc_rowsum[m];
-        const float sa = p.acc_ascale[m], ws = p.acc_wscale[0];
+        const bool prev = ho && ho->use_prev;
+        const int rs = prev ? ho->prev_rowsum : p.acc_rowsum[m];
+        const float sa = prev ? ho->prev_scale : p.acc_ascale[m], ws = p.acc_wscale[0];
         const float* arow = p.acc + (size_t)m * p.acc_ld;
         const __nv_bfloat16* hrow = p.hid_in + (size_t)m * K;
         float4 a0[MAXIT], a1[MAXIT];
 #pragma unroll
         for (int it = 0; it < MAXIT; ++it) {
             const int k = (it * NT + tid) * 8;
-            if (k < K) { xv[it] = ldcg_u4(hrow + k); a0[it] = ldcg_f4(arow + k); a1[it] = ldcg_f4(arow + k + 4); }
+            if (k < K) {
+                xv[it] = (ho && ho->hid_sm_in) ? *reinterpret_cast<const uint4*>(ho->hid_sm_in + k) : ldcg_u4(hrow + k);
+                if (ho && ho->poll) { a0[it] = handoff_poll_f4(arow + k, ho->err, ho->tag + 1000 * (k >> 3)); a1[it] = handoff_poll_f4(arow + k + 4, ho->err, ho->tag + 10 + 1000 * (k >> 3)); }
+                else { a0[it] = ldcg_f4(arow + k); a1[it] = ldcg_f4(arow + k + 4); }
+            }
         }
 #pragma unroll
         for (int it = 0; it < MAXIT; ++it) {
@@ -380,6 +424,7 @@ __device__ __forceinline__ void glue_row_regs(const GlueParams& p, int m, int8_t
                 }
                 xv[it] = make_uint4(o[0], o[1], o[2], o[3]);
                 if (write_side && p.hid_out) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = xv[it];
+                if (ho && ho->hid_sm_out) *reinterpret_cast<uint4*>(ho->hid_sm_out + k) = xv[it];
             }
         }
     } else {
@@ -387,7 +432,7 @@ __device__ __forceinline__ void glue_row_regs(const GlueParams& p, int m, int8_t
 #pragma unroll
         for (int it = 0; it < MAXIT; ++it) {
             const int k = (it * NT + tid) * 8;
-            if (k < K) xv[it] = ldcg_u4(row + k);
+            if (k < K) xv[it] = (ho && ho->poll) ? handoff_poll_u4(row + k, ho->err, ho->tag + 1000 * (k >> 3)) : ldcg_u4(row + k);
         }
 #pragma unroll
         for (int it = 0; it < MAXIT; ++it) {
@@ -523,6 +568,7 @@ struct TailArgs {
     unsigned long long* bar; // [LT_MAX_PHASES] arrival counters of THIS launch site (zero-initialised once, monotonic)
     int* epoch;              // device counter of tail-path decode steps: barrier target = grid * epoch
     int bump_epoch;          // this launch (the first of a step, single phase) increments the epoch
+    int lam;                 // batch 1: flag-in-data hand-offs between the phases instead of grid barriers (the engine keeps the sentinels armed)
     int* err;                // device error word (bounded spins)
     unsigned long long* trace;   // WF_TRACE timeline taps of this launch site (32 slots) or null
 };

@@ -19,6 +19,11 @@
 //     outputs are written once by their owner — no split-K, no atomics, no zeroing duty — and gate|up can apply
 //     relu(gate)^2 * up in its epilogue; the extra CTAs of a non-divisible phase are rotated so that the bytes a CTA streams
 //     over the whole tail stay balanced;
+//   * batch 1 (the north-star shape) goes one step further: NO grid barrier between the phases.  The accumulator / h rows are
+//     hand-off buffers that hold a sentinel until their owner stores the data; the consumer's row glue polls the words it needs
+//     (one L2 hop instead of release fence + atomic arrival + acquire poll + load), every CTA keeps the residual row and the
+//     previous phase's activation scale / rowsum locally (it computed them itself), and owners re-arm the sentinels two phases
+//     after the last reader is known to be done: acc_o rows in the down epilogue, h and acc_down rows in the o epilogue;
 //   * the norm / quant prologue (fused_common.cuh glue_row) runs redundantly in every CTA (<= 8 rows), results stay in
 //     shared memory; consumers: dp4a on the tile words (M = 1) or mma.sync.m16n8k32 with the batch in the n dimension.
 #include "fused_common.cuh"
@@ -26,7 +31,7 @@
 
 namespace wf {
 
-constexpr int LT_CW = 12;                                 // consumer warps
+constexpr int LT_CW = 12;                                 // consumer warps (+ the producer warp = 12 warps: the register file is handed out per 4 warps, so 13 warps are budgeted as 16 = 128 registers per thread, 12 as 168)
 constexpr int LT_TPW = 2;                                 // adjacent tiles per consumer warp per stage
 constexpr int LT_STAGE_TILES = LT_TPW * LT_CW;            // 24 tiles = 12 KB per stage
 constexpr int LT_STAGE_BYTES = LT_STAGE_TILES * WF_TILE_BYTES;
@@ -51,11 +56,12 @@ struct TailPhase {
 };
 
 struct TailParams {
-    int nph, M, stages, act_stride, sacc_rbs, ys_elems;
+    int nph, M, stages, act_stride, sacc_rbs, ys_elems, xs_elems;   // xs: flag-in-data form, the residual row kept from phase 1 to phase 3
     TailPhase ph[LT_MAX_PHASES];
     unsigned long long* bar;     // [LT_MAX_PHASES] monotonic arrival counters of this launch site
     int* epoch;                  // tail-path decode steps so far (device counter): barrier target = grid * epoch
     int bump_epoch;              // the first launch of a step (single phase, no barrier) increments it
+    int lam;                     // 1 (M = 1, every K <= 9216): phases hand their outputs over flag-in-data (fused_common.cuh HandOff), no grid barrier
     int* err;
     unsigned long long* trace;   // WF_TRACE timeline taps (CTA 0): [0] entry, [1] dependency wait done, then per phase 5 stamps
 };
@@ -95,13 +101,14 @@ __device__ __forceinline__ void lt_grid_barrier(unsigned long long* slot, unsign
     group_bar<1, LT_CT>();
 }
 
-template <int MR>
+template <int MR, bool LAM>
 __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_constant__ TailParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* ring = smem;                                                       // stages * LT_STAGE_BYTES
     unsigned char* acts = ring + p.stages * LT_STAGE_BYTES;                           // M * act_stride
     __nv_bfloat16* ys = reinterpret_cast<__nv_bfloat16*>(acts + ((p.M * p.act_stride + 127) & ~127));
-    int* sacc = reinterpret_cast<int*>(reinterpret_cast<unsigned char*>(ys) + ((p.ys_elems * 2 + 127) & ~127));   // [rbl][8][16]
+    __nv_bfloat16* xs = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<unsigned char*>(ys) + ((p.ys_elems * 2 + 127) & ~127));
+    int* sacc = reinterpret_cast<int*>(reinterpret_cast<unsigned char*>(xs) + ((p.xs_elems * 2 + 127) & ~127));   // [rbl][8][16]
     __shared__ __align__(8) uint64_t full_bar[LT_MAX_STAGES];
     __shared__ __align__(8) uint64_t empty_bar[LT_MAX_STAGES];
     __shared__ float fs[32];
@@ -159,11 +166,14 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
 
     for (int pi = 0; pi < p.nph; ++pi) {
         const TailPhase& ph = p.ph[pi];
+        constexpr bool lam = LAM;   // (its own instantiation: the hand-off code costs registers the barrier form does not have to pay)
         if (pi > 0) {
             glue_prefetch_gamma<LT_CT>(ph.g);
-            lt_grid_barrier(p.bar + (pi - 1), bar_target, p.err);
-            // every CTA of this grid is resident now: letting the next kernel's CTAs in can no longer starve the barrier
-            if (pi == 1) pdl_launch_dependents();
+            if (!lam) {
+                lt_grid_barrier(p.bar + (pi - 1), bar_target, p.err);
+                // every CTA of this grid is resident now: letting the next kernel's CTAs in can no longer starve the barrier
+                if (pi == 1) pdl_launch_dependents();
+            }
         }
         if (tr) p.trace[2 + 5 * pi] = gtimer();          // barrier passed
         int rb_lo, rb_hi;
@@ -178,7 +188,19 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
         for (int m = 0; m < M; ++m) {
             float sc; int rsum;
             // K <= 9216 (every 2B vector): the row stays in registers between the three passes
-            if (ph.g.K <= LT_CT * 8 * 3 && ph.g.mode != GL_RELU2 && ph.g.acc_own_cols == 0)
+            if (lam) {
+                // phase 0 reads the attention kernel's output (kernel boundary); 1..3 read what phase pi-1 is still writing.  The residual
+                // row of phase 1 (hid + o) stays in shared memory for phase 3; scale / rowsum of the producing linear are this CTA's own.
+                HandOff ho;
+                ho.poll = pi > 0; ho.use_prev = pi > 0; ho.prev_scale = s_scale[0]; ho.prev_rowsum = s_rsum[0];
+                ho.hid_sm_in = (pi == 3) ? xs : nullptr;
+                ho.hid_sm_out = (pi == 1) ? xs : nullptr;
+                ho.err = p.err; ho.tag = 300 + pi;
+                if (ph.g.K <= LT_CT * 8 * 3)
+                    glue_row_regs<1, LT_CT, 3>(ph.g, m, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, MR == 1, &ho);
+                else   // a long GL_PLAIN row (8B / 70B ffn vectors): the scratch form, polling its source the same way
+                    glue_row<1, LT_CT>(ph.g, m, ys, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, nullptr, MR == 1, &ho);
+            } else if (ph.g.K <= LT_CT * 8 * 3 && ph.g.mode != GL_RELU2 && ph.g.acc_own_cols == 0)
                 glue_row_regs<1, LT_CT, 3>(ph.g, m, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, MR == 1);
             else
                 glue_row<1, LT_CT>(ph.g, m, ys, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, nullptr, MR == 1);
@@ -188,6 +210,9 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
             }
         }
         group_bar<1, LT_CT>();     // activations (and the cleared accumulators) complete
+        // flag-in-data form: having read every word of the previous phase's output means every CTA of the grid is resident (each wrote
+        // its rows), so letting the next kernel's CTAs in can no longer starve this grid
+        if (lam && pi == 1) pdl_launch_dependents();
         if (tr) p.trace[3 + 5 * pi] = gtimer();          // glue done
 
         // ---- main loop: S[m, n] += sum_k code[n, k] * a[m, k] over this CTA's row-blocks
@@ -290,6 +315,25 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
         group_bar<1, LT_CT>();
         if (tr) p.trace[5 + 5 * pi] = gtimer();          // main loop done
 
+        if (lam && (pi == 0 || pi == 2)) {
+            // re-arm the sentinels of the rows this CTA owns in buffers whose readers are all done (see the header): in the o epilogue
+            // h (this CTA's gate|up pairs) and acc_down (its down rows), in the down epilogue acc_o (its o rows)
+            auto arm = [&](const TailPhase& q, bool h_buf) {
+                int lo, hi;
+                lt_slab(q, cta, grid, lo, hi);
+                if (h_buf) {
+                    uint32_t* dst = reinterpret_cast<uint32_t*>(q.h_out) + (lo >> 1) * 8;            // 16 bf16 = 8 words per pair
+                    for (int i = tid; i < ((hi - lo) >> 1) * 8; i += LT_CT) dst[i] = WF_HANDOFF_SENTINEL;
+                } else {
+                    uint32_t* dst = reinterpret_cast<uint32_t*>(q.acc) + lo * 16;
+                    const int n = min(hi * 16, q.N) - lo * 16;
+                    for (int i = tid; i < n; i += LT_CT) dst[i] = WF_HANDOFF_SENTINEL;
+                }
+            };
+            if (pi == 0) { arm(p.ph[1], true); arm(p.ph[2], false); }
+            else arm(p.ph[0], false);
+        }
+        if (lam && (pi == 0 || pi == 2)) group_bar<1, LT_CT>();   // (the sentinels are issued before this phase's data)
         // ---- epilogue: this CTA owns every k of its rows — plain stores
         if (ph.epi == 0) {
             for (int i = tid; i < n_rbs * 32; i += LT_CT) {
@@ -336,8 +380,8 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-static size_t lt_fixed_smem(int M, int Kmax, int sacc_rbs) {
-    return (((size_t)M * (Kmax + 16) + 127) & ~(size_t)127) + (((size_t)Kmax * 2 + 127) & ~(size_t)127) + (size_t)sacc_rbs * 512 + 1024;
+static size_t lt_fixed_smem(int M, int Kmax, int sacc_rbs, int xs_elems = 0) {
+    return (((size_t)M * (Kmax + 16) + 127) & ~(size_t)127) + (((size_t)Kmax * 2 + 127) & ~(size_t)127) + (((size_t)xs_elems * 2 + 127) & ~(size_t)127) + (size_t)sacc_rbs * 512 + 1024;
 }
 
 bool layer_tail_fits(int M, int Kmax, int max_rb_per_cta) {
@@ -374,7 +418,13 @@ int launch_layer_tail(const TailArgs& a, cudaStream_t s, bool pdl) {
     p.act_stride = Kmax + 16;
     p.ys_elems = Kmax;
     p.sacc_rbs = max_rbs + 2;
-    const size_t fixed = lt_fixed_smem(a.M, Kmax, p.sacc_rbs);
+    // flag-in-data form: batch 1, the whole tail, every RESID row in the register form (hidden <= 9216), long rows only as GL_PLAIN sources
+    bool lam_ok = a.lam && a.M == 1 && a.nph >= 3;
+    for (int i = 0; i < a.nph && lam_ok; ++i)
+        if (a.ph[i].K > LT_CT * 8 * 3 && a.ph[i].g.mode != GL_PLAIN) lam_ok = false;
+    p.lam = lam_ok ? 1 : 0;
+    p.xs_elems = lam_ok ? a.ph[1].K : 0;
+    const size_t fixed = lt_fixed_smem(a.M, Kmax, p.sacc_rbs, p.xs_elems);
     int stages = (int)((220 * 1024 - fixed) / LT_STAGE_BYTES);
     if (stages > LT_MAX_STAGES) stages = LT_MAX_STAGES;
     if (stages < 3) { set_error("layer_tail: M*K=%d*%d does not fit in shared memory", a.M, Kmax); return WF_ERR_UNSUPPORTED; }
@@ -392,13 +442,15 @@ int launch_layer_tail(const TailArgs& a, cudaStream_t s, bool pdl) {
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl ? 1 : 0;
-    if (a.M == 1) return launch_check(cudaLaunchKernelEx(&cfg, layer_tail_kernel<1>, p), "layer_tail");
-    return launch_check(cudaLaunchKernelEx(&cfg, layer_tail_kernel<0>, p), "layer_tail");
+    if (a.M == 1 && p.lam) return launch_check(cudaLaunchKernelEx(&cfg, layer_tail_kernel<1, true>, p), "layer_tail");
+    if (a.M == 1) return launch_check(cudaLaunchKernelEx(&cfg, layer_tail_kernel<1, false>, p), "layer_tail");
+    return launch_check(cudaLaunchKernelEx(&cfg, layer_tail_kernel<0, false>, p), "layer_tail");
 }
 
 void layer_tail_init_attrs() {
-    cudaFuncSetAttribute(layer_tail_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    cudaFuncSetAttribute(layer_tail_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(layer_tail_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(layer_tail_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(layer_tail_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
 }
 
 }  // namespace wf
