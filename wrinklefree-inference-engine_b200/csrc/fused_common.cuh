@@ -226,7 +226,7 @@ __device__ __forceinline__ float4 handoff_poll_f4(const float* p, int* err, int 
 template <int ID, int NT>
 __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat16* ys, int8_t* qdst, float* fs, int* is,
                                          bool write_side, float& scale_ret, int& rowsum_ret, unsigned long long* tr = nullptr,
-                                         int qmap = QMAP_PLAIN, const HandOff* ho = nullptr) {   // ho: GL_PLAIN sources only
+                                         int qmap = QMAP_PLAIN) {
     const int K = p.K;
     const int tid = threadIdx.x;
     float ss = 0.f;
@@ -240,7 +240,7 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
 #pragma unroll
             for (int u = 0; u < GU; ++u) {
                 const int k = k0 + u * NT * 8;
-                if (k < K) t[u] = (ho && ho->poll) ? handoff_poll_u4(row + k, ho->err, ho->tag + 1000 * (k >> 3)) : ldcg_u4(row + k);
+                if (k < K) t[u] = ldcg_u4(row + k);
             }
 #pragma unroll
             for (int u = 0; u < GU; ++u) {

@@ -162,6 +162,22 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
     if (p.bump_epoch && cta == 0 && tid == 0) atomicAdd(p.epoch, 1);
     const unsigned long long bar_target = (unsigned long long)grid * (unsigned long long)ld_relaxed_gpu(p.epoch);
     int s = 0, ph_bit = 0;                              // ring position, continues across phases
+    // flag-in-data form: re-arm the sentinels of the rows THIS CTA owns in a hand-off buffer, once every reader of the buffer is known to
+    // be done and (at least a phase) before this CTA stores the next data there
+    auto arm = [&](const TailPhase& q, bool h_buf) {
+        int lo, hi;
+        lt_slab(q, cta, grid, lo, hi);
+        if (h_buf) {
+            uint32_t* dst = reinterpret_cast<uint32_t*>(q.h_out) + (lo >> 1) * 8;            // 16 bf16 = 8 words per gate|up pair
+            for (int i = tid; i < ((hi - lo) >> 1) * 8; i += LT_CT) dst[i] = WF_HANDOFF_SENTINEL;
+        } else {
+            uint32_t* dst = reinterpret_cast<uint32_t*>(q.acc) + lo * 16;
+            const int n = min(hi * 16, q.N) - lo * 16;
+            for (int i = tid; i < n; i += LT_CT) dst[i] = WF_HANDOFF_SENTINEL;
+        }
+    };
+    // h and acc_down: their readers were the previous launch (a kernel boundary ago); this CTA writes them in phases 1 and 2
+    if (LAM) { arm(p.ph[1], true); arm(p.ph[2], false); }
     const int arow = min(lane & 7, M - 1);
 
     for (int pi = 0; pi < p.nph; ++pi) {
@@ -196,10 +212,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
                 ho.hid_sm_in = (pi == 3) ? xs : nullptr;
                 ho.hid_sm_out = (pi == 1) ? xs : nullptr;
                 ho.err = p.err; ho.tag = 300 + pi;
-                if (ph.g.K <= LT_CT * 8 * 3)
-                    glue_row_regs<1, LT_CT, 3>(ph.g, m, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, MR == 1, &ho);
-                else   // a long GL_PLAIN row (8B / 70B ffn vectors): the scratch form, polling its source the same way
-                    glue_row<1, LT_CT>(ph.g, m, ys, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, nullptr, MR == 1, &ho);
+                glue_row_regs<1, LT_CT, 3>(ph.g, m, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, MR == 1, &ho);
             } else if (ph.g.K <= LT_CT * 8 * 3 && ph.g.mode != GL_RELU2 && ph.g.acc_own_cols == 0)
                 glue_row_regs<1, LT_CT, 3>(ph.g, m, reinterpret_cast<int8_t*>(acts + m * p.act_stride), fs, is, cta == 0, sc, rsum, MR == 1);
             else
@@ -213,6 +226,9 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
         // flag-in-data form: having read every word of the previous phase's output means every CTA of the grid is resident (each wrote
         // its rows), so letting the next kernel's CTAs in can no longer starve this grid
         if (lam && pi == 1) pdl_launch_dependents();
+        // acc_o: read by every CTA's phase-1 glue; all of them are past it, since this CTA has just read every word of h, which each
+        // CTA stores after its own phase-1 glue.  Its owner writes it again in the next launch.
+        if (lam && pi == 2) arm(p.ph[0], false);
         if (tr) p.trace[3 + 5 * pi] = gtimer();          // glue done
 
         // ---- main loop: S[m, n] += sum_k code[n, k] * a[m, k] over this CTA's row-blocks
@@ -315,25 +331,6 @@ __global__ void __launch_bounds__(LT_THREADS, 1) layer_tail_kernel(const __grid_
         group_bar<1, LT_CT>();
         if (tr) p.trace[5 + 5 * pi] = gtimer();          // main loop done
 
-        if (lam && (pi == 0 || pi == 2)) {
-            // re-arm the sentinels of the rows this CTA owns in buffers whose readers are all done (see the header): in the o epilogue
-            // h (this CTA's gate|up pairs) and acc_down (its down rows), in the down epilogue acc_o (its o rows)
-            auto arm = [&](const TailPhase& q, bool h_buf) {
-                int lo, hi;
-                lt_slab(q, cta, grid, lo, hi);
-                if (h_buf) {
-                    uint32_t* dst = reinterpret_cast<uint32_t*>(q.h_out) + (lo >> 1) * 8;            // 16 bf16 = 8 words per pair
-                    for (int i = tid; i < ((hi - lo) >> 1) * 8; i += LT_CT) dst[i] = WF_HANDOFF_SENTINEL;
-                } else {
-                    uint32_t* dst = reinterpret_cast<uint32_t*>(q.acc) + lo * 16;
-                    const int n = min(hi * 16, q.N) - lo * 16;
-                    for (int i = tid; i < n; i += LT_CT) dst[i] = WF_HANDOFF_SENTINEL;
-                }
-            };
-            if (pi == 0) { arm(p.ph[1], true); arm(p.ph[2], false); }
-            else arm(p.ph[0], false);
-        }
-        if (lam && (pi == 0 || pi == 2)) group_bar<1, LT_CT>();   // (the sentinels are issued before this phase's data)
         // ---- epilogue: this CTA owns every k of its rows — plain stores
         if (ph.epi == 0) {
             for (int i = tid; i < n_rbs * 32; i += LT_CT) {
@@ -418,10 +415,10 @@ int launch_layer_tail(const TailArgs& a, cudaStream_t s, bool pdl) {
     p.act_stride = Kmax + 16;
     p.ys_elems = Kmax;
     p.sacc_rbs = max_rbs + 2;
-    // flag-in-data form: batch 1, the whole tail, every RESID row in the register form (hidden <= 9216), long rows only as GL_PLAIN sources
-    bool lam_ok = a.lam && a.M == 1 && a.nph >= 3;
-    for (int i = 0; i < a.nph && lam_ok; ++i)
-        if (a.ph[i].K > LT_CT * 8 * 3 && a.ph[i].g.mode != GL_PLAIN) lam_ok = false;
+    // flag-in-data form: batch 1, the whole tail, every row in the register form of the glue (K <= 9216: the 2B shape).  Extending it to
+    // the 8B / 70B ffn rows through the scratch form of the glue was measured: 1.95 -> 1.92 ms (8B), 9.25 -> 9.59 ms (70B), and the extra
+    // code cost the 2B shape 8 % (profiles/r02v_summary.txt) — not kept.
+    const bool lam_ok = a.lam && a.M == 1 && a.nph >= 3 && Kmax <= LT_CT * 8 * 3;
     p.lam = lam_ok ? 1 : 0;
     p.xs_elems = lam_ok ? a.ph[1].K : 0;
     const size_t fixed = lt_fixed_smem(a.M, Kmax, p.sacc_rbs, p.xs_elems);
