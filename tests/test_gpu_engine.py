@@ -212,6 +212,29 @@ def test_layer_tail_kernel_equals_phase_kernels(B, monkeypatch):
         assert (na == nb).all()
 
 
+@pytest.mark.parametrize("shape", ["2b", "8b"])
+def test_layer_tail_handoff_forms_equal_phase_kernels(shape, monkeypatch):
+    """Batch 1 at the real layer widths: the persistent tail kernel with flag-in-data hand-offs (default at the 2B shape; the 8B ffn row
+    is too long for the register glue, so there the default IS the grid-barrier form), the same kernel with grid barriers (WF_TAIL_LAM=0) and the
+    per-phase kernels (WF_TAIL=0) must produce identical logits over a run of steps — a lost or early hand-off would flip bits."""
+    import dataclasses
+    from wf_bitnet.engine import EngineConfig
+    mk = EngineConfig.bitnet_2b if shape == "2b" else EngineConfig.llama3_8b
+    cfg = dataclasses.replace(mk(max_seq=1024, max_batch=1), layers=3, vocab=4096)
+    rng = np.random.default_rng(3)
+    steps = [[int(rng.integers(0, cfg.vocab))] for _ in range(12)]
+    runs = {}
+    for name, env in (("handoff", {"WF_TAIL": "1", "WF_TAIL_LAM": "1"}), ("barrier", {"WF_TAIL": "1", "WF_TAIL_LAM": "0"}), ("phase", {"WF_TAIL": "0", "WF_TAIL_LAM": "1"})):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        runs[name] = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=600, synthetic=9)
+    assert runs["handoff"][0][2] == runs["barrier"][0][2] < runs["phase"][0][2]          # launches per step
+    for name in ("handoff", "barrier"):
+        for i, ((la, na, _), (lb, nb, _)) in enumerate(zip(runs[name], runs["phase"])):
+            assert torch.equal(la, lb), (name, i, (la - lb).abs().max().item())
+            assert (na == nb).all()
+
+
 @pytest.mark.parametrize("B,ctx", [(1, 500), (4, 700), (16, 1200), (40, 100), (64, 300)])
 def test_phase_kernels_equal_per_op_kernels_2b_shape(B, ctx, monkeypatch):
     """same identity at the BitNet-2B layer shapes (split attention chunks, 54 k-blocks) on a 4-layer slice"""

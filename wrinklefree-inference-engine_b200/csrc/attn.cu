@@ -966,6 +966,7 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
         }
     }
     nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+    if (fused_q && cl_s && atoi(cl_s) == 2) p.cluster = 1;   // WF_ATTN_CLUSTER=2: clusters on large grids too — measured slower (5.40 vs 5.31 ms at batch 64 / 4K, profiles/r02y_summary.txt)
     if (p.cluster && (nchunks < 2 || nchunks > 8)) p.cluster = 0;
     p.chunk_blocks = chunk_blocks;
     p.max_chunks = nchunks;

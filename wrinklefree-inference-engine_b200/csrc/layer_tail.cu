@@ -417,7 +417,8 @@ int launch_layer_tail(const TailArgs& a, cudaStream_t s, bool pdl) {
     p.sacc_rbs = max_rbs + 2;
     // flag-in-data form: batch 1, the whole tail, every row in the register form of the glue (K <= 9216: the 2B shape).  Extending it to
     // the 8B / 70B ffn rows through the scratch form of the glue was measured: 1.95 -> 1.92 ms (8B), 9.25 -> 9.59 ms (70B), and the extra
-    // code cost the 2B shape 8 % (profiles/r02v_summary.txt) — not kept.
+    // code cost the 2B shape 8 % (profiles/r02v_summary.txt) — not kept.  Neither was an instantiation whose register glue holds the 8B ffn
+    // row in 5 granules per thread: 316 bytes of spills, 1.95 -> 2.69 ms (profiles/r02x_summary.txt).
     const bool lam_ok = a.lam && a.M == 1 && a.nph >= 3 && Kmax <= LT_CT * 8 * 3;
     p.lam = lam_ok ? 1 : 0;
     p.xs_elems = lam_ok ? a.ph[1].K : 0;
