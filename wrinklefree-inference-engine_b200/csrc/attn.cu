@@ -930,20 +930,44 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
         if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT8_SMEM), "attn smem")) return WF_ERR_CUDA;
     }
     const int max_blocks16 = (max_seq_hint + AT_BLK - 1) / AT_BLK;
-    // chunk size: aim for >= 4 CTAs per SM-slot (2 per SM) over the whole grid, but never below 4 blocks (64 tokens)
+    // Chunking of a sequence's KV stream over CTAs (large grids; small ones take the cluster form below).  Cost model, in units of
+    // one 16-token block of one warp-quartet: a grid of pairs * n CTAs runs in ceil(pairs * n / slots) waves, and a wave costs the
+    // chunk length plus a CTA's fixed work (q dequant + RoPE prologue, ring fill, 4-warp merge: ~C0 blocks) plus, when a pair is
+    // split, the partial store / fence / atomic / merge chain (~C1 blocks).  The old rule (>= 4 CTAs per slot, chunks >= 512 tokens)
+    // gave 8B batch 32 / 2K five chunks of 28 blocks (5 waves x 42) where one chunk per pair is 1 wave x 137.  Measured, new vs old rule
+    // (profiles/r02z_summary.txt, ms per step): 8B bs32/2K 4.27 vs 4.74, 8B bs64/2K 5.69 vs 6.10, 8B bs16/2K 3.93 vs 4.16, 70B bs16/8K
+    // 23.5 vs 24.7, 2B bs8/8K 2.51 vs 2.83, 2B bs32/2K 2.80 vs 2.88, 2B bs64/4K 5.33 vs 5.30.  WF_ATTN_WANT > 0 restores the old rule.
     const long long pairs = (long long)p.B * p.Hkv;
-    static const int want_mult = getenv("WF_ATTN_WANT") ? atoi(getenv("WF_ATTN_WANT")) : 4;
-    const long long want = (long long)want_mult * 2 * sm_count();
-    int chunks = (int)((want + pairs - 1) / pairs);
-    if (chunks < 1) chunks = 1;
-    int chunk_blocks = (max_blocks16 + chunks - 1) / chunks;
-    // a chunk split costs a partial write + an atomic + a merge (~4 us of dependent round trips): never split below 512 tokens
-    if (chunk_blocks < 32) chunk_blocks = 32;
-    chunk_blocks = (chunk_blocks + 3) & ~3;
-    int nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
-    // equal chunks for that count (129 blocks at a floor of 32 would be 32, 32, 32, 32, 1: five CTAs, four of them useful)
-    chunk_blocks = (((max_blocks16 + nchunks - 1) / nchunks) + 3) & ~3;
-    nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+    static const int want_mult = getenv("WF_ATTN_WANT") ? atoi(getenv("WF_ATTN_WANT")) : 0;
+    static const int cm_c0 = getenv("WF_ATTN_C0") ? atoi(getenv("WF_ATTN_C0")) : 8;
+    static const int cm_c1 = getenv("WF_ATTN_C1") ? atoi(getenv("WF_ATTN_C1")) : 6;
+    int chunk_blocks, nchunks;
+    if (want_mult > 0) {
+        const long long want = (long long)want_mult * 2 * sm_count();
+        int chunks = (int)((want + pairs - 1) / pairs);
+        if (chunks < 1) chunks = 1;
+        chunk_blocks = (max_blocks16 + chunks - 1) / chunks;
+        if (chunk_blocks < 32) chunk_blocks = 32;
+        chunk_blocks = (chunk_blocks + 3) & ~3;
+        nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+        chunk_blocks = (((max_blocks16 + nchunks - 1) / nchunks) + 3) & ~3;
+        nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+    } else {
+        const long long slots = (long long)(p.kv_scales ? 3 : 2) * sm_count();
+        long long best = -1;
+        chunk_blocks = (max_blocks16 + 3) & ~3; nchunks = 1;
+        for (int n = 1; n <= 64; ++n) {
+            const int cb = (((max_blocks16 + n - 1) / n) + 3) & ~3;
+            if (n > 1 && cb < 16) break;                                  // never below 256 tokens per CTA
+            const int nn = (max_blocks16 + cb - 1) / cb;
+            if (nn != n) continue;                                        // the rounding collapsed this count onto a smaller one
+            const long long waves = (pairs * nn + slots - 1) / slots;
+            // + the serial merge of nn partials by the pair's last CTA (~1.4 blocks each: batch 1 / 16K with 52 chunks of 20 blocks
+            //   measured 1.90 ms against 1.71 ms with 33 chunks of 32)
+            const long long cost = 10 * waves * (cb + cm_c0 + (nn > 1 ? cm_c1 : 0)) + (nn > 1 ? 14 * nn : 0);
+            if (best < 0 || cost < best) { best = cost; chunk_blocks = cb; nchunks = nn; }
+        }
+    }
     // Small grids (every CTA resident at once, latency-bound): the chunks of a pair form a thread-block cluster of <= 8 CTAs and
     // merge through DSMEM.  A split is cheap there (~1 us), so chunks are short (~12 blocks = 3 per warp) instead of >= 32.
     const bool fused_q = p.qkv_acc != nullptr;
