@@ -185,7 +185,7 @@ def test_lm_head_argmax():
     gen = torch.Generator().manual_seed(8)
     V, K = 128256, 2560
     E = (0.02 * torch.randn(V, K, generator=gen)).to(torch.bfloat16)
-    for B in (1, 5, 64):
+    for B in (1, 5, 16, 17, 33, 64):     # <= 16: mma.sync kernel, above: tcgen05 kind::f16 kernel (lm_head_tc.cu), partial token tiles included
         h = torch.randn(B, K, generator=gen).to(torch.bfloat16)
         nxt, logits = ops.lm_head_argmax(h.cuda(), E.cuda())
         ref = (h.float() @ E.float().t())

@@ -7,6 +7,7 @@
 #include "tp_comm.cuh"
 #include "wf_bitnet.h"
 #include "kernels.cuh"
+#include <stdlib.h>
 
 namespace wf {
 
@@ -348,7 +349,11 @@ int launch_lm_head_argmax_tp(const void* h, const void* E, int B, int V, int K, 
     float* pv = (float*)workspace;
     int* pi = (int*)(pv + (size_t)B * nparts);
     int rc;
-    if (B <= 8) rc = launch_lm<1>(h, E, B, V, K, logits_out, ldl, v_off, pv, pi, nparts, s);
+    // 17..64 tokens: tcgen05 kind::f16 kernel (lm_head_tc.cu) — operands straight from shared memory, accumulators in TMEM; the mma.sync
+    // kernel below re-reads the 64-token activation tile with every warp and stops at 65 % of the HBM peak at batch 64 (WF_LM_TC=0: off)
+    static const int lm_tc = getenv("WF_LM_TC") ? atoi(getenv("WF_LM_TC")) : 1;
+    if (lm_tc && lm_head_tc_usable(B, V, K, h, E)) rc = launch_lm_head_tc(h, E, B, V, K, logits_out, ldl, v_off, pv, pi, nparts, s, false);
+    else if (B <= 8) rc = launch_lm<1>(h, E, B, V, K, logits_out, ldl, v_off, pv, pi, nparts, s);
     else if (B <= 16) rc = launch_lm<2>(h, E, B, V, K, logits_out, ldl, v_off, pv, pi, nparts, s);
     else if (B <= 32) rc = launch_lm<4>(h, E, B, V, K, logits_out, ldl, v_off, pv, pi, nparts, s);
     else rc = launch_lm<8>(h, E, B, V, K, logits_out, ldl, v_off, pv, pi, nparts, s);

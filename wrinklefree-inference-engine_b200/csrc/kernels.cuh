@@ -40,5 +40,10 @@ void attn_init_attrs();
 void lm_init_attrs();
 void quant_init_attrs();
 void gemm_tc_init_attrs();
-inline void init_all_kernel_attrs() { gemm_mma_init_attrs(); gemv_stream_init_attrs(); attn_init_attrs(); lm_init_attrs(); quant_init_attrs(); gemm_tc_init_attrs(); }
+void lm_head_tc_init_attrs();
+inline void init_all_kernel_attrs() { gemm_mma_init_attrs(); gemv_stream_init_attrs(); attn_init_attrs(); lm_init_attrs(); quant_init_attrs(); gemm_tc_init_attrs(); lm_head_tc_init_attrs(); }
+// tcgen05 LM head for 9..64 tokens (lm_head_tc.cu); same outputs as the mma.sync kernel in glue.cu
+bool lm_head_tc_usable(int B, int V, int K, const void* h, const void* E);
+int launch_lm_head_tc(const void* h, const void* E, int B, int V, int K, float* logits_out, int ldl, int v_off, float* pv, int* pi, int nparts,
+                      cudaStream_t s, bool pdl);
 }
