@@ -968,6 +968,13 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
             if (best < 0 || cost < best) { best = cost; chunk_blocks = cb; nchunks = nn; }
         }
     }
+    {   // experiments: WF_ATTN_NCHUNKS forces the chunk count of the large-grid form
+        static const int force_n = getenv("WF_ATTN_NCHUNKS") ? atoi(getenv("WF_ATTN_NCHUNKS")) : 0;
+        if (force_n > 0) {
+            chunk_blocks = (((max_blocks16 + force_n - 1) / force_n) + 3) & ~3;
+            nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+        }
+    }
     // Small grids (every CTA resident at once, latency-bound): the chunks of a pair form a thread-block cluster of <= 8 CTAs and
     // merge through DSMEM.  A split is cheap there (~1 us), so chunks are short (~12 blocks = 3 per warp) instead of >= 32.
     const bool fused_q = p.qkv_acc != nullptr;
