@@ -108,6 +108,8 @@ struct AttnParams {
     int direct;                  // 1: single chunk per sequence everywhere -> write final output
     int cluster;                 // 1 (fused form, small grids): the chunks of a (sequence, kv head) pair are ONE thread-block cluster; their partials
                                  // meet in distributed shared memory (two cluster barriers) instead of global memory + fence + atomic + reload
+    int two_pa, two_nb;          // two-class grid (fused form): the first two_pa pairs are ONE CTA each (no split, no merge), every later pair is
+                                 // two_nb CTAs of chunk_blocks blocks; 1-D grid, long CTAs first (two_nb = 0: uniform grid)
     int chunk_major;             // legacy grid order: 1 = (kv head, sequence, chunk), 0 = (chunk, kv head, sequence)
     int even;                    // 1 (fused form only): the grid is ONE wave of persistent CTAs and the (sequence, kv head, block) space is cut
                                  // into gridDim.x equal contiguous ranges (see the kernel); chunk_blocks / max_chunks / direct are unused
@@ -213,15 +215,25 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
     if (!(FUSED && p.even)) {
         if (seg_i > 0) break;
         // chunk index slowest in the dispatch order: the last (shortest) chunk of every sequence forms the final partial wave
-        if (p.chunk_major) { kvh = blockIdx.x; b = blockIdx.y; chunk = blockIdx.z; }
+        int cbk = p.chunk_blocks;
+        bool whole = false;
+        if (FUSED && p.two_nb > 0) {
+            // two-class grid: as many whole pairs as fill the resident slots exactly stream unsplit; the leftover pairs — which would run
+            // as a thin second wave at a fraction of the HBM bandwidth — are cut fine enough to fill one short wave of their own
+            int pair;
+            if (bid < p.two_pa) { pair = bid; chunk = 0; whole = true; }
+            else { const int j = bid - p.two_pa; pair = p.two_pa + j / p.two_nb; chunk = j - (pair - p.two_pa) * p.two_nb; }
+            b = pair / p.Hkv; kvh = pair - b * p.Hkv;
+        } else if (p.chunk_major) { kvh = blockIdx.x; b = blockIdx.y; chunk = blockIdx.z; }
         else { chunk = blockIdx.x; kvh = blockIdx.y; b = blockIdx.z; }
         seq_len = p.seq_lens[b];
         nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
-        blk0 = chunk * p.chunk_blocks;
+        if (whole) cbk = max(nblocks, 1);
+        blk0 = chunk * cbk;
         active = !(blk0 >= nblocks && chunk != 0);
-        blk1 = min(nblocks, blk0 + p.chunk_blocks);
-        seg_direct = p.direct != 0;
-        nch = (nblocks + p.chunk_blocks - 1) / p.chunk_blocks;
+        blk1 = min(nblocks, blk0 + cbk);
+        seg_direct = whole || p.direct != 0;
+        nch = (nblocks + cbk - 1) / cbk;
         my_c = chunk;
     } else {
         if (x_lin >= x_hi) break;
@@ -930,30 +942,43 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
         if (cuda_check(cudaFuncSetAttribute(paged_decode_attn_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT8_SMEM), "attn smem")) return WF_ERR_CUDA;
     }
     const int max_blocks16 = (max_seq_hint + AT_BLK - 1) / AT_BLK;
-    // Chunking of a sequence's KV stream over CTAs (large grids; small ones take the cluster form below).  Cost model, in units of
-    // one 16-token block of one warp-quartet: a grid of pairs * n CTAs runs in ceil(pairs * n / slots) waves, and a wave costs the
-    // chunk length plus a CTA's fixed work (q dequant + RoPE prologue, ring fill, 4-warp merge: ~C0 blocks) plus, when a pair is
-    // split, the partial store / fence / atomic / merge chain (~C1 blocks).  The old rule (>= 4 CTAs per slot, chunks >= 512 tokens)
-    // gave 8B batch 32 / 2K five chunks of 28 blocks (5 waves x 42) where one chunk per pair is 1 wave x 137.  Measured, new vs old rule
-    // (profiles/r02z_summary.txt, ms per step): 8B bs32/2K 4.27 vs 4.74, 8B bs64/2K 5.69 vs 6.10, 8B bs16/2K 3.93 vs 4.16, 70B bs16/8K
-    // 23.5 vs 24.7, 2B bs8/8K 2.51 vs 2.83, 2B bs32/2K 2.80 vs 2.88, 2B bs64/4K 5.33 vs 5.30.  WF_ATTN_WANT > 0 restores the old rule.
+    // Chunking of a sequence's KV stream over CTAs (large grids; small ones take the cluster form below).  Cost model, calibrated on
+    // forced chunk counts (profiles/r02ab_summary.txt, r02ac_summary.txt), in units of one 16-token block of a CTA:
+    //   * J = pairs * n CTAs of length L = chunk + C0 (prologue, ring fill, 4-warp merge) run in waves of `slots` resident CTAs;
+    //   * the KV stream is bandwidth-bound long before every slot is busy: R ~ 3/8 of the slots saturate HBM, so a wave of m >= R
+    //     CTAs takes m * L / R, a wave of fewer takes L (each CTA then runs at its own latency-bound rate);
+    //   * a split pair pays 1.4 blocks per partial for the serial merge by its last CTA.
+    // Consequences the old rule (>= 4 CTAs per slot, chunks >= 512 tokens) missed: with pairs between R and `slots` ONE chunk per pair
+    // is best (8B bs32/2K 4.74 -> 4.21 ms, 2B bs32/2K 2.88 -> 2.55, 2B bs48/4K 4.54 -> 4.41, 70B bs16/8K 24.7 -> 22.9), while
+    // pairs just above `slots` (2B bs64: 320 on 296) need the split to dissolve the 24-CTA second wave (n = 1: 5.81 ms, n = 4: 5.28).
+    // Among 3..5 chunks the model's differences there are ~3 % and the measured ones ~1 %, so the old rule's count keeps the tie.
     const long long pairs = (long long)p.B * p.Hkv;
     static const int want_mult = getenv("WF_ATTN_WANT") ? atoi(getenv("WF_ATTN_WANT")) : 0;
-    static const int cm_c0 = getenv("WF_ATTN_C0") ? atoi(getenv("WF_ATTN_C0")) : 8;
-    static const int cm_c1 = getenv("WF_ATTN_C1") ? atoi(getenv("WF_ATTN_C1")) : 6;
+    static const int cm_c0 = getenv("WF_ATTN_C0") ? atoi(getenv("WF_ATTN_C0")) : 10;
     int chunk_blocks, nchunks;
-    if (want_mult > 0) {
-        const long long want = (long long)want_mult * 2 * sm_count();
+    int old_cb, old_n;
+    {
+        const long long want = (long long)(want_mult > 0 ? want_mult : 4) * 2 * sm_count();
         int chunks = (int)((want + pairs - 1) / pairs);
         if (chunks < 1) chunks = 1;
-        chunk_blocks = (max_blocks16 + chunks - 1) / chunks;
-        if (chunk_blocks < 32) chunk_blocks = 32;
-        chunk_blocks = (chunk_blocks + 3) & ~3;
-        nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
-        chunk_blocks = (((max_blocks16 + nchunks - 1) / nchunks) + 3) & ~3;
-        nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+        old_cb = (max_blocks16 + chunks - 1) / chunks;
+        if (old_cb < 32) old_cb = 32;
+        old_cb = (old_cb + 3) & ~3;
+        old_n = (max_blocks16 + old_cb - 1) / old_cb;
+        old_cb = (((max_blocks16 + old_n - 1) / old_n) + 3) & ~3;
+        old_n = (max_blocks16 + old_cb - 1) / old_cb;
+    }
+    if (want_mult > 0) {
+        chunk_blocks = old_cb; nchunks = old_n;
     } else {
         const long long slots = (long long)(p.kv_scales ? 3 : 2) * sm_count();
+        const long long R = slots * 3 / 8;
+        auto model = [&](int nn, int cb) -> long long {
+            const long long J = pairs * nn, L = cb + cm_c0;
+            const long long full = J / slots, rem = J % slots;
+            auto wave = [&](long long m) -> long long { return m >= R ? m * L * 10 / R : (m > 0 ? L * 10 : 0); };
+            return full * wave(slots) + wave(rem) + (nn > 1 ? 14 * nn : 0);
+        };
         long long best = -1;
         chunk_blocks = (max_blocks16 + 3) & ~3; nchunks = 1;
         for (int n = 1; n <= 64; ++n) {
@@ -961,12 +986,10 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
             if (n > 1 && cb < 16) break;                                  // never below 256 tokens per CTA
             const int nn = (max_blocks16 + cb - 1) / cb;
             if (nn != n) continue;                                        // the rounding collapsed this count onto a smaller one
-            const long long waves = (pairs * nn + slots - 1) / slots;
-            // + the serial merge of nn partials by the pair's last CTA (~1.4 blocks each: batch 1 / 16K with 52 chunks of 20 blocks
-            //   measured 1.90 ms against 1.71 ms with 33 chunks of 32)
-            const long long cost = 10 * waves * (cb + cm_c0 + (nn > 1 ? cm_c1 : 0)) + (nn > 1 ? 14 * nn : 0);
+            const long long cost = model(nn, cb);
             if (best < 0 || cost < best) { best = cost; chunk_blocks = cb; nchunks = nn; }
         }
+        if (model(old_n, old_cb) * 100 <= best * 104) { chunk_blocks = old_cb; nchunks = old_n; }
     }
     {   // experiments: WF_ATTN_NCHUNKS forces the chunk count of the large-grid form
         static const int force_n = getenv("WF_ATTN_NCHUNKS") ? atoi(getenv("WF_ATTN_NCHUNKS")) : 0;
@@ -1025,6 +1048,24 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
         }
     }
     if (p.even) p.cluster = 0;
+    // Two-class grid (see the kernel): pairs = q * slots + r with a thin remainder r < R.
+    p.two_pa = 0; p.two_nb = 0;
+    {
+        static const int two_env = getenv("WF_ATTN_TWO") ? atoi(getenv("WF_ATTN_TWO")) : 1;
+        const long long slots = (long long)(i8_pool ? 3 : 2) * sm_count();
+        const long long q = pairs / slots, r = pairs % slots;
+        if (two_env && fused_form && !p.even && !p.cluster && q >= 1 && r > 0 && r < slots * 3 / 8 && max_blocks16 >= 64) {
+            int nb2 = (int)(slots / r);
+            if (nb2 > max_blocks16 / 16) nb2 = max_blocks16 / 16;        // >= 256 tokens per CTA
+            if (nb2 > 16) nb2 = 16;
+            if (nb2 >= 2) {
+                chunk_blocks = (((max_blocks16 + nb2 - 1) / nb2) + 3) & ~3;
+                nchunks = (max_blocks16 + chunk_blocks - 1) / chunk_blocks;
+                p.chunk_blocks = chunk_blocks; p.max_chunks = nchunks; p.direct = 0;
+                p.two_pa = (int)(q * slots); p.two_nb = nchunks;
+            }
+        }
+    }
     if (!p.direct && !p.even && !p.cluster) {
         const size_t need = (size_t)p.B * p.H * nchunks * (AT_D + 2) * sizeof(float);
         if (!workspace || workspace_bytes < need) { set_error("paged_decode_attn: workspace too small (%zu < %zu)", workspace_bytes, need); return WF_ERR_INVALID; }
@@ -1039,7 +1080,8 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     {
         cudaLaunchConfig_t cfg = {};
         const int nchg = nchunks < 1 ? 1 : nchunks;
-        cfg.gridDim = p.even ? dim3(even_ctas) : (p.chunk_major ? dim3(p.Hkv, p.B, nchg) : dim3(nchg, p.Hkv, p.B));
+        cfg.gridDim = p.even ? dim3(even_ctas) : p.two_nb > 0 ? dim3((unsigned)(p.two_pa + (pairs - p.two_pa) * p.two_nb))
+                             : (p.chunk_major ? dim3(p.Hkv, p.B, nchg) : dim3(nchg, p.Hkv, p.B));
         cfg.blockDim = dim3(AT_WARPS * 32);
         const bool i8 = p.kv_scales != nullptr;
         cfg.dynamicSmemBytes = i8 ? AT8_SMEM : AT_SMEM;
