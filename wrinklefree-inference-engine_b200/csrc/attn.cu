@@ -1051,11 +1051,13 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     // Two-class grid (see the kernel): pairs = q * slots + r with a thin remainder r < R.
     p.two_pa = 0; p.two_nb = 0;
     {
-        static const int two_env = getenv("WF_ATTN_TWO") ? atoi(getenv("WF_ATTN_TWO")) : 1;
+        const char* two_s = getenv("WF_ATTN_TWO");   // read per launch: the parity test switches it inside one process
+        const int two_env = two_s ? atoi(two_s) : 1;
         const long long slots = (long long)(i8_pool ? 3 : 2) * sm_count();
         const long long q = pairs / slots, r = pairs % slots;
         if (two_env && fused_form && !p.even && !p.cluster && q >= 1 && r > 0 && r < slots * 3 / 8 && max_blocks16 >= 64) {
-            int nb2 = (int)(slots / r);
+            static const int two_fill = getenv("WF_ATTN_TWO_FILL") ? atoi(getenv("WF_ATTN_TWO_FILL")) : 4;   // eighths of the slots the short wave fills: measured 8: 5.22, 6: 5.14, 4: 5.07, 3: 5.09 ms (bs64/4K; uniform grid 5.29)
+            int nb2 = (int)((slots * two_fill / 8 + r - 1) / r);
             if (nb2 > max_blocks16 / 16) nb2 = max_blocks16 / 16;        // >= 256 tokens per CTA
             if (nb2 > 16) nb2 = 16;
             if (nb2 >= 2) {
