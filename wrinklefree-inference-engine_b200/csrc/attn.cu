@@ -108,6 +108,8 @@ struct AttnParams {
     int direct;                  // 1: single chunk per sequence everywhere -> write final output
     int cluster;                 // 1 (fused form, small grids): the chunks of a (sequence, kv head) pair are ONE thread-block cluster; their partials
                                  // meet in distributed shared memory (two cluster barriers) instead of global memory + fence + atomic + reload
+    int two_short_first;         // two-class grid: dispatch the short CTAs before the whole pairs (WF_ATTN_TWO_ORDER=1; measured worse: 5.26 vs 5.10 ms
+                                 // at bs64/4K, 8.43 vs 8.09 at 8K, profiles/r02ag_summary.txt)
     int two_pa, two_nb;          // two-class grid (fused form): the first two_pa pairs are ONE CTA each (no split, no merge), every later pair is
                                  // two_nb CTAs of chunk_blocks blocks; 1-D grid, long CTAs first (two_nb = 0: uniform grid)
     int chunk_major;             // legacy grid order: 1 = (kv head, sequence, chunk), 0 = (chunk, kv head, sequence)
@@ -221,8 +223,10 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
             // two-class grid: as many whole pairs as fill the resident slots exactly stream unsplit; the leftover pairs — which would run
             // as a thin second wave at a fraction of the HBM bandwidth — are cut fine enough to fill one short wave of their own
             int pair;
-            if (bid < p.two_pa) { pair = bid; chunk = 0; whole = true; }
-            else { const int j = bid - p.two_pa; pair = p.two_pa + j / p.two_nb; chunk = j - (pair - p.two_pa) * p.two_nb; }
+            const int nshort = (p.B * p.Hkv - p.two_pa) * p.two_nb;
+            const int wid = p.two_short_first ? bid - nshort : bid;            // index among the whole pairs (when in range)
+            if (wid >= 0 && wid < p.two_pa) { pair = wid; chunk = 0; whole = true; }
+            else { const int j = p.two_short_first ? bid : bid - p.two_pa; pair = p.two_pa + j / p.two_nb; chunk = j - (pair - p.two_pa) * p.two_nb; }
             b = pair / p.Hkv; kvh = pair - b * p.Hkv;
         } else if (p.chunk_major) { kvh = blockIdx.x; b = blockIdx.y; chunk = blockIdx.z; }
         else { chunk = blockIdx.x; kvh = blockIdx.y; b = blockIdx.z; }
@@ -1050,6 +1054,7 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     if (p.even) p.cluster = 0;
     // Two-class grid (see the kernel): pairs = q * slots + r with a thin remainder r < R.
     p.two_pa = 0; p.two_nb = 0;
+    { static const int sf = getenv("WF_ATTN_TWO_ORDER") ? atoi(getenv("WF_ATTN_TWO_ORDER")) : 0; p.two_short_first = sf; }
     {
         const char* two_s = getenv("WF_ATTN_TWO");   // read per launch: the parity test switches it inside one process
         const int two_env = two_s ? atoi(two_s) : 1;
