@@ -515,8 +515,9 @@ void gemm_tc_init_attrs() {
     }
     if (!g_tc_cluster) {
         const char* e = getenv("WF_TC_CLUSTER");
-        g_tc_cluster = e ? atoi(e) : 1;
-        if (g_tc_cluster != 1 && g_tc_cluster != 2 && g_tc_cluster != 4) g_tc_cluster = 1;
+        // pairs of CTAs share one multicast activation tile: 2B prefill shape 2312 -> 2331 TOP/s, 8B 2146 -> 2221 (call r02ah); 4 is slower
+        g_tc_cluster = e ? atoi(e) : 2;
+        if (g_tc_cluster != 1 && g_tc_cluster != 2 && g_tc_cluster != 4) g_tc_cluster = 2;
         const char* u = getenv("WF_TC_NU");
         g_tc_nu = u ? atoi(u) : 2;     // two unpack groups: 18 warps at 112 registers (three groups = 22 warps at 88 spill)
         if (g_tc_nu < 1 || g_tc_nu > 3) g_tc_nu = 2;
