@@ -137,6 +137,19 @@ int wf_bitnet_gemv(const uint8_t* packed_i2s, const int8_t* x, float scale, int 
 int wf_bitnet_gemm(const uint8_t* packed_i2s, const int8_t* x, float scale, int M, int N, int K, float* y,
                    void* workspace, size_t workspace_bytes, void* stream);
 
+/* wf_bitnet_gemm with no caller workspace and no allocation of any kind (M = 1 is bitnet_gemv).
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The split-K accumulators and tile
+ * counters live in a file-scope __device__ array of WF_STATIC_WS_BYTES inside the library (csrc/no_alloc.cu), held by every
+ * GPU that loads it until exit.  Same kernel and same bits as wf_bitnet_gemm.  Shapes whose scratch
+ * (wf_linear_workspace_bytes(M, N, K) = 4*M*N + 4*ceil(N/16)*ceil(M/8) + 256 bytes) exceeds the array return
+ * WF_ERR_UNSUPPORTED with the sizes in wf_last_error().  All calls on a device share the array and each call clears
+ * the part it uses on `stream` first: calls that overlap on the GPU (different streams) race — serialise them. */
+#define WF_STATIC_WS_BYTES (4u << 20)
+size_t wf_static_workspace_max_bytes(void);
+int wf_bitnet_gemm_static(const uint8_t* packed_i2s, const int8_t* x, float scale, int M, int N, int K, float* y,
+                          void* stream);
+
 /* ---- paged KV cache + decode attention (north-star item 5) ------------ */
 
 /* Pool layout: [max_pages][L][2][Hkv][page_size][D] bf16 — one (page, layer, K|V, head) block is

@@ -72,6 +72,8 @@ SYMBOLS = {
     "wf_ternary_linear": (_i, [C.POINTER(LinearArgs), _vp]),
     "wf_bitnet_gemv": (_i, [_vp, _vp, _f, _i, _i, _vp, _vp, _sz, _vp]),
     "wf_bitnet_gemm": (_i, [_vp, _vp, _f, _i, _i, _i, _vp, _vp, _sz, _vp]),
+    "wf_static_workspace_max_bytes": (_sz, []),
+    "wf_bitnet_gemm_static": (_i, [_vp, _vp, _f, _i, _i, _i, _vp, _vp]),
     "wf_kv_pool_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
     "wf_kv_scatter": (_i, [C.POINTER(KvLayout), _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "wf_kv_gather": (_i, [C.POINTER(KvLayout), _vp, _vp, _vp, _vp, _i, _i, _vp]),
