@@ -238,6 +238,31 @@ def test_attention_two_class_grid_matches_uniform_grid(kv, monkeypatch):
     assert (na == nb).mean() >= 0.9
 
 
+@pytest.mark.parametrize("kv", ["bf16", "int8"])
+def test_attention_per_sequence_chunks_match_fixed_chunks(kv, monkeypatch):
+    """Sequences of 1100 tokens under a 2048-token length hint (max_seq 4096): fixed chunks of the hint leave the later chunks of a
+    pair nearly empty, per-sequence chunking (default) cuts the actual length evenly.  Same attention output up to the summation order
+    of the softmax partials (tolerance of the two-class test)."""
+    from wf_bitnet.engine import EngineConfig
+    B, ctx = 64, 1100
+    cfg = EngineConfig.bitnet_2b(max_seq=4096, max_batch=B, layers=1, vocab=4096)
+    if kv == "int8":
+        cfg.kv_dtype = "int8"
+    rng = np.random.default_rng(72)
+    steps = [list(map(int, rng.integers(0, cfg.vocab, B))) for _ in range(2)]
+    taps = (("attn", (cfg.max_batch, cfg.heads * cfg.head_dim), torch.bfloat16),)
+    monkeypatch.setenv("WF_ATTN_ADAPT", "1")
+    a = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=ctx, synthetic=5, taps=taps)
+    monkeypatch.setenv("WF_ATTN_ADAPT", "0")
+    b = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=ctx, synthetic=5, taps=taps)
+    (la, na, _, xa), (lb, nb, _, xb) = a[0], b[0]
+    xa, xb = xa[:B].float(), xb[:B].float()
+    assert torch.isfinite(xa).all() and xa.abs().max() > 0
+    assert (xa - xb).abs().max().item() <= 2.0 ** -7 * xb.abs().max().item()
+    assert (xa != xb).float().mean().item() < 0.2
+    assert (na == nb).mean() >= 0.9
+
+
 @pytest.mark.parametrize("shape", ["2b", "8b"])
 def test_layer_tail_handoff_forms_equal_phase_kernels(shape, monkeypatch):
     """Batch 1 at the real layer widths: the persistent tail kernel with flag-in-data hand-offs (default at the 2B shape; the 8B ffn row

@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--shape", default="2b", choices=["2b", "8b", "70b"])
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (0 = the shape's own)")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--kv", default="bf16", choices=["bf16", "int8"], help="KV cache precision")
     ap.add_argument("--tp-shard", type=int, default=0, help="single-GPU stand-in for ONE rank of a TP=n engine: heads, kv heads and ffn divided by n "
                                                           "(the compute of a rank without the exchanges)")
     args = ap.parse_args()
@@ -39,6 +40,8 @@ def main():
     torch.cuda.set_device(0)
     mk = {"2b": EngineConfig.bitnet_2b, "8b": EngineConfig.llama3_8b, "70b": EngineConfig.llama3_70b}[args.shape]
     kw = dict(max_seq=args.ctx + 64, page_size=16, max_batch=args.batch)
+    if args.kv == "int8":
+        kw["kv_dtype"] = "int8"
     cfg = mk(**kw)
     if args.layers:
         cfg.layers = args.layers
@@ -63,7 +66,7 @@ def main():
     e1.record(ext)
     e1.synchronize()
     torch.cuda.profiler.stop()
-    print(f"batch={args.batch} ctx={args.ctx} shape={args.shape} steps={args.steps} ms_per_step={e0.elapsed_time(e1) / args.steps:.4f} "
+    print(f"batch={args.batch} ctx={args.ctx} shape={args.shape} kv={args.kv} steps={args.steps} ms_per_step={e0.elapsed_time(e1) / args.steps:.4f} "
           f"launches_per_step={eng.launches_per_step()}")
     eng.close()
 

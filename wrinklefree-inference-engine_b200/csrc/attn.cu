@@ -100,6 +100,8 @@ struct AttnParams {
     int page_shift;              // log2(page_size) when it is a power of two, else -1
     int chunk_blocks;            // 16-token blocks per CTA
     int max_chunks;              // partial slots per (b, h)
+    int min_cb;                  // > 0: a sequence's ACTUAL blocks are cut into max_chunks near-equal chunks of >= min_cb blocks (chunk_blocks, which
+                                 // the host derives from the graph's length hint, is then only the upper bound); 0: fixed chunk_blocks
     float scale_log2e;           // softmax scale * log2(e)
     void* out;                   // [B][H][D] bf16 or f32
     int out_dtype;
@@ -157,18 +159,32 @@ __device__ __forceinline__ size_t kv_scale_offset(int page, int layers, int laye
     return ((((size_t)page * layers + layer) * 2 + kv) * Hkv + head) * (size_t)page_size;
 }
 
+// Blocks per chunk of a sequence with `nblocks` 16-token blocks.  The host sizes chunk_blocks from the length HINT of the captured graph
+// (a power of two >= the longest sequence); a sequence well below the hint would fill only the first chunks (2049 tokens under a 4096
+// hint: chunks of 128 + 1 blocks) — so every (sequence, kv head) pair cuts its own length evenly.  Same value in every CTA of the pair
+// and in the merge kernel (it depends on seq_lens only).
+__device__ __forceinline__ int chunk_blocks_of(int nblocks, int chunk_blocks, int max_chunks, int min_cb) {
+    if (min_cb <= 0 || max_chunks <= 1) return chunk_blocks;
+    int c = ((max(nblocks, 1) + max_chunks - 1) / max_chunks + 3) & ~3;
+    c = max(c, min_cb);
+    return min(c, chunk_blocks);
+}
+
 template <bool FUSED, bool I8>
 __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_kernel(const AttnParams p) {
     constexpr int ST = I8 ? AT8_STAGES : AT_STAGES;
     constexpr int SB = I8 ? AT8_STAGE_BYTES : AT_STAGE_BYTES;
     constexpr int ROW = I8 ? AT8_ROW : AT_ROW;
+    // the even form (opt-in, measured slower) is not compiled into the int8 kernel: its range state pushed that instantiation over the
+    // 170 registers three CTAs per SM allow (80 bytes of spills in an issue-bound loop; 84 vs 74 us per layer at batch 64 / 4K)
+    constexpr bool EVEN_OK = FUSED && !I8;
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     const int nctas = gridDim.x * gridDim.y * gridDim.z;
     const int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
 
-    const bool tr = FUSED && p.trace && bid == 0 && threadIdx.x == 0;
+    const bool tr = FUSED && !I8 && p.trace && bid == 0 && threadIdx.x == 0;
     if (tr) p.trace[0] = gtimer();
     if (FUSED) pdl_launch_dependents();
 
@@ -186,7 +202,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
     __shared__ int s_cum[AT_EVEN_MAXB + 1];
     __shared__ int s_wsum[AT_WARPS];
     long long W = 0, x_lin = 0, x_hi = 0;
-    if (FUSED && p.even) {
+    if (EVEN_OK && p.even) {
         int nbv = 0;
         if (tid < p.B) nbv = max(1, (p.seq_lens[tid] + AT_BLK - 1) / AT_BLK) * p.Hkv;
         int incl = nbv;
@@ -214,7 +230,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
     int chunk, kvh, b, seq_len, nblocks, blk0, blk1;
     bool active, seg_direct;
     int nch = 1, my_c = 0, seg_c0 = 0, seg_c0_which = 0;   // partials of the pair: count, this CTA's index, first CTA, its slot
-    if (!(FUSED && p.even)) {
+    if (!(EVEN_OK && p.even)) {
         if (seg_i > 0) break;
         // chunk index slowest in the dispatch order: the last (shortest) chunk of every sequence forms the final partial wave
         int cbk = p.chunk_blocks;
@@ -224,14 +240,15 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
             // as a thin second wave at a fraction of the HBM bandwidth — are cut fine enough to fill one short wave of their own
             int pair;
             const int nshort = (p.B * p.Hkv - p.two_pa) * p.two_nb;
-            const int wid = p.two_short_first ? bid - nshort : bid;            // index among the whole pairs (when in range)
+            const int wid = (!I8 && p.two_short_first) ? bid - nshort : bid;            // index among the whole pairs (when in range)
             if (wid >= 0 && wid < p.two_pa) { pair = wid; chunk = 0; whole = true; }
-            else { const int j = p.two_short_first ? bid : bid - p.two_pa; pair = p.two_pa + j / p.two_nb; chunk = j - (pair - p.two_pa) * p.two_nb; }
+            else { const int j = (!I8 && p.two_short_first) ? bid : bid - p.two_pa; pair = p.two_pa + j / p.two_nb; chunk = j - (pair - p.two_pa) * p.two_nb; }
             b = pair / p.Hkv; kvh = pair - b * p.Hkv;
-        } else if (p.chunk_major) { kvh = blockIdx.x; b = blockIdx.y; chunk = blockIdx.z; }
+        } else if (!I8 && p.chunk_major) { kvh = blockIdx.x; b = blockIdx.y; chunk = blockIdx.z; }
         else { chunk = blockIdx.x; kvh = blockIdx.y; b = blockIdx.z; }
         seq_len = p.seq_lens[b];
         nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
+        cbk = chunk_blocks_of(nblocks, cbk, p.max_chunks, p.min_cb);
         if (whole) cbk = max(nblocks, 1);
         blk0 = chunk * cbk;
         active = !(blk0 >= nblocks && chunk != 0);
@@ -265,11 +282,11 @@ __global__ void __launch_bounds__(AT_WARPS * 32, I8 ? 3 : 2) paged_decode_attn_k
     }
     // slot of partial c (0 .. nch-1) of this pair, head hh
     auto pslot = [&](int c, int hh) -> size_t {
-        if (!(FUSED && p.even)) return ((size_t)b * p.H + (size_t)kvh * p.G + hh) * p.max_chunks + c;
+        if (!(EVEN_OK && p.even)) return ((size_t)b * p.H + (size_t)kvh * p.G + hh) * p.max_chunks + c;
         const int which = (c == 0) ? seg_c0_which : 0;               // every later CTA starts its range inside the pair
         return ((size_t)(seg_c0 + c) * 2 + which) * 8 + hh;
     };
-    const int mstride = (FUSED && p.even) ? nch : p.max_chunks;       // row stride of the merge scratch in shared memory
+    const int mstride = (EVEN_OK && p.even) ? nch : p.max_chunks;       // row stride of the merge scratch in shared memory
     const int blk_pos = (seq_len - 1) / AT_BLK;          // block of the token appended in this step (pos = seq_len - 1)
     const int my_n = active ? (blk1 - blk0 - warp + AT_WARPS - 1) / AT_WARPS : 0;   // blocks blk0 + warp + 4*i
     const int32_t* bt = p.block_table + (size_t)b * p.max_blocks;
@@ -775,7 +792,7 @@ struct MergeParams {
     const float* part_o;
     const float* part_ml;
     const int32_t* seq_lens;
-    int H, max_chunks, chunk_tokens;
+    int H, max_chunks, chunk_blocks, min_cb;
     void* out;
     int out_dtype;
 };
@@ -785,7 +802,9 @@ __global__ void __launch_bounds__(AT_D) attn_merge_kernel(const MergeParams p) {
     const int h = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
     pdl_wait_prior();
     const int seq_len = p.seq_lens[b];
-    const int nch = (seq_len + p.chunk_tokens - 1) / p.chunk_tokens;
+    const int nblocks = (seq_len + AT_BLK - 1) / AT_BLK;
+    const int cbk = chunk_blocks_of(nblocks, p.chunk_blocks, p.max_chunks, p.min_cb);
+    const int nch = (nblocks + cbk - 1) / cbk;
     const size_t base = ((size_t)b * p.H + h) * p.max_chunks;
     float M = -INFINITY;
     for (int c = 0; c < nch; ++c) M = fmaxf(M, p.part_ml[(base + c) * 2]);
@@ -976,9 +995,11 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
         chunk_blocks = old_cb; nchunks = old_n;
     } else {
         const long long slots = (long long)(p.kv_scales ? 3 : 2) * sm_count();
-        const long long R = slots * 3 / 8;
+        // the int8 form is issue-bound, not HBM-bound: it gains from every resident CTA (R = slots).  Forced counts, profiles/r02ak_summary.txt:
+        // 2B bs32/2K one chunk 2.81 ms, two 2.45; bs48/4K one 4.09, three 3.77; bs64/4K and bs64/2K one chunk (320 CTAs on 444 slots) best
+        const long long R = p.kv_scales ? slots : slots * 3 / 8;
         auto model = [&](int nn, int cb) -> long long {
-            const long long J = pairs * nn, L = cb + cm_c0;
+            const long long J = pairs * nn, L = cb + (p.kv_scales && !getenv("WF_ATTN_C0") ? 30 : cm_c0);   // int8: n = 4 at bs64/4K predicted 14 % ahead of n = 1 with C0 = 10, measured 3 % behind
             const long long full = J / slots, rem = J % slots;
             auto wave = [&](long long m) -> long long { return m >= R ? m * L * 10 / R : (m > 0 ? L * 10 : 0); };
             return full * wave(slots) + wave(rem) + (nn > 1 ? 14 * nn : 0);
@@ -993,7 +1014,7 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
             const long long cost = model(nn, cb);
             if (best < 0 || cost < best) { best = cost; chunk_blocks = cb; nchunks = nn; }
         }
-        if (model(old_n, old_cb) * 100 <= best * 104) { chunk_blocks = old_cb; nchunks = old_n; }
+        if (!p.kv_scales && model(old_n, old_cb) * 100 <= best * 104) { chunk_blocks = old_cb; nchunks = old_n; }   // (a bf16 calibration)
     }
     {   // experiments: WF_ATTN_NCHUNKS forces the chunk count of the large-grid form
         static const int force_n = getenv("WF_ATTN_NCHUNKS") ? atoi(getenv("WF_ATTN_NCHUNKS")) : 0;
@@ -1040,7 +1061,7 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     { const char* cm = getenv("WF_ATTN_CHUNK_MAJOR"); p.chunk_major = cm ? atoi(cm) : 0; }   // measured: chunk-major dispatch 5.71 vs 5.47 ms (bs64/4K)
     int even_ctas = 0;
     p.even = 0;
-    if (fused_form && even_env && p.B <= AT_EVEN_MAXB) {
+    if (fused_form && even_env && !i8_pool && p.B <= AT_EVEN_MAXB) {
         long long nc = pairs * max_blocks16 / 32;
         const long long slots = (long long)(i8_pool ? 3 : 2) * sm_count();
         if (nc > slots) nc = slots;
@@ -1055,6 +1076,7 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     // Two-class grid (see the kernel): pairs = q * slots + r with a thin remainder r < R.
     p.two_pa = 0; p.two_nb = 0;
     { static const int sf = getenv("WF_ATTN_TWO_ORDER") ? atoi(getenv("WF_ATTN_TWO_ORDER")) : 0; p.two_short_first = sf; }
+    if (i8_pool) { p.chunk_major = 0; p.two_short_first = 0; }   // experiment orders: not compiled into the int8 kernel (register budget)
     {
         const char* two_s = getenv("WF_ATTN_TWO");   // read per launch: the parity test switches it inside one process
         const int two_env = two_s ? atoi(two_s) : 1;
@@ -1072,6 +1094,10 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
                 p.two_pa = (int)(q * slots); p.two_nb = nchunks;
             }
         }
+    }
+    {   // per-sequence chunking (WF_ATTN_ADAPT=0: fixed chunks of the hint, the round-2 parity twin); read per launch like WF_ATTN_TWO
+        const char* ad = getenv("WF_ATTN_ADAPT");
+        p.min_cb = (ad && atoi(ad) == 0) ? 0 : (p.cluster ? 4 : 16);
     }
     if (!p.direct && !p.even && !p.cluster) {
         const size_t need = (size_t)p.B * p.H * nchunks * (AT_D + 2) * sizeof(float);
@@ -1109,7 +1135,7 @@ int launch_paged_decode_attn(AttnParams p, int max_seq_hint, void* workspace, si
     if (!p.direct) {
         MergeParams mp;
         mp.part_o = p.part_o; mp.part_ml = p.part_ml; mp.seq_lens = p.seq_lens;
-        mp.H = p.H; mp.max_chunks = nchunks; mp.chunk_tokens = chunk_blocks * AT_BLK;
+        mp.H = p.H; mp.max_chunks = p.max_chunks; mp.chunk_blocks = p.chunk_blocks; mp.min_cb = p.min_cb;
         mp.out = p.out; mp.out_dtype = p.out_dtype;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(p.H, p.B);
