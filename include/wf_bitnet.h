@@ -272,6 +272,11 @@ int wf_engine_time_kernel(wf_engine* e, const char* which, int B, int iters, flo
  * 4 = fused dequant epilogue (WF_OUT_LINEAR, bf16) instead of raw int32, 8 = force the mma.sync path, 16 / 32 = force 16 / 8 consumer warps, bits 8..15 = TMA
  * ring depth in 8 KB stages (0 = default).  ms_out = average per launch. */
 int wf_bench_gemv(int N, int K, int M, int iters, int flags, float* ms_out);
+/* The engine's streaming batched GEMM on its own (csrc/gemm_stream.cu; 1 <= M <= 32 activation rows): acc[m][n] += sum_k (w[n,k]+1) * q[m,k]
+ * as exact integers in fp32 — the accumulator convention of bitnet_gemm (docs/research/sglang_optimization_plan.md:66-70) before its scale.
+ * w_tile is b200_tile_v1 (wf_repack_i2s_to_tile), q is int8 [M][ldq], acc is f32 [M][N] that the caller zeroes.  For the parity tests and
+ * kernel timing; iters > 1 repeats the launch (acc then holds iters times the sums). */
+int wf_gemm_stream_acc(const uint8_t* w_tile, int N, int K, const int8_t* q, int M, int ldq, float* acc, int iters, void* stream);
 
 #ifdef __cplusplus
 }

@@ -320,6 +320,29 @@ def test_tcgen05_decode_linears_equal_per_op_kernels(B, ctx, monkeypatch):
         assert (na == nb).all() and (nc == nb).all()
 
 
+@pytest.mark.parametrize("shape,B,ctx", [("2b", 2, 80), ("2b", 13, 200), ("2b", 32, 120), ("8b", 5, 90), ("8b", 16, 150), ("8b", 32, 60)])
+def test_streaming_decode_gemm_equals_default_kernels(shape, B, ctx, monkeypatch):
+    """WF_DECODE_STREAM=2: every decode linear of 2..32 rows on the streaming batched GEMM (gemm_stream.cu: K windows, TMA ring, masked
+    2-bit fields on mma.sync with M/8 n-tiles, fp32 REDs) — same logits, bit for bit, as the step on the default linears (one-shot /
+    tcgen05 forms; those are held against the one-kernel-per-op path by the tests above).  Both runs share the attention kernel and its
+    chunking, so any difference is the GEMM's.  2B widths: one window (K = 2560) and two windows of 27 k-blocks (K = 6912); 8B widths:
+    one window of 32 and four of 28."""
+    import dataclasses
+    from wf_bitnet.engine import EngineConfig
+    mk = EngineConfig.bitnet_2b if shape == "2b" else EngineConfig.llama3_8b
+    cfg = dataclasses.replace(mk(max_seq=1024, max_batch=B), layers=2, vocab=4096)
+    rng = np.random.default_rng(23 + B)
+    steps = [list(map(int, rng.integers(0, cfg.vocab, B))) for _ in range(3)]
+    monkeypatch.setenv("WF_DECODE_STREAM", "2")
+    a = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=ctx, synthetic=5)
+    monkeypatch.setenv("WF_DECODE_STREAM", "0")
+    c = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=ctx, synthetic=5)
+    for i, ((la, na, _), (lc, nc, _)) in enumerate(zip(a, c)):
+        assert torch.isfinite(la).all()
+        assert torch.equal(la, lc), (i, (la - lc).abs().max().item())
+        assert (na == nc).all()
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # BASELINE.json configs[0]: the full BitNet-2B-4T shape (30 layers, hidden 2560, 20/5 heads, ffn 6912, vocab 128256),
 # batch 1, 512-token prompt, 128 greedy tokens -- the protocol of extern/BitNet/utils/e2e_benchmark.py:36-53 run through

@@ -306,3 +306,26 @@ def test_wrapper_module_and_native_shim():
     assert np.array_equal(kern.gemv(native.pack_weights(wn), xa[0], 2.0), (xa[0].astype(np.float32) @ wn.T) * 2.0)
     r = benchmark_kernels(in_features=256, out_features=256, batch_size=1, num_iterations=5)
     assert "native_ms" in r and r["native_ms"] > 0
+
+
+@pytest.mark.parametrize("nk", [(4096, 4096), (4096, 14336), (6144, 4096), (28672, 4096), (2560, 6912), (3840, 2560), (13824, 2560), (1040, 1024), (8192, 8192)])
+@pytest.mark.parametrize("m", [1, 2, 5, 8, 13, 16, 24, 32])
+def test_streaming_gemm_accumulators_bit_exact(nk, m):
+    """csrc/gemm_stream.cu on its own (wf_gemm_stream_acc): sum (w+1)*a as exact integers in fp32 == the oracle's int32 row dots, on one
+    window (K <= 4096), two windows of 27 k-blocks (6912), four of 28 (14336), a short last row-block (1040 rows) — and again on a second
+    and third launch into a re-zeroed accumulator (the shared tile and the ring leave no state behind)."""
+    import ctypes as C
+    from wf_bitnet import ops
+    from wf_bitnet._lib import lib
+    n, k = nk
+    _, packed, _, q, _, _ = make(n, k, m, n * 7 + k + m)
+    want = torch.from_numpy(O.gemm_i32_fast(packed, q, 0).astype(np.float32))
+    tile = ops.i2s_to_tile(cu(packed))
+    qd = cu(q)
+    for rep in range(3):
+        acc = torch.zeros(m, n, dtype=torch.float32, device="cuda")
+        rc = lib().wf_gemm_stream_acc(tile.data_ptr(), n, k, qd.data_ptr(), m, k, acc.data_ptr(), 1, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert rc == 0, lib().wf_last_error().decode()
+        got = acc.cpu()
+        bad = (got != want).nonzero()
+        assert bad.numel() == 0, (rep, bad[:8].tolist(), got[tuple(bad[0])].item(), want[tuple(bad[0])].item())

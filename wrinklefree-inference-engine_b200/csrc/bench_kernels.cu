@@ -2,6 +2,8 @@
 // scripts/benchmark_kernels.py:28-66 does — a loop of calls, bytes = N*K/4 + M*K + out — except that the launches
 // rotate over enough independent weight copies to exceed the 126 MB L2, so the figure is an HBM figure.
 #include "kernels.cuh"
+#include "fused_common.cuh"
+#include <string.h>
 #include <vector>
 
 using namespace wf;
@@ -107,4 +109,22 @@ extern "C" int wf_bench_gemv(int N, int K, int M, int iters, int flags, float* m
     for (void* p : frees) cudaFree(p);
     cudaStreamDestroy(s);
     return rc;
+}
+
+extern "C" int wf_gemm_stream_acc(const uint8_t* w_tile, int N, int K, const int8_t* q, int M, int ldq, float* acc, int iters, void* stream) {
+    if (!w_tile || !q || !acc || iters < 1) { set_error("wf_gemm_stream_acc: bad arguments"); return WF_ERR_INVALID; }
+    if (!gemm_stream_fits(M, N, K)) { set_error("wf_gemm_stream_acc: M=%d N=%d K=%d outside the kernel's range", M, N, K); return WF_ERR_UNSUPPORTED; }
+    init_all_kernel_attrs();
+    gemm_stream_init_attrs();
+    OneshotArgs o;
+    memset(&o, 0, sizeof o);
+    o.w = w_tile; o.N = N; o.K = K; o.q = q; o.M = M; o.ldq = ldq; o.k_off = 0;
+    o.dest.n = 1; o.dest.own_cols = 0; o.dest.acc[0] = acc; o.dest.signal_flag = -1;
+    o.acc_ld = N;
+    o.tp.size = 1;
+    for (int it = 0; it < iters; ++it) {
+        const int rc = launch_gemm_stream(o, (cudaStream_t)stream, false);
+        if (rc) return rc;
+    }
+    return WF_OK;
 }

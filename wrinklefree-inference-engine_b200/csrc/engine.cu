@@ -79,6 +79,10 @@ struct wf_engine {
     int decode_tc = 1;       // batched decode linears (B >= decode_tc_min, single GPU) on tcgen05 split-K REDs (gemm_tc.cu launch_gemm_tc_red) instead of the mma.sync one-shot
                              // GEMM: bit-identical; with the round-2 issue loop / epilogue 3.65 -> 3.23 ms at batch 40 / 2K, 5.48 -> 5.32 ms at batch 64 / 4K (WF_DECODE_TC=0: off)
     int decode_tc_min = 33;  // WF_DECODE_TC_MIN
+    int decode_stream = 1;   // WF_DECODE_STREAM: streaming batched GEMM (gemm_stream.cu); 0 off, 1 = batches up to decode_stream_max rows, 2 = every batch it takes (<= 32)
+    int decode_stream_max = 16;   // WF_DECODE_STREAM_MAX.  Measured (profiles/r02ap_summary.txt), ms per step stream / default: 2B bs2 1.33 / 1.58, bs8 1.43 / 1.63,
+                                  // bs16/2K 1.99 / 2.17; 8B bs4 1.97 / 3.00, bs8 2.26 / 3.24, bs16/2K 3.06 / 3.85; 70B bs16/8K 20.0 / 22.9; but 17..32 rows (four n-tiles,
+                                  // one CTA per SM): 2B bs32/2K 2.74 / 2.56, 8B bs32/2K 4.55 / 4.20
     int tail_batch = 0;      // WF_TAIL_BATCH=1: the same for 8 < B <= 64 (layer_tail_batch.cu).  Opt-in: measured 5.74 ms vs 5.44 ms per bs64/4K step for the phase path (profiles/r02d_*)
     int small_max = 1;       // WF_SMALL_MAX: largest batch on the GEMV-style kernels (linear_small / layer_tail: the row glue runs per CTA and per row,
                              // ~3 us x B x 4 phases per layer); above it the batched kernels (row glue once per row in its own CTA + batched GEMM).
@@ -381,6 +385,11 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
         // tokens up; from 9 tokens for K >= 8192 (70B shapes); from 24 tokens for >= 16 MB matrices.  Measured in profiles/r02q_summary.txt:
         // 70B bs16 32.2 -> 24.6 ms, 8B bs32 4.95 -> 4.84 ms, while 8B bs16 gate|up (29 MB, K = 4096) is faster on the one-shot GEMM.
         const size_t wbytes = (size_t)N * K / 4;
+        if (e->decode_stream && B <= (e->decode_stream >= 2 ? 32 : e->decode_stream_max) && gemm_stream_fits(B, N, K)) {
+            OneshotArgs o;
+            o.w = w; o.N = N; o.K = K; o.q = e->q8; o.M = B; o.ldq = Kfull; o.k_off = k_off; o.dest = dest; o.acc_ld = N; o.tp = e->tp;
+            return launch_gemm_stream(o, s, pdl);
+        }
         const bool use_tc = B >= e->decode_tc_min || (B >= 9 && K >= 8192) || (B >= 24 && wbytes >= ((size_t)16 << 20));
         // (tensor-parallel engines: the column-parallel linears — q|k|v, gate|up: local accumulator, no exchange — take it too; the
         //  row-parallel ones RED into peers and stay on the one-shot GEMM)
@@ -629,6 +638,8 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     { const char* x = getenv("WF_TAIL_BATCH"); if (x) e->tail_batch = atoi(x) != 0; }
     { const char* x = getenv("WF_DECODE_TC"); if (x) e->decode_tc = atoi(x) != 0; }
     { const char* x = getenv("WF_DECODE_TC_MIN"); if (x) e->decode_tc_min = atoi(x) < 2 ? 2 : atoi(x); }
+    { const char* x = getenv("WF_DECODE_STREAM"); if (x) e->decode_stream = atoi(x); }
+    { const char* x = getenv("WF_DECODE_STREAM_MAX"); if (x) e->decode_stream_max = atoi(x) < 1 ? 1 : (atoi(x) > 32 ? 32 : atoi(x)); }
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
     int rc = WF_OK;
     auto fail = [&](int r) { wf_engine_destroy(e); return r; };
@@ -1044,6 +1055,10 @@ extern "C" void* wf_engine_buffer(wf_engine* e, const char* name) {
     if (n == "block_table") return e->d_block_table;
     if (n == "q8") return e->q8;
     if (n == "trace") return e->trace;
+    if (n == "acc_qkv") return e->acc_qkv;
+    if (n == "acc_o") return e->acc_o;
+    if (n == "acc_gu") return e->acc_gu;
+    if (n == "acc_down") return e->acc_down;
     return nullptr;
 }
 

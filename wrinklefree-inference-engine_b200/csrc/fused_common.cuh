@@ -545,6 +545,10 @@ struct HExchangeArgs {
 };
 int launch_h_exchange(const HExchangeArgs& a, cudaStream_t s, bool pdl);
 int launch_gemm_oneshot(const OneshotArgs& a, cudaStream_t s, bool pdl);
+// streaming batched GEMM for 2..32 rows on large matrices (gemm_stream.cu); same contract as the one-shot GEMM
+bool gemm_stream_fits(int M, int N, int K);
+int launch_gemm_stream(const OneshotArgs& a, cudaStream_t s, bool pdl);
+void gemm_stream_init_attrs();
 void fused_init_attrs();
 
 // persistent layer-tail kernel (layer_tail.cu): all linear phases between two attention kernels in one launch

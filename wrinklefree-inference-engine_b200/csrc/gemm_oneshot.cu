@@ -198,6 +198,7 @@ void fused_init_attrs() {
     linear_small_init_attrs();
     layer_tail_init_attrs();
     layer_tail_batch_init_attrs();
+    gemm_stream_init_attrs();
     cudaFuncSetAttribute(gemm_oneshot_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(gemm_oneshot_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(gemm_oneshot_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);

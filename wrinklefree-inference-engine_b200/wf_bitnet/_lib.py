@@ -104,6 +104,7 @@ SYMBOLS = {
     "wf_engine_launches_per_step": (_i, [_vp]),
     "wf_engine_time_kernel": (_i, [_vp, C.c_char_p, _i, _i, C.POINTER(_f)]),
     "wf_bench_gemv": (_i, [_i, _i, _i, _i, _i, C.POINTER(_f)]),
+    "wf_gemm_stream_acc": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _vp]),
 }
 
 _lib = None
