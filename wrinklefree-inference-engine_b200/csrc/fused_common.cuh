@@ -223,11 +223,59 @@ __device__ __forceinline__ float4 handoff_poll_f4(const float* p, int* err, int 
     return make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z), __uint_as_float(v.w));
 }
 
-template <int ID, int NT>
+// Cross-CTA part of the three row reductions of glue_row.  NoXR: the row belongs to one CTA.  ClusterXR: the row is cut into contiguous
+// slices over the CTAs of a thread-block cluster (long rows at small batch: one 512-thread CTA per 28672-element row is 10 us); a CTA
+// leaves its partial in its own shared memory, one cluster barrier, everybody sums the partials in rank order over DSMEM (the same
+// total in every CTA).  The fp32 sum of squares is then cut differently from the one-CTA form — like between the one-CTA forms of
+// different block sizes, the bf16 rounding of 1/rms absorbs that; absmax and the int32 row sum are exact.
+struct NoXR {
+    __device__ __forceinline__ float sum(float v) const { return v; }
+    __device__ __forceinline__ float max(float v) const { return v; }
+    __device__ __forceinline__ int sumi(int v) const { return v; }
+};
+struct ClusterXR {
+    float* slot;     // this CTA's shared float[4] (one word per reduction: no reuse, so no second barrier)
+    int n;           // CTAs in the cluster
+    __device__ __forceinline__ void sync() const {
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
+    __device__ __forceinline__ float peer(const float* q, int r) const {
+        uint32_t ra; float v;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(smem_u32(q)), "r"(r));
+        asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+        return v;
+    }
+    __device__ __forceinline__ float sum(float v) const {
+        if (threadIdx.x == 0) slot[0] = v;
+        sync();
+        float t = 0.f;
+        for (int r = 0; r < n; ++r) t += peer(slot, r);
+        return t;
+    }
+    __device__ __forceinline__ float max(float v) const {
+        if (threadIdx.x == 0) slot[1] = v;
+        sync();
+        float t = 0.f;
+        for (int r = 0; r < n; ++r) t = fmaxf(t, peer(slot + 1, r));
+        return t;
+    }
+    __device__ __forceinline__ int sumi(int v) const {
+        if (threadIdx.x == 0) slot[2] = __int_as_float(v);
+        sync();
+        int t = 0;
+        for (int r = 0; r < n; ++r) t += __float_as_int(peer(slot + 2, r));
+        return t;
+    }
+};
+template <int ID, int NT, class XR = NoXR>
 __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat16* ys, int8_t* qdst, float* fs, int* is,
                                          bool write_side, float& scale_ret, int& rowsum_ret, unsigned long long* tr = nullptr,
-                                         int qmap = QMAP_PLAIN) {
+                                         int qmap = QMAP_PLAIN, int kb = 0, int ke = -1, XR xr = XR()) {
+    // [kb, ke): the slice of the row this CTA works on (the whole row by default); ys holds the slice
     const int K = p.K;
+    const int KE = ke < 0 ? K : ke;
+    __nv_bfloat16* ysb = ys - kb;
     const int tid = threadIdx.x;
     float ss = 0.f;
     // ---- pass 1: x (bf16) -> ys, sum of squares.  All global loads of GU iterations are issued before the first use:
@@ -235,18 +283,18 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
     constexpr int GU = 2;
     if (p.mode == GL_EMBED || p.mode == GL_PLAIN) {
         const __nv_bfloat16* row = (p.mode == GL_EMBED) ? p.embed + (size_t)p.tokens[m] * K : p.src + (size_t)m * K;
-        for (int k0 = tid * 8; k0 < K; k0 += NT * 8 * GU) {
+        for (int k0 = kb + tid * 8; k0 < KE; k0 += NT * 8 * GU) {
             uint4 t[GU];
 #pragma unroll
             for (int u = 0; u < GU; ++u) {
                 const int k = k0 + u * NT * 8;
-                if (k < K) t[u] = ldcg_u4(row + k);
+                if (k < KE) t[u] = ldcg_u4(row + k);
             }
 #pragma unroll
             for (int u = 0; u < GU; ++u) {
                 const int k = k0 + u * NT * 8;
-                if (k < K) {
-                    *reinterpret_cast<uint4*>(ys + k) = t[u];
+                if (k < KE) {
+                    *reinterpret_cast<uint4*>(ysb + k) = t[u];
                     if (write_side && p.hid_out && p.mode == GL_EMBED) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = t[u];
                     const uint32_t w[4] = {t[u].x, t[u].y, t[u].z, t[u].w};
 #pragma unroll
@@ -259,13 +307,13 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
         const float sa = p.acc_ascale[m], ws = p.acc_wscale[0];
         const float* arow = p.acc + (size_t)m * p.acc_ld;
         const __nv_bfloat16* hrow = p.hid_in + (size_t)m * K;
-        for (int k0 = tid * 8; k0 < K; k0 += NT * 8 * GU) {
+        for (int k0 = kb + tid * 8; k0 < KE; k0 += NT * 8 * GU) {
             uint4 t[GU];
             float4 a0[GU], a1[GU];
 #pragma unroll
             for (int u = 0; u < GU; ++u) {
                 const int k = k0 + u * NT * 8;
-                if (k < K) {
+                if (k < KE) {
                     const float* ak = (p.acc_own_cols > 0 ? p.acc_peer[k / p.acc_own_cols] + (size_t)m * p.acc_ld : arow) + k;
                     t[u] = ldcg_u4(hrow + k); a0[u] = ldcg_f4(ak); a1[u] = ldcg_f4(ak + 4);
                 }
@@ -273,7 +321,7 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
 #pragma unroll
             for (int u = 0; u < GU; ++u) {
                 const int k = k0 + u * NT * 8;
-                if (k < K) {
+                if (k < KE) {
                     const float S[8] = {a0[u].x, a0[u].y, a0[u].z, a0[u].w, a1[u].x, a1[u].y, a1[u].z, a1[u].w};
                     const uint32_t hw[4] = {t[u].x, t[u].y, t[u].z, t[u].w};
                     uint32_t o[4];
@@ -286,7 +334,7 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
                         o[i] = pack_bf16x2(x0, x1);
                     }
                     const uint4 ov = make_uint4(o[0], o[1], o[2], o[3]);
-                    *reinterpret_cast<uint4*>(ys + k) = ov;
+                    *reinterpret_cast<uint4*>(ysb + k) = ov;
                     if (write_side && p.hid_out) *reinterpret_cast<uint4*>(p.hid_out + (size_t)m * K + k) = ov;
                 }
             }
@@ -295,7 +343,7 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
         const int rs = p.acc_rowsum[m];
         const float sa = p.acc_ascale[m], wg = p.acc_wscale[0], wu = p.acc_wscale[1];
         const float* arow = p.acc + (size_t)m * p.acc_ld;
-        for (int k = tid * 8; k < K; k += NT * 8) {
+        for (int k = kb + tid * 8; k < KE; k += NT * 8) {
             const int ng = (k >> 4) * 32 + (k & 15);   // gate rows of this 8-group; up rows at +16
             const float4 g0 = ldcg_f4(arow + ng), g1 = ldcg_f4(arow + ng + 4);
             const float4 u0 = ldcg_f4(arow + ng + 16), u1 = ldcg_f4(arow + ng + 20);
@@ -310,20 +358,20 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
                 x[i] = bf16_round(bf16_round(r * r) * uu);
                 ss += x[i] * x[i];
             }
-            *reinterpret_cast<uint4*>(ys + k) =
+            *reinterpret_cast<uint4*>(ysb + k) =
                 make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
         }
     }
     static_assert(NT / 32 <= 16, "scratch layout: 16 slots per reduction");
     if (tr) tr[0] = gtimer();
-    ss = group_sum1<ID, NT>(ss, fs);
+    ss = xr.sum(group_sum1<ID, NT>(ss, fs));
     if (tr) tr[1] = gtimer();
     const float var = ss / (float)K;
     const float r = bf16_round(1.0f / sqrtf(var + p.eps));
     // ---- pass 2: y = bf16(bf16(x*r)*gamma) in place, absmax
     float amax = 0.f;
-    for (int k = tid * 8; k < K; k += NT * 8) {
-        const uint4 t = *reinterpret_cast<const uint4*>(ys + k);
+    for (int k = kb + tid * 8; k < KE; k += NT * 8) {
+        const uint4 t = *reinterpret_cast<const uint4*>(ysb + k);
         const uint4 gq = *reinterpret_cast<const uint4*>(p.gamma + k);
         const uint32_t xw[4] = {t.x, t.y, t.z, t.w}, gw[4] = {gq.x, gq.y, gq.z, gq.w};
         uint32_t o[4];
@@ -335,18 +383,18 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
             o[i] = pack_bf16x2(y0, y1);
         }
         const uint4 ov = make_uint4(o[0], o[1], o[2], o[3]);
-        *reinterpret_cast<uint4*>(ys + k) = ov;
+        *reinterpret_cast<uint4*>(ysb + k) = ov;
         if (write_side && p.y_out) *reinterpret_cast<uint4*>(p.y_out + (size_t)m * K + k) = ov;
     }
     if (tr) tr[2] = gtimer();
-    amax = group_max1<ID, NT>(amax, fs + 16);
+    amax = xr.max(group_max1<ID, NT>(amax, fs + 16));
     if (tr) tr[3] = gtimer();
     const float scale = act_scale_from_absmax(amax);
     const QDiv qd = make_qdiv(scale);
     // ---- pass 3: int8 codes (each thread re-reads exactly what it wrote)
     int psum = 0;
-    for (int k = tid * 8; k < K; k += NT * 8) {
-        const uint4 t = *reinterpret_cast<const uint4*>(ys + k);
+    for (int k = kb + tid * 8; k < KE; k += NT * 8) {
+        const uint4 t = *reinterpret_cast<const uint4*>(ysb + k);
         const uint32_t yw[4] = {t.x, t.y, t.z, t.w};
         uint32_t w0 = 0, w1 = 0;
 #pragma unroll
@@ -369,7 +417,7 @@ __device__ __forceinline__ void glue_row(const GlueParams& p, int m, __nv_bfloat
         }
     }
     if (tr) tr[4] = gtimer();
-    const int total = group_sum_i1<ID, NT>(psum, is);
+    const int total = xr.sumi(group_sum_i1<ID, NT>(psum, is));
     scale_ret = scale;
     rowsum_ret = total;
 }

@@ -322,8 +322,68 @@ int launch_linear_small(const SmallLinArgs& a, cudaStream_t s, bool pdl) {
     return launch_check(cudaLaunchKernelEx(&cfg, linear_small_kernel<0>, p), "linear_small");
 }
 
+// Long rows at small batch: a thread-block cluster of C CTAs per row, each a contiguous slice; the three row reductions are finished over DSMEM
+// (ClusterXR).  grid = (C, M), cluster = (C, 1, 1): blockIdx.x is the rank.
+__global__ void __launch_bounds__(GR_T) glue_rows_cluster_kernel(const GlueParams p) {
+    extern __shared__ __align__(16) unsigned char gsm[];
+    __nv_bfloat16* ys = reinterpret_cast<__nv_bfloat16*>(gsm);
+    __shared__ float fs[32];
+    __shared__ int is[32];
+    __shared__ float xs[4];
+    pdl_launch_dependents();
+    pdl_wait_prior();
+    if (p.wait_flag >= 0) {
+        if (threadIdx.x < 32) tp_wait_flags_warp(p.tp, p.wait_flag);
+        __syncthreads();
+    }
+    {   // accumulator clearing duty, strided over the whole 2-D grid
+        const int gtid = (blockIdx.y * gridDim.x + blockIdx.x) * GR_T + threadIdx.x, gstride = gridDim.x * gridDim.y * GR_T;
+        if (p.zero0)
+            for (int i = gtid * 4; i < p.zero0_n; i += gstride * 4) *reinterpret_cast<float4*>(p.zero0 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (p.zero1)
+            for (int i = gtid * 4; i < p.zero1_n; i += gstride * 4) *reinterpret_cast<float4*>(p.zero1 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const int C = gridDim.x, rank = blockIdx.x, m = blockIdx.y;
+    const int gran = p.K / 8;
+    const int kb = (int)((long long)gran * rank / C) * 8, ke = (int)((long long)gran * (rank + 1) / C) * 8;
+    ClusterXR xr;
+    xr.slot = xs; xr.n = C;
+    float sc; int rsum;
+    glue_row<1, GR_T, ClusterXR>(p, m, ys, p.q_out + (size_t)m * p.K, fs, is, true, sc, rsum, nullptr, QMAP_PLAIN, kb, ke, xr);
+    if (threadIdx.x == 0 && rank == 0) {
+        if (p.scale_out) p.scale_out[m] = sc;
+        if (p.rowsum_out) p.rowsum_out[m] = rsum;
+    }
+    xr.sync();   // nobody leaves while a peer may still read its partials
+}
+
 int launch_glue_rows(const GlueParams& g, cudaStream_t s, bool pdl) {
     if (g.M < 1 || g.K % 8) { set_error("glue_rows: bad shape"); return WF_ERR_INVALID; }
+    // clusters for long rows when the rows alone leave most SMs idle: OPT-IN (WF_GLUE_CLUSTER=1), measured (profiles/r02ax_summary.txt): 70B bs16/8K
+    // 19.84 -> 19.73 ms, bs8/4K 10.74 -> 10.56; forced on shorter rows it loses — 2B bs64/4K 5.10 -> 5.39 ms, 8B bs16/2K 3.05 -> 3.27: a cluster
+    // launch and its three cluster barriers cost more than the second half of a 4096..6912-element row
+    static const int cl_env = getenv("WF_GLUE_CLUSTER") ? atoi(getenv("WF_GLUE_CLUSTER")) : 0;
+    // default: only rows of >= 8192 elements (the 70B widths).  The slices cut the fp32 sum of squares differently from the one-CTA kernels, so the
+    // bit-identity with the one-kernel-per-op path that the tests hold at the 2B / 8B widths (where 1/rms rounds to the same bf16 in all but
+    // ~5e-4 of the rows) is not claimed there; WF_GLUE_CLUSTER=2..8 forces that cluster size for any row of >= 2048 elements (measurement).
+    int C = g.K >= 16384 ? 8 : (g.K >= 8192 ? 4 : 1);
+    if (cl_env > 1 && g.K >= 2048) C = cl_env > 8 ? 8 : cl_env;
+    while (C > 1 && g.M * C > 2 * sm_count()) C >>= 1;
+    if (cl_env && C > 1 && g.q_out) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(C, g.M);
+        cfg.blockDim = dim3(GR_T);
+        cfg.dynamicSmemBytes = ((size_t)(g.K / 8 / C) + 1) * 16;
+        cfg.stream = s;
+        cudaLaunchAttribute at[2];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[1].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = pdl ? 2 : 1;
+        return launch_check(cudaLaunchKernelEx(&cfg, glue_rows_cluster_kernel, g), "glue_rows_cluster");
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(g.M);
     cfg.blockDim = dim3(GR_T);
