@@ -275,6 +275,7 @@ def test_layer_tail_handoff_forms_equal_phase_kernels(shape, monkeypatch):
     rng = np.random.default_rng(3)
     steps = [[int(rng.integers(0, cfg.vocab))] for _ in range(12)]
     runs = {}
+    monkeypatch.setenv("WF_SMALL_MAX", "1")   # (at the 8B widths batch 1 defaults to the row glue + streaming GEMM; this test is about the GEMV-style forms)
     for name, env in (("handoff", {"WF_TAIL": "1", "WF_TAIL_LAM": "1"}), ("barrier", {"WF_TAIL": "1", "WF_TAIL_LAM": "0"}), ("phase", {"WF_TAIL": "0", "WF_TAIL_LAM": "1"})):
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -320,7 +321,7 @@ def test_tcgen05_decode_linears_equal_per_op_kernels(B, ctx, monkeypatch):
         assert (na == nb).all() and (nc == nb).all()
 
 
-@pytest.mark.parametrize("shape,B,ctx", [("2b", 2, 80), ("2b", 13, 200), ("2b", 32, 120), ("8b", 5, 90), ("8b", 16, 150), ("8b", 32, 60)])
+@pytest.mark.parametrize("shape,B,ctx", [("2b", 2, 80), ("2b", 13, 200), ("2b", 32, 120), ("8b", 1, 90), ("8b", 5, 90), ("8b", 16, 150), ("8b", 32, 60)])
 def test_streaming_decode_gemm_equals_default_kernels(shape, B, ctx, monkeypatch):
     """WF_DECODE_STREAM=2: every decode linear of 2..32 rows on the streaming batched GEMM (gemm_stream.cu: K windows, TMA ring, masked
     2-bit fields on mma.sync with M/8 n-tiles, fp32 REDs) — same logits, bit for bit, as the step on the default linears (one-shot /
@@ -333,6 +334,8 @@ def test_streaming_decode_gemm_equals_default_kernels(shape, B, ctx, monkeypatch
     cfg = dataclasses.replace(mk(max_seq=1024, max_batch=B), layers=2, vocab=4096)
     rng = np.random.default_rng(23 + B)
     steps = [list(map(int, rng.integers(0, cfg.vocab, B))) for _ in range(3)]
+    if B == 1:
+        monkeypatch.setenv("WF_SMALL_MAX", "0")   # batch 1 through the row glue + batched GEMM in both runs (the default at the 8B widths)
     monkeypatch.setenv("WF_DECODE_STREAM", "2")
     a = _run_tokens(cfg, None, True, steps, monkeypatch, ctx=ctx, synthetic=5)
     monkeypatch.setenv("WF_DECODE_STREAM", "0")

@@ -641,6 +641,14 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     { const char* x = getenv("WF_DECODE_STREAM"); if (x) e->decode_stream = atoi(x); }
     { const char* x = getenv("WF_DECODE_STREAM_MAX"); if (x) e->decode_stream_max = atoi(x) < 1 ? 1 : (atoi(x) > 32 ? 32 : atoi(x)); }
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
+    // Batch 1 on shapes whose ffn row is too long for the hand-off form of the tail kernel (register glue: <= 9216 elements; the 8B / 70B widths)
+    // goes through the row glue + streaming batched GEMM instead of the grid-barrier tail kernel: 8B bs1 1.97 -> 1.86 ms, 70B bs1 9.32 -> 8.22 ms
+    // (profiles/r02az_summary.txt).  Single-GPU engines only: under tensor parallelism batch 1 keeps the all-RED exchange of the GEMV-style kernels.
+    if (!getenv("WF_SMALL_MAX") && T == 1 && e->decode_stream) {
+        int maxK = e->hidden > e->attn_full ? e->hidden : e->attn_full;
+        if (e->ffn_full > maxK) maxK = e->ffn_full;
+        if (maxK > 9216) e->small_max = 0;
+    }
     int rc = WF_OK;
     auto fail = [&](int r) { wf_engine_destroy(e); return r; };
     if (cuda_check(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking), "stream create")) return fail(WF_ERR_CUDA);
