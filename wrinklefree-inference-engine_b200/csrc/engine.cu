@@ -385,7 +385,10 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
         // tokens up; from 9 tokens for K >= 8192 (70B shapes); from 24 tokens for >= 16 MB matrices.  Measured in profiles/r02q_summary.txt:
         // 70B bs16 32.2 -> 24.6 ms, 8B bs32 4.95 -> 4.84 ms, while 8B bs16 gate|up (29 MB, K = 4096) is faster on the one-shot GEMM.
         const size_t wbytes = (size_t)N * K / 4;
-        if (e->decode_stream && B <= (e->decode_stream >= 2 ? 32 : e->decode_stream_max) && gemm_stream_fits(B, N, K)) {
+        // (17..24 rows: the two-pass form wins where the tcgen05 split-K form does not apply (K < 8192): 8B bs20/2K 4.19 -> 3.91 ms, bs24 4.35 -> 4.06;
+        //  at the 70B widths it loses, 70B bs20/4K 20.0 -> 22.3: profiles/r02bc_summary.txt)
+        const int stream_rows = e->decode_stream >= 2 ? 32 : (K < 8192 && e->decode_stream_max == 16 ? 24 : e->decode_stream_max);
+        if (e->decode_stream && B <= stream_rows && gemm_stream_fits(B, N, K)) {
             OneshotArgs o;
             o.w = w; o.N = N; o.K = K; o.q = e->q8; o.M = B; o.ldq = Kfull; o.k_off = k_off; o.dest = dest; o.acc_ld = N; o.tp = e->tp;
             return launch_gemm_stream(o, s, pdl);
