@@ -213,12 +213,15 @@ def _tp_time(cfg, wl, K, W, rank, world, dist):
 def _tp_parity(rank, world, dist):
     """TP = world vs TP = 1 at the 8B LAYER shape (hidden 4096, 32/8 heads, ffn 14336; 2 layers, vocab 8192): every rank builds the
     same seeded model and keeps its shard, rank 0 also runs the unsharded engine; the final normalised hidden state and the greedy
-    tokens must be BIT-identical at batch 1 (GEMV phases, all-reduce by RED) and batch 32 (batched phases, reduce-scatter + pull)."""
+    tokens must be BIT-identical at batch 1 (GEMV phases, all-reduce by RED), 16 / 20 (streaming batched GEMM, reduce-scatter + pull) and 32 (one-shot / tcgen05 forms)."""
     from wf_bitnet import tp
     from wf_bitnet.engine import Engine, EngineConfig
     from wf_bitnet.synth import make_weights
     ok, detail = True, []
-    for batch, steps, ctx in ((1, 5, 40), (32, 4, 24)):
+    cases = ((1, 5, 40), (16, 4, 24), (20, 3, 24), (32, 4, 24))   # 16 / 20: the streaming batched GEMM under the exchanges
+    if os.environ.get("WF_TP_PARITY_BATCHES"):   # diagnostics: other batch sizes
+        cases = tuple((int(b), 4, 24) for b in os.environ["WF_TP_PARITY_BATCHES"].split(","))
+    for batch, steps, ctx in cases:
         cfg = EngineConfig(hidden=4096, layers=2, heads=32, kv_heads=8, head_dim=128, ffn=14336, vocab=8192, max_seq=128, page_size=16, max_batch=batch)
         weights = make_weights(cfg, seed=11 + batch)
         eng = Engine(cfg, tp_rank=rank, tp_size=world)

@@ -1,0 +1,8 @@
+#!/bin/bash
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+rm -f gpurun_out/summary.txt
+T="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29541 tools/tp_parity_diag.py"
+WF_TP_PARITY_BATCHES=1,16,20,32,16,16,16,16,16,16,16,16 timeout 400 $T 2>&1 | grep DIAG >> gpurun_out/summary.txt
+WF_TP_PARITY_BATCHES=1,16,20,32,16,16,16,16,16,16,16,16 WF_DECODE_STREAM=0 timeout 400 $T 2>&1 | grep DIAG >> gpurun_out/summary.txt
+cat gpurun_out/summary.txt
