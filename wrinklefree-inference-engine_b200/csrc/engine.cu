@@ -645,7 +645,7 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     { const char* x = getenv("WF_DECODE_STREAM_MAX"); if (x) e->decode_stream_max = atoi(x) < 1 ? 1 : (atoi(x) > 32 ? 32 : atoi(x)); }
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
     // Tensor-parallel engines keep the one-shot / tcgen05 linears: with the streaming GEMM under the exchanges TP = 2 at the 8B layer shape, batch 16, was
-    // bit-identical to TP = 1 in 12 of 14 runs only (profiles/r02bf_summary.txt; 0 mismatches in 9 runs without it, 0 in 10 x 7 single-GPU runs) — a
+    // bit-identical to TP = 1 in 12 of 14 runs only (profiles/r02bf_summary.txt; 0 mismatches in 33 runs without it, 0 in 10 x 7 single-GPU runs) — a
     // rare ordering problem between its REDs into peer accumulators and the flag protocol that was not tracked down.  WF_DECODE_STREAM=1 forces it.
     if (T > 1 && !getenv("WF_DECODE_STREAM")) e->decode_stream = 0;
     // Batch 1 on shapes whose ffn row is too long for the hand-off form of the tail kernel (register glue: <= 9216 elements; the 8B / 70B widths)
