@@ -1,4 +1,4 @@
-// Streaming batched ternary GEMM for the decode step, 2..32 activation rows (bitnet_gemm at decode batch sizes; the
+// Streaming batched ternary GEMM for the decode step, 1..32 activation rows (the engine uses it up to 16 rows, 24 where K < 8192, and for batch 1 at the 8B / 70B widths) (bitnet_gemm at decode batch sizes; the
 // engine's linears on the 8B / 70B matrices, DESIGN 7 gap 3).
 //
 //   acc[m, n] += sum_k code[n, k] * a[m, k]        exact integers in fp32 (|S| < 2^24), RED into the step's split-K accumulators
@@ -16,8 +16,8 @@
 //   * 8 consumer warps, warp j takes k-blocks j, j + 8, ... of the unit.  A lane's 16-byte LDS is its four mma A-fragment words; the 2-bit
 //     fields are masked IN PLACE (one AND per fragment, four k-groups -> four accumulators, shifted back at the flush: exact), activations
 //     come through ldmatrix from a skewed copy, M/8 n-tiles of mma.sync.m16n8k32.u8.s8 share every weight fragment;
-//   * per unit: warps add their partial sums into a double-buffered [M][16] shared tile, one consumer barrier, 4 * M lanes issue
-//     red.global.add.v4.f32 into the accumulator (or, tensor parallel, into the owner rank's / every rank's accumulator, as the one-shot GEMM).
+//   * per unit: warps add their partial sums into a double-buffered shared tile laid out [n-tile][fragment register][lane] (every lane its own
+//     bank), one consumer barrier, 4 * M lanes (a duty that rotates over the warps) issue red.global.add.v4.f32 into the accumulator (or, tensor parallel, into the owner rank's / every rank's accumulator, as the one-shot GEMM).
 #include "fused_common.cuh"
 
 namespace wf {
