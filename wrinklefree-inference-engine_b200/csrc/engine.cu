@@ -80,6 +80,7 @@ struct wf_engine {
                              // GEMM: bit-identical; with the round-2 issue loop / epilogue 3.65 -> 3.23 ms at batch 40 / 2K, 5.48 -> 5.32 ms at batch 64 / 4K (WF_DECODE_TC=0: off)
     int decode_tc_min = 33;  // WF_DECODE_TC_MIN
     int decode_stream = 1;   // WF_DECODE_STREAM: streaming batched GEMM (gemm_stream.cu); 0 off, 1 = batches up to decode_stream_max rows, 2 = every batch it takes (<= 32)
+    int decode_stream_mask = 15;  // WF_DECODE_STREAM_MASK: which linears may take it (1 q|k|v, 2 o, 4 gate|up, 8 down) — for bisecting the TP mismatch
     int decode_stream_max = 16;   // WF_DECODE_STREAM_MAX.  Measured (profiles/r02ap_summary.txt), ms per step stream / default: 2B bs2 1.33 / 1.58, bs8 1.43 / 1.63,
                                   // bs16/2K 1.99 / 2.17; 8B bs4 1.97 / 3.00, bs8 2.26 / 3.24, bs16/2K 3.06 / 3.85; 70B bs16/8K 20.0 / 22.9; but 17..32 rows (four n-tiles,
                                   // one CTA per SM): 2B bs32/2K 2.74 / 2.56, 8B bs32/2K 4.55 / 4.20
@@ -388,7 +389,7 @@ int run_step_fused(wf_engine* e, int B, int feed_back) {
         // (17..24 rows: the two-pass form wins where the tcgen05 split-K form does not apply (K < 8192): 8B bs20/2K 4.19 -> 3.91 ms, bs24 4.35 -> 4.06;
         //  at the 70B widths it loses, 70B bs20/4K 20.0 -> 22.3: profiles/r02bc_summary.txt)
         const int stream_rows = e->decode_stream >= 2 ? 32 : (K < 8192 && e->decode_stream_max == 16 ? 24 : e->decode_stream_max);
-        if (e->decode_stream && B <= stream_rows && gemm_stream_fits(B, N, K)) {
+        if (e->decode_stream && ((e->decode_stream_mask >> slot) & 1) && B <= stream_rows && gemm_stream_fits(B, N, K)) {
             OneshotArgs o;
             o.w = w; o.N = N; o.K = K; o.q = e->q8; o.M = B; o.ldq = Kfull; o.k_off = k_off; o.dest = dest; o.acc_ld = N; o.tp = e->tp;
             return launch_gemm_stream(o, s, pdl);
@@ -642,6 +643,7 @@ extern "C" int wf_engine_create(const wf_model_config* cfg, wf_engine** out) {
     { const char* x = getenv("WF_DECODE_TC"); if (x) e->decode_tc = atoi(x) != 0; }
     { const char* x = getenv("WF_DECODE_TC_MIN"); if (x) e->decode_tc_min = atoi(x) < 2 ? 2 : atoi(x); }
     { const char* x = getenv("WF_DECODE_STREAM"); if (x) e->decode_stream = atoi(x); }
+    { const char* x = getenv("WF_DECODE_STREAM_MASK"); if (x) e->decode_stream_mask = atoi(x) & 15; }
     { const char* x = getenv("WF_DECODE_STREAM_MAX"); if (x) e->decode_stream_max = atoi(x) < 1 ? 1 : (atoi(x) > 32 ? 32 : atoi(x)); }
     if (e->fused && !env_pdl) e->pdl = true;   // the phase kernels are built around programmatic dependent launch
     // Tensor-parallel engines keep the one-shot / tcgen05 linears: with the streaming GEMM under the exchanges TP = 2 at the 8B layer shape, batch 16, was
