@@ -5,7 +5,7 @@ cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
 nproc >> gpurun_out/gpu.txt
-for f in tests/test_gpu_pack_quant.py tests/test_gpu_linear.py tests/test_gpu_attention.py tests/test_gpu_engine.py tests/test_gpu_gemm_tc.py tests/test_gpu_loader.py tests/test_gpu_sglang_model.py tests/test_gpu_kv_int8.py; do
+for f in tests/test_gpu_pack_quant.py tests/test_gpu_linear.py tests/test_gpu_attention.py tests/test_gpu_engine.py tests/test_gpu_gemm_tc.py tests/test_gpu_loader.py tests/test_gpu_sglang_model.py tests/test_gpu_kv_int8.py tests/test_zz_no_alloc.py; do
   b=$(basename $f .py)
   timeout ${TEST_TIMEOUT:-600} python -m pytest $f -m gpu -q --no-header -rf -p no:cacheprovider > gpurun_out/$b.log 2>&1
   echo "$b exit=$?" >> gpurun_out/summary.txt
